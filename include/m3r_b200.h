@@ -1,0 +1,226 @@
+/*
+ * m3r_b200.h — C ABI of libm3r_b200.so: B200 (sm_100a) dense matching and Sim3
+ * Gauss-Newton registration, the drop-in for MASt3R-SLAM's `mast3r_slam_backends`
+ * extension (reference: mast3r_slam/backend/include/gn.h, src/gn.cpp:116-122).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer to a dense, contiguous, row-major array
+ *     (the reference asserts contiguity only: gn.h:5, gn.cpp:14-21,92-94,108-110);
+ *   - `stream` is a cudaStream_t passed as an opaque pointer; all work is enqueued
+ *     on it and the call returns without synchronising (the reference launches on
+ *     the legacy default stream and blocks: matching_kernels.cu:104,303,
+ *     gn_kernels.cu:1183-1220);
+ *   - the library never allocates or frees device memory: outputs and workspace are
+ *     caller-owned (the reference allocates with torch::zeros per call:
+ *     matching_kernels.cu:99-101,295-301; gn_kernels.cu:1173-1174);
+ *   - return value: 0 on success, a negative M3R_E* code for usage/launch errors.
+ *     Numerical failure (non-SPD system) is NOT an error: like the reference
+ *     (gn_kernels.cu:142-150) the step is zero and the poses are left unchanged;
+ *   - bool tensors are one byte per element (torch.bool).
+ *
+ * No torch types appear here; the Python package `mast3r_slam_backends` binds these
+ * with ctypes and owns all allocations.
+ */
+#ifndef M3R_B200_H
+#define M3R_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* m3r_stream_t; /* cudaStream_t */
+
+enum {
+  M3R_OK = 0,
+  M3R_EINVAL = -1,    /* bad shape / null pointer / unsupported parameter */
+  M3R_ELAUNCH = -2,   /* CUDA launch or runtime error (see m3r_last_cuda_error) */
+  M3R_EWORKSPACE = -3 /* workspace too small */
+};
+
+/* Residual family of a Gauss-Newton accumulation pass. */
+enum {
+  M3R_GN_RAYS = 0,  /* ray_align_kernel   gn_kernels.cu:813-1138  (4 residuals / point) */
+  M3R_GN_CALIB = 1, /* calib_proj_kernel  gn_kernels.cu:1231-1543 (3 residuals / point) */
+  M3R_GN_POINTS = 2 /* point_align_kernel gn_kernels.cu:455-723   (3 residuals / point) */
+};
+
+int m3r_version(void);
+const char* m3r_error_string(int code);
+/* cudaError_t of the last failing runtime call on this thread (0 if none). */
+int m3r_last_cuda_error(void);
+/* Number of kernels this library has launched in this process (bench `gpu_launches`). */
+unsigned long long m3r_launch_count(void);
+
+/* ------------------------------------------------------------------------- *
+ * Dense matching
+ * ------------------------------------------------------------------------- */
+
+/* iter_proj — replaces mast3r_slam_backends.iter_proj (gn.cpp:84-99,
+ * matching_kernels.cu:119-315).  Per query pixel: <= max_iter Levenberg-Marquardt
+ * steps on (u,v) minimising |normalize(bilinear(ray_img)(u,v)) - target_ray|^2.
+ *   rays_img_with_grad (b,H,W,9) f32   [ray(3), d ray/du (3), d ray/dv (3)]
+ *   pts_3d_norm        (b,n,3)   f32   unit target rays
+ *   p_init             (b,n,2)   f32   initial (u,v)
+ *   p_new              (b,n,2)   f32   out
+ *   converged          (b,n)     u8    out (torch.bool)
+ * Unlike the reference (no bounds guard, matching_kernels.cu:131) any n is safe. */
+int m3r_iter_proj(const float* rays_img_with_grad, const float* pts_3d_norm,
+                  const float* p_init, int b, int H, int W, int n, int max_iter,
+                  float lambda_init, float cost_thresh, float* p_new,
+                  uint8_t* converged, m3r_stream_t stream);
+
+/* refine_matches, fp16 descriptors — replaces mast3r_slam_backends.refine_matches
+ * for the dtype its only caller uses (matching.py:79-85; gn.cpp:101-114,
+ * matching_kernels.cu:25-116).  Dilated (2*radius+1)^2 window argmax of the
+ * descriptor dot product, dilation_max..1, re-centred per dilation; scores are
+ * accumulated in the reference's sequential fp16-rounded order and compared with
+ * strict `>` starting from fp16 zero, so p1_new is bit-exact.
+ *   D11 (b,H,W,F) f16 ; D21 (b,n,F) f16 ; p1 (b,n,2) i64 (u,v) ; p1_new (b,n,2) i64
+ * F must be a multiple of 8 and <= 64 (MASt3R: 24). */
+int m3r_refine_matches_f16(const uint16_t* D11, const uint16_t* D21,
+                           const int64_t* p1, int b, int H, int W, int n, int F,
+                           int radius, int dilation_max, int64_t* p1_new,
+                           m3r_stream_t stream);
+
+/* refine_matches, fp32 descriptors (the reference's <float> instantiation:
+ * sequential `score += a*b` in fp32, initial max = FLT_MIN). */
+int m3r_refine_matches_f32(const float* D11, const float* D21, const int64_t* p1,
+                           int b, int H, int W, int n, int F, int radius,
+                           int dilation_max, int64_t* p1_new, m3r_stream_t stream);
+
+/* Fused caller-side glue of matching.match_iterative_proj (matching.py:25-90,
+ * image.py:5-38): everything around the two kernels above in three launches.
+ *
+ * m3r_match_prep: X11 (b,H,W,3) f32 -> rays_img_with_grad (b,H,W,9) f32
+ *   (F.normalize eps 1e-12, reflect-padded 3x3 [-3,0,3;-10,0,10;-3,0,3]/32 gradients),
+ *   and D11 (b,H,W,F) f32 -> D11h (b,H,W,F) f16 (round-to-nearest-even, == .half()).
+ *   Either half may be skipped by passing NULL for its output. */
+int m3r_match_prep(const float* X11, const float* D11, int b, int H, int W, int F,
+                   float* rays_img_with_grad, uint16_t* D11h, m3r_stream_t stream);
+
+/* m3r_match_iter_proj_fused: iter_proj with the caller's pre/post-processing fused:
+ *   target rays = normalize(X21) computed on the fly; p_init = (idx%W, idx/W) from
+ *   idx_init (b,n) i64 or the identity map when idx_init == NULL; after the LM loop
+ *   p1 = trunc(p_new) and valid = converged & (|X11[p1] - X21| < dist_thresh).
+ *   Outputs: p1 (b,n,2) i64 and valid (b,n) u8; p_new (b,n,2) f32 optional (NULL ok). */
+int m3r_match_iter_proj_fused(const float* rays_img_with_grad, const float* X11,
+                              const float* X21, const int64_t* idx_init, int b, int H,
+                              int W, int max_iter, float lambda_init,
+                              float cost_thresh, float dist_thresh, int64_t* p1,
+                              uint8_t* valid, float* p_new, m3r_stream_t stream);
+
+/* m3r_match_refine_fused: refine_matches reading D21 as f32 (rounded to f16 on the
+ * fly, == .half()) against the f16 copy of D11 made by m3r_match_prep, and writing
+ * the linear index idx_1_to_2 = u + W*v (pixel_to_lin, matching.py:13-15).
+ * radius == 0 skips the search (idx from p1 directly, matching.py:78). */
+int m3r_match_refine_fused(const uint16_t* D11h, const float* D21, const int64_t* p1,
+                           int b, int H, int W, int F, int radius, int dilation_max,
+                           int64_t* idx_1_to_2, m3r_stream_t stream);
+
+/* ------------------------------------------------------------------------- *
+ * Sim3 retraction
+ * ------------------------------------------------------------------------- */
+
+/* pose_retr — T_k <- Exp(dx_{k-num_fix}) * T_k for k >= num_fix
+ * (pose_retr_kernel / retrSim3 / expSim3 / expSO3, gn_kernels.cu:299-453).
+ *   poses (N,8) f32 [t(3), q(xyzw), s] in place ; dx (N-num_fix,7) f32 [tau, phi, sigma] */
+int m3r_pose_retr(float* poses, const float* dx, int num_poses, int num_fix,
+                  m3r_stream_t stream);
+
+/* ------------------------------------------------------------------------- *
+ * Sim3 factor-graph Gauss-Newton
+ * ------------------------------------------------------------------------- */
+
+typedef struct m3r_gn_params {
+  int mode;           /* M3R_GN_RAYS | M3R_GN_CALIB | M3R_GN_POINTS */
+  float sigma_a;      /* rays: sigma_ray   | calib: sigma_pixel | points: sigma_point */
+  float sigma_b;      /* rays: sigma_dist  | calib: sigma_depth | points: unused      */
+  float C_thresh;
+  float Q_thresh;
+  /* calib only (gn.h:74-87) */
+  float fx, fy, cx, cy; /* K[0][0], K[1][1], K[0][2], K[1][2]  (gn_kernels.cu:1274-1279) */
+  int height, width, pixel_border;
+  float z_eps;
+} m3r_gn_params;
+
+/* Bytes of caller-provided scratch needed by the m3r_gn_* calls for a graph with
+ * num_poses keyframes, num_edges directed edges (of which at most local_edges are
+ * accumulated by this process) and n points per keyframe. */
+size_t m3r_gn_workspace_bytes(int num_poses, int num_edges, int local_edges, int n);
+
+/* One call == mast3r_slam_backends.gauss_newton_{rays,calib,points}
+ * (gn.cpp:3-82; host loops gn_kernels.cu:725-811,1140-1228,1546-1638).
+ *   Twc (N,8) f32 in/out ; Xs (N,n,3) f32 ; Cs (N,n,1) f32 ; ii,jj (M) i64 keyframe ids ;
+ *   idx_ii2jj (M,n) i64 ; valid_match (M,n,1) u8 ; Q (M,n,1) f32 ;
+ *   dx (N-1,7) f32 out: the last iteration's update (zeros if max_iter == 0).
+ * Rows of Twc/Xs/Cs follow the sorted unique keyframe ids of cat(ii,jj); the first
+ * row is the gauge (num_fix = 1, gn_kernels.cu:1157).  The whole loop — index setup,
+ * accumulation, assembly, fp64 Cholesky, retraction, |dx| < delta_thresh early exit —
+ * runs on `stream` with no host synchronisation. */
+int m3r_gauss_newton(const m3r_gn_params* prm, float* Twc, const float* Xs,
+                     const float* Cs, const int64_t* ii, const int64_t* jj,
+                     const int64_t* idx_ii2jj, const uint8_t* valid_match,
+                     const float* Q, int num_poses, int n, int num_edges,
+                     int max_iter, float delta_thresh, float* dx, void* workspace,
+                     size_t workspace_bytes, m3r_stream_t stream);
+
+/* Stepwise form of the same loop, for edge-sharded multi-GPU solves (each process
+ * accumulates its slice of the edge list, the per-edge blocks are exchanged with an
+ * NCCL all-gather, every process then runs the identical replicated solve) and for
+ * block-level parity tests.
+ *
+ * m3r_gn_prepare: once per solve.  Maps keyframe ids to pose rows
+ *   (get_unique_kf_idx/create_inds, gn_kernels.cu:161-170) for ALL num_edges edges,
+ *   builds the pose->edge adjacency used by the deterministic assembly, packs
+ *   (Xs,Cs) as float4 and resets the convergence flag.
+ * m3r_gn_accumulate: one pass over directed edges [edge_begin, edge_begin+edge_count).
+ *   The per-edge stream pointers (idx_ii2jj, valid_match, Q) address the LOCAL slice,
+ *   i.e. row 0 is edge `edge_begin`.  Writes blocks[e] for those edges, e global:
+ *   56 doubles per edge = S (7x7, row-major) followed by v (7), where in the
+ *   reference's layout (gn_kernels.cu:1096-1137)
+ *     Hs[0][e] = Hs[3][e] = S, Hs[1][e] = Hs[2][e] = -S, gs[1][e] = v, gs[0][e] = -v.
+ * m3r_gn_solve_step: assemble all num_edges blocks, factorise, dx = -x, retract Twc,
+ *   set the convergence flag if |dx| < delta_thresh.  Once the flag is set,
+ *   m3r_gn_accumulate and m3r_gn_solve_step become no-ops (the reference's `break`). */
+int m3r_gn_prepare(const float* Xs, const float* Cs, const int64_t* ii,
+                   const int64_t* jj, int num_poses, int n, int num_edges,
+                   int local_edges, void* workspace, size_t workspace_bytes,
+                   m3r_stream_t stream);
+int m3r_gn_accumulate(const m3r_gn_params* prm, const float* Twc,
+                      const int64_t* idx_ii2jj, const uint8_t* valid_match,
+                      const float* Q, int num_poses, int n, int num_edges,
+                      int edge_begin, int edge_count, double* blocks, void* workspace,
+                      size_t workspace_bytes, m3r_stream_t stream);
+int m3r_gn_solve_step(float* Twc, const double* blocks, int num_poses, int num_edges,
+                      float delta_thresh, float* dx, void* workspace,
+                      size_t workspace_bytes, m3r_stream_t stream);
+/* Device pointer (inside workspace) of the int32 convergence flag: 0 running, 1 done. */
+int* m3r_gn_done_flag(void* workspace);
+/* Device pointer (inside workspace) of the per-edge block buffer (num_edges*56 doubles). */
+double* m3r_gn_blocks(void* workspace, int num_poses, int num_edges, int local_edges, int n);
+
+/* ------------------------------------------------------------------------- *
+ * Two-frame tracker solve
+ * ------------------------------------------------------------------------- */
+
+/* Whole FrameTracker.opt_pose_ray_dist_sim3 loop (tracker.py:156-214 with
+ * geometry.py:17-52, nonlinear_optimizer.py:5-33) in one launch sequence:
+ *   Xf (n,3), Xk (n,3) f32 ; Qk (n,1) f32 ; valid (n,1) u8 ;
+ *   T_CkCf (8) f32 in/out [t, q(xyzw), s]: relative pose, updated in place ;
+ *   status (4) i32 out: [iterations run, converged(0/1), cholesky_failed(0/1), reserved] ;
+ *   cost (max_iters) f32 out: cost at each iteration (0.5*b^T b) — optional (NULL ok).
+ * Stops when |d cost / cost| < rel_error or |tau| < delta_norm, or after max_iters. */
+size_t m3r_track_workspace_bytes(int n);
+int m3r_track_ray_dist(const float* Xf, const float* Xk, const float* Qk,
+                       const uint8_t* valid, int n, float sigma_ray, float sigma_dist,
+                       float huber_k, int max_iters, float rel_error, float delta_norm,
+                       float* T_CkCf, int* status, float* cost, void* workspace,
+                       size_t workspace_bytes, m3r_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* M3R_B200_H */
