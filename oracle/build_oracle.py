@@ -1,0 +1,21 @@
+"""Compile oracle/m3r_oracle.c (the CPU restatement; TEST INFRASTRUCTURE ONLY) with gcc."""
+import os
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SRC = os.path.join(HERE, "m3r_oracle.c")
+LIB = os.path.join(HERE, "libm3r_oracle.so")
+
+
+def build(force=False):
+    if (not force and os.path.exists(LIB)
+            and os.path.getmtime(LIB) >= os.path.getmtime(SRC)):
+        return LIB
+    cmd = ["gcc", "-O2", "-ffp-contract=off", "-fopenmp", "-shared", "-fPIC",
+           "-Wall", "-o", LIB, SRC, "-lm"]
+    subprocess.check_call(cmd)
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force=True))
