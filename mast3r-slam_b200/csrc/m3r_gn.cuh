@@ -1,0 +1,90 @@
+// m3r_gn.cuh — workspace layout shared by the Gauss-Newton kernels (m3r_gn_*.cu).
+//
+// HBM layout of one solve (all inside the caller-provided workspace, 256-B aligned):
+//   hdr      : GnHeader (flags, counters)
+//   ie, je   : int32[M]      pose row of each directed edge's i / j keyframe
+//   keys     : int64[P]      sort scratch (P = pow2 >= 2M)
+//   rank     : int32[P]      rank of each sorted key among the unique ids
+//   row_ptr  : int32[N+1]    CSR over pose rows -> incident (edge, role) slots
+//   adj      : int32[2M]     slot = e (pose is the i end) or M+e (pose is the j end)
+//   xc       : float4[N*n]   (X, C) packed: one 16-B aligned gather per correspondence
+//   part     : float[Ml*S*36] per-CTA partial sums of the LOCAL 28+7 normal-equation terms
+//   blocks   : double[M*56]  per-edge S (7x7) and v (7) after the adjoint transform
+//   A        : double[Dp*Dp] augmented normal matrix [H b; b^T 1], padded to 32
+//   x        : double[2*Dp]  forward-substituted rhs y, then the solution x
+#pragma once
+#include "m3r_common.cuh"
+
+namespace m3r {
+
+constexpr int kGnNB = 32;        // Cholesky panel width
+constexpr int kGnPartStride = 36;  // 28 + 7 (+1 pad) floats per partial
+constexpr int kGnBlock = 56;     // doubles per edge block: S(49) + v(7)
+
+struct GnHeader {
+  int done;        // 1 once |dx| < delta_thresh (the reference's `break`)
+  int chol_fail;   // set by the factorisation of the current iteration
+  int iters;       // iterations actually executed
+  int pad;
+};
+
+struct GnLayout {
+  size_t hdr, ie, je, keys, rank, row_ptr, adj, xc, part, blocks, A, x, total;
+  int P;       // sort size
+  int S;       // point splits per edge
+  int chunk;   // points per split
+  int D;       // 7*(N-1)
+  int Dp;      // padded dimension of the augmented system
+};
+
+inline int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+// Splits per edge depend only on (n, M) — never on how many edges THIS process owns —
+// so an edge's block is bit-identical whether the graph is solved on 1 GPU or sharded.
+inline void gn_splits(int n, int M, int& S, int& chunk) {
+  const int unit = 1024;  // 256 threads x 4 points
+  int want = (8 * 2 * kNumSMs + (M > 0 ? M : 1) - 1) / (M > 0 ? M : 1);  // ~8 waves of 2 CTA/SM
+  if (want < 1) want = 1;
+  if (want > 32) want = 32;
+  int max_s = (n + unit - 1) / unit;
+  if (max_s < 1) max_s = 1;
+  if (want > max_s) want = max_s;
+  chunk = ((n + want - 1) / want + unit - 1) / unit * unit;
+  S = (n + chunk - 1) / chunk;
+  if (S < 1) S = 1;
+}
+
+inline GnLayout gn_layout(int N, int M, int Ml, int n) {
+  GnLayout L;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
+  L.P = next_pow2(2 * (M > 0 ? M : 1));
+  gn_splits(n, M, L.S, L.chunk);
+  L.D = 7 * (N - 1);
+  L.Dp = (L.D + 1 + kGnNB - 1) / kGnNB * kGnNB;
+  L.hdr = take(sizeof(GnHeader));
+  L.ie = take(sizeof(int) * (size_t)M);
+  L.je = take(sizeof(int) * (size_t)M);
+  L.keys = take(sizeof(int64_t) * (size_t)L.P);
+  L.rank = take(sizeof(int) * (size_t)L.P);
+  L.row_ptr = take(sizeof(int) * (size_t)(N + 1));
+  L.adj = take(sizeof(int) * (size_t)2 * M);
+  L.blocks = take(sizeof(double) * (size_t)M * kGnBlock);
+  L.A = take(sizeof(double) * (size_t)L.Dp * L.Dp);
+  L.x = take(sizeof(double) * (size_t)2 * L.Dp);  // y (work) and x (solution)
+  // n- and Ml-dependent arrays last: every offset above depends on (N, M) only, `xc` on
+  // (N, M, n), and only the TOTAL depends on how many edges this process accumulates.
+  L.xc = take(sizeof(float4) * (size_t)N * n);
+  L.part = take(sizeof(float) * (size_t)Ml * L.S * kGnPartStride);
+  L.total = off;
+  return L;
+}
+
+template <typename T>
+inline T* ws_ptr(void* ws, size_t off) { return reinterpret_cast<T*>(static_cast<char*>(ws) + off); }
+
+// m3r_gn_solve.cu
+int gn_solve_launch(float* Twc, const double* blocks, int N, int M, float delta_thresh, float* dx,
+                    void* ws, const GnLayout& L, cudaStream_t st);
+
+}  // namespace m3r

@@ -1,0 +1,479 @@
+// m3r_gn_accum.cu — Sim3 factor-graph Gauss-Newton: index setup, packing and the fused
+// residual + Jacobian + normal-equation accumulation kernels (sm_100a).
+//
+// Replaces ray_align_kernel / calib_proj_kernel / point_align_kernel and the index helpers
+// of the reference (gn_kernels.cu:161-170, 455-723, 813-1138, 1231-1543).
+//
+// What is different from the reference, and why:
+//   * The reference pushes every Jacobian row through apply_Sim3_adj_inv(T_i) per point and
+//     accumulates a 14x14 upper triangle (105 values, in local memory) plus 2x7 gradients.
+//     Since Ji = -Jj and Jj = J_local * Adj(T_i)^-1 with Adj constant per edge, this kernel
+//     accumulates only the LOCAL 7x7 (28 unique values) + 7 gradient values in registers,
+//     skipping the structural zeros of each residual row at compile time, and the adjoint is
+//     applied once per edge afterwards, in fp64 (gn_edge_finish_kernel).  This moves the pass
+//     from ALU/local-memory bound to HBM bound.
+//   * Each directed edge is split over S CTAs (the reference runs one 256-thread CTA per edge)
+//     and reduced in two fixed-order stages, so the result is deterministic and independent of
+//     how edges are distributed over GPUs.
+//   * (Xs, Cs) are packed once per solve as float4, so the Xi/Ci gather is one aligned 16-B
+//     load and the Xj/Cj stream is a coalesced 128-bit load.
+#include "m3r_gn.cuh"
+#include "m3r_sim3.cuh"
+
+namespace m3r {
+
+// ------------------------------------------------------------------------------------
+// Index setup: unique sorted keyframe ids -> pose rows, CSR pose -> incident edge slots.
+// ------------------------------------------------------------------------------------
+constexpr int kIdxThreads = 1024;
+constexpr int kIdxSmemKeys = 4096;
+
+__device__ void bitonic_sort_block(int64_t* buf, int P) {
+  for (int k = 2; k <= P; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = threadIdx.x; t < P; t += blockDim.x) {
+        const int x = t ^ j;
+        if (x > t) {
+          const bool asc = (t & k) == 0;
+          const int64_t a = buf[t], b = buf[x];
+          if ((a > b) == asc) { buf[t] = b; buf[x] = a; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+__device__ __forceinline__ int lower_bound_i64(const int64_t* a, int len, int64_t v) {
+  int lo = 0, hi = len;
+  while (lo < hi) { const int mid = (lo + hi) >> 1; if (a[mid] < v) lo = mid + 1; else hi = mid; }
+  return lo;
+}
+
+__global__ void __launch_bounds__(kIdxThreads)
+gn_index_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, int M, int N, int P,
+                int64_t* keys, int* rank, int* ie, int* je, int* row_ptr, int* adj, GnHeader* hdr) {
+  __shared__ int64_t skeys[kIdxSmemKeys];
+  __shared__ int scan[kIdxThreads];
+  const int tid = threadIdx.x;
+  if (tid == 0) { hdr->done = 0; hdr->chol_fail = 0; hdr->iters = 0; hdr->pad = 0; }
+  int64_t* buf = (P <= kIdxSmemKeys) ? skeys : keys;
+  const int64_t kMax = 0x7fffffffffffffffLL;
+  // 1. sorted keyframe ids  (torch::_unique(cat(ii,jj), sorted), gn_kernels.cu:161-164)
+  for (int t = tid; t < P; t += kIdxThreads) buf[t] = t < M ? ii[t] : (t < 2 * M ? jj[t - M] : kMax);
+  __syncthreads();
+  bitonic_sort_block(buf, P);
+  // 2. rank[t] = (#distinct ids in buf[0..t]) - 1
+  const int per = (P + kIdxThreads - 1) / kIdxThreads;
+  const int t0 = tid * per, t1 = min(P, t0 + per);
+  int cnt = 0;
+  for (int t = t0; t < t1; t++) cnt += (t == 0 || buf[t] != buf[t - 1]) ? 1 : 0;
+  scan[tid] = cnt;
+  __syncthreads();
+  for (int o = 1; o < kIdxThreads; o <<= 1) {
+    const int v = tid >= o ? scan[tid - o] : 0;
+    __syncthreads();
+    scan[tid] += v;
+    __syncthreads();
+  }
+  int run = scan[tid] - cnt;  // exclusive prefix
+  for (int t = t0; t < t1; t++) {
+    run += (t == 0 || buf[t] != buf[t - 1]) ? 1 : 0;
+    rank[t] = run - 1;
+  }
+  __syncthreads();
+  // 3. searchsorted (create_inds, gn_kernels.cu:166-170)
+  for (int e = tid; e < M; e += kIdxThreads) {
+    ie[e] = rank[lower_bound_i64(buf, 2 * M, ii[e])];
+    je[e] = rank[lower_bound_i64(buf, 2 * M, jj[e])];
+  }
+  __syncthreads();
+  // 4. CSR: sort (row, slot) pairs; slot < M: pose is the i end of edge slot, else j end of slot-M
+  const int64_t span = 2 * (int64_t)M;
+  for (int t = tid; t < P; t += kIdxThreads)
+    buf[t] = t < 2 * M ? (int64_t)(t < M ? ie[t] : je[t - M]) * span + t : kMax;
+  __syncthreads();
+  bitonic_sort_block(buf, P);
+  for (int t = tid; t < 2 * M; t += kIdxThreads) adj[t] = (int)(buf[t] % span);
+  for (int r = tid; r <= N; r += kIdxThreads) row_ptr[r] = lower_bound_i64(buf, 2 * M, (int64_t)r * span);
+}
+
+// (Xs (N,n,3), Cs (N,n,1)) -> float4 (x,y,z,c)
+__global__ void __launch_bounds__(256)
+gn_pack_kernel(const float* __restrict__ Xs, const float* __restrict__ Cs, size_t count,
+               float4* __restrict__ xc) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
+    xc[i] = make_float4(ld_stream_f(Xs + 3 * i), ld_stream_f(Xs + 3 * i + 1),
+                        ld_stream_f(Xs + 3 * i + 2), ld_stream_f(Cs + i));
+  }
+}
+
+// ------------------------------------------------------------------------------------
+// Accumulation
+// ------------------------------------------------------------------------------------
+struct GnDev {  // kernel-side copy of m3r_gn_params with the sigmas pre-inverted
+  float inv_var_a, inv_var_b;  // 1/sigma^2
+  float C_thresh, Q_thresh;
+  float fx, fy, cx, cy;
+  float u_lo, u_hi, v_lo, v_hi;  // pixel_border, width-1-border, ... as floats
+  float z_eps;
+  int width;
+};
+
+__device__ __forceinline__ float fast_rcp(float x) {
+  float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r;
+}
+
+// h: upper^T packed 7x7 (index a*(a+1)/2 + c, c <= a); skips Jacobian entries whose bit is
+// clear in MASK (structural zeros of the residual row) at compile time.
+template <unsigned MASK>
+__device__ __forceinline__ void acc_row(float* h, float* g, float w, float e, const float* J) {
+  float wJ[7];
+#pragma unroll
+  for (int a = 0; a < 7; a++)
+    if ((MASK >> a) & 1u) wJ[a] = w * J[a];
+#pragma unroll
+  for (int a = 0; a < 7; a++) {
+    if (!((MASK >> a) & 1u)) continue;
+#pragma unroll
+    for (int c = 0; c <= a; c++)
+      if ((MASK >> c) & 1u) h[a * (a + 1) / 2 + c] = fmaf(wJ[a], J[c], h[a * (a + 1) / 2 + c]);
+    g[a] = fmaf(wJ[a], e, g[a]);
+  }
+}
+
+// Huber-robustified weight.  Reference: w = huber(sqrt_w * err) * sqrt_w^2 with
+// sqrt_w = sigma^-1 sqrt(q) (gn_kernels.cu:963-978); |sqrt_w err| < k  <=>  wc err^2 < k^2.
+__device__ __forceinline__ float robust_weight(float wc, float err) {
+  const float s2 = wc * err * err;
+  const float hub = s2 < 1.345f * 1.345f ? 1.0f : 1.345f * rsqrtf(s2);
+  return hub * wc;
+}
+
+template <int MODE>
+__device__ __forceinline__ void point_terms(const GnDev& prm, const float* R, const float* t,
+                                            const float4 xi, const float4 xj, long long ind,
+                                            float q, bool vm, float* h, float* g) {
+  // P = s_ij R_ij Xj + t_ij  (actSim3, gn_kernels.cu:207-219)
+  const float Px = fmaf(R[0], xj.x, fmaf(R[1], xj.y, fmaf(R[2], xj.z, t[0])));
+  const float Py = fmaf(R[3], xj.x, fmaf(R[4], xj.y, fmaf(R[5], xj.z, t[1])));
+  const float Pz = fmaf(R[6], xj.x, fmaf(R[7], xj.y, fmaf(R[8], xj.z, t[2])));
+  const bool valid = vm & (q > prm.Q_thresh) & (xi.w > prm.C_thresh) & (xj.w > prm.C_thresh);
+  if (MODE == M3R_GN_RAYS) {  // gn_kernels.cu:924-1089
+    const float n2i = xi.x * xi.x + xi.y * xi.y + xi.z * xi.z;
+    const float ni_inv = rsqrtf(n2i);
+    const float n2j = Px * Px + Py * Py + Pz * Pz;
+    const float nj_inv = rsqrtf(n2j);
+    const float nj = n2j * nj_inv;
+    const float rx = Px * nj_inv, ry = Py * nj_inv, rz = Pz * nj_inv;
+    const float e0 = rx - xi.x * ni_inv, e1 = ry - xi.y * ni_inv, e2 = rz - xi.z * ni_inv;
+    const float e3 = nj - n2i * ni_inv;
+    const float wc_ray = valid ? q * prm.inv_var_a : 0.f;
+    const float wc_dist = valid ? q * prm.inv_var_b : 0.f;
+    const float w0 = robust_weight(wc_ray, e0), w1 = robust_weight(wc_ray, e1);
+    const float w2 = robust_weight(wc_ray, e2), w3 = robust_weight(wc_dist, e3);
+    // d r / d P = (I - r r^T) / |P|
+    const float dxx = nj_inv - rx * rx * nj_inv, dyy = nj_inv - ry * ry * nj_inv;
+    const float dzz = nj_inv - rz * rz * nj_inv;
+    const float dxy = -rx * ry * nj_inv, dxz = -rx * rz * nj_inv, dyz = -ry * rz * nj_inv;
+    { const float J[7] = {dxx, dxy, dxz, 0.f, rz, -ry, 0.f}; acc_row<0x37u>(h, g, w0, e0, J); }
+    { const float J[7] = {dxy, dyy, dyz, -rz, 0.f, rx, 0.f}; acc_row<0x2Fu>(h, g, w1, e1, J); }
+    { const float J[7] = {dxz, dyz, dzz, ry, -rx, 0.f, 0.f}; acc_row<0x1Fu>(h, g, w2, e2, J); }
+    { const float J[7] = {rx, ry, rz, 0.f, 0.f, 0.f, nj}; acc_row<0x47u>(h, g, w3, e3, J); }
+  } else if (MODE == M3R_GN_CALIB) {  // gn_kernels.cu:1360-1495
+    const int u_t = (int)(ind % prm.width), v_t = (int)(ind / prm.width);
+    const bool valid_z = (Pz > prm.z_eps) && (xi.z > prm.z_eps);
+    const float zinv = valid_z ? 1.0f / Pz : 0.f;
+    const float zj_log = valid_z ? logf(Pz) : 0.f;
+    const float zi_log = valid_z ? logf(xi.z) : 0.f;
+    const float xz = Px * zinv, yz = Py * zinv;
+    const float u = fmaf(prm.fx, xz, prm.cx), v = fmaf(prm.fy, yz, prm.cy);
+    const bool valid_u = (u > prm.u_lo) && (u < prm.u_hi);
+    const bool valid_v = (v > prm.v_lo) && (v < prm.v_hi);
+    const float e0 = u - (float)u_t, e1 = v - (float)v_t, e2 = zj_log - zi_log;
+    const bool ok = valid & valid_u & valid_v & valid_z;
+    const float wc_pix = ok ? q * prm.inv_var_a : 0.f;
+    const float wc_dep = ok ? q * prm.inv_var_b : 0.f;
+    const float w0 = robust_weight(wc_pix, e0), w1 = robust_weight(wc_pix, e1);
+    const float w2 = robust_weight(wc_dep, e2);
+    { const float J[7] = {prm.fx * zinv, 0.f, -prm.fx * xz * zinv, -prm.fx * xz * yz,
+                          prm.fx * (1.f + xz * xz), -prm.fx * yz, 0.f};
+      acc_row<0x3Du>(h, g, w0, e0, J); }
+    { const float J[7] = {0.f, prm.fy * zinv, -prm.fy * yz * zinv, -prm.fy * (1.f + yz * yz),
+                          prm.fy * xz * yz, prm.fy * xz, 0.f};
+      acc_row<0x3Eu>(h, g, w1, e1, J); }
+    { const float J[7] = {0.f, 0.f, zinv, yz, -xz, 0.f, 1.f}; acc_row<0x5Cu>(h, g, w2, e2, J); }
+  } else {  // points, gn_kernels.cu:567-674
+    const float e0 = Px - xi.x, e1 = Py - xi.y, e2 = Pz - xi.z;
+    const float wc = valid ? q * prm.inv_var_a : 0.f;
+    const float w0 = robust_weight(wc, e0), w1 = robust_weight(wc, e1), w2 = robust_weight(wc, e2);
+    { const float J[7] = {1.f, 0.f, 0.f, 0.f, Pz, -Py, Px}; acc_row<0x71u>(h, g, w0, e0, J); }
+    { const float J[7] = {0.f, 1.f, 0.f, -Pz, 0.f, Px, Py}; acc_row<0x6Au>(h, g, w1, e1, J); }
+    { const float J[7] = {0.f, 0.f, 1.f, Py, -Px, 0.f, Pz}; acc_row<0x5Cu>(h, g, w2, e2, J); }
+  }
+}
+
+constexpr int kAccThreads = 256;
+constexpr int kAccUnroll = 4;
+
+template <int MODE>
+__global__ void __launch_bounds__(kAccThreads, 2)
+gn_accum_kernel(const GnDev prm, const float* __restrict__ Twc, const float4* __restrict__ xc,
+                const int* __restrict__ ie, const int* __restrict__ je,
+                const int64_t* __restrict__ idx, const uint8_t* __restrict__ vmatch,
+                const float* __restrict__ Q, int n, int edge_begin, int chunk, int S,
+                float* __restrict__ part, const GnHeader* __restrict__ hdr) {
+  if (hdr->done) return;
+  const int el = blockIdx.y, split = blockIdx.x;
+  const int e = edge_begin + el;
+  const int ix = ie[e], jx = je[e];
+  // T_ij = T_i^-1 T_j in fp32 like the reference (relSim3), then as a 3x4 affine map.
+  float R[9], t[3];
+  {
+    float Ti[8], Tj[8], qij[4], sij;
+#pragma unroll
+    for (int k = 0; k < 8; k++) { Ti[k] = __ldg(Twc + ix * 8 + k); Tj[k] = __ldg(Twc + jx * 8 + k); }
+    rel_sim3<float>(Ti, Ti + 3, Ti[7], Tj, Tj + 3, Tj[7], t, qij, sij);
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      float ev[3] = {0.f, 0.f, 0.f}, col[3];
+      ev[c] = 1.f;
+      act_so3<float>(qij, ev, col);
+      R[0 + c] = sij * col[0]; R[3 + c] = sij * col[1]; R[6 + c] = sij * col[2];
+    }
+  }
+  float h[28], g[7];
+#pragma unroll
+  for (int k = 0; k < 28; k++) h[k] = 0.f;
+#pragma unroll
+  for (int k = 0; k < 7; k++) g[k] = 0.f;
+
+  const float4* xi_base = xc + (size_t)ix * n;
+  const float4* xj_base = xc + (size_t)jx * n;
+  const int64_t* idx_e = idx + (size_t)el * n;
+  const uint8_t* vm_e = vmatch + (size_t)el * n;
+  const float* q_e = Q + (size_t)el * n;
+  const int p_begin = split * chunk;
+  const int p_end = min(n, p_begin + chunk);
+  for (int base = p_begin + threadIdx.x; base < p_end; base += kAccThreads * kAccUnroll) {
+    long long ind[kAccUnroll];
+    float qv[kAccUnroll];
+    bool vm[kAccUnroll];
+    float4 xj[kAccUnroll], xi[kAccUnroll];
+#pragma unroll
+    for (int u = 0; u < kAccUnroll; u++) {
+      const int k = base + u * kAccThreads;
+      const bool in = k < p_end;
+      const int kk = in ? k : p_begin;
+      vm[u] = in && (vm_e[kk] != 0);
+      ind[u] = vm[u] ? idx_e[kk] : 0;  // invalid matches gather pixel 0 (gn_kernels.cu:913-914)
+      qv[u] = in ? ld_stream_f(q_e + kk) : 0.f;
+      xj[u] = ld_stream_f4(xj_base + kk);
+      if (!in) qv[u] = -3.0e38f;  // fails q > Q_thresh for any finite threshold
+    }
+#pragma unroll
+    for (int u = 0; u < kAccUnroll; u++) xi[u] = __ldg(xi_base + ind[u]);
+#pragma unroll
+    for (int u = 0; u < kAccUnroll; u++)
+      point_terms<MODE>(prm, R, t, xi[u], xj[u], ind[u], qv[u], vm[u], h, g);
+  }
+
+  // two-stage fixed-order reduction: warp shuffle tree, then 8 warps summed in order
+  __shared__ float red[kAccThreads / 32][kGnPartStride];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 28; k++) { const float v = warp_sum(h[k]); if (lane == 0) red[warp][k] = v; }
+#pragma unroll
+  for (int k = 0; k < 7; k++) { const float v = warp_sum(g[k]); if (lane == 0) red[warp][28 + k] = v; }
+  __syncthreads();
+  if (threadIdx.x < 35) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < kAccThreads / 32; w++) s += red[w][threadIdx.x];
+    part[((size_t)el * S + split) * kGnPartStride + threadIdx.x] = s;
+  }
+}
+
+// Per edge: sum the S partials (fp64, fixed order), apply the adjoint of T_i once:
+//   Jj = J_local * A with A[k][:] = apply_Sim3_adj_inv(T_i, e_k)   (gn_kernels.cu:277-297)
+//   S = A^T H_local A,  v = A^T g_local.
+__global__ void __launch_bounds__(64)
+gn_edge_finish_kernel(const float* __restrict__ Twc, const int* __restrict__ ie,
+                      const float* __restrict__ part, int edge_begin, int S,
+                      double* __restrict__ blocks, const GnHeader* __restrict__ hdr) {
+  if (hdr->done) return;
+  __shared__ double Hl[7][7], gl[7], A[7][7], HA[7][7];
+  const int el = blockIdx.x, e = edge_begin + el, t = threadIdx.x;
+  if (t < 35) {
+    double s = 0.0;
+    for (int sp = 0; sp < S; sp++) s += (double)part[((size_t)el * S + sp) * kGnPartStride + t];
+    if (t < 28) {
+      int a = 0;
+      while ((a + 1) * (a + 2) / 2 <= t) a++;
+      const int c = t - a * (a + 1) / 2;
+      Hl[a][c] = s; Hl[c][a] = s;
+    } else {
+      gl[t - 28] = s;
+    }
+  } else if (t >= 40 && t < 47) {
+    const int k = t - 40;
+    const int ix = ie[e];
+    double Ti[8], X[7], Y[7];
+    for (int m = 0; m < 8; m++) Ti[m] = (double)Twc[ix * 8 + m];
+    for (int m = 0; m < 7; m++) X[m] = (m == k) ? 1.0 : 0.0;
+    adj_inv_row<double>(Ti, Ti + 3, Ti[7], X, Y);
+    for (int m = 0; m < 7; m++) A[k][m] = Y[m];
+  }
+  __syncthreads();
+  if (t < 49) {
+    const int a = t / 7, b = t % 7;
+    double s = 0.0;
+    for (int l = 0; l < 7; l++) s += Hl[a][l] * A[l][b];
+    HA[a][b] = s;
+  }
+  __syncthreads();
+  if (t < 49) {
+    const int a = t / 7, b = t % 7;
+    double s = 0.0;
+    for (int k = 0; k < 7; k++) s += A[k][a] * HA[k][b];
+    blocks[(size_t)e * kGnBlock + t] = s;
+  } else if (t < 56) {
+    const int m = t - 49;
+    double s = 0.0;
+    for (int k = 0; k < 7; k++) s += gl[k] * A[k][m];
+    blocks[(size_t)e * kGnBlock + t] = s;
+  }
+}
+
+static GnDev make_dev_params(const m3r_gn_params* p) {
+  GnDev d;
+  d.inv_var_a = (float)(1.0 / ((double)p->sigma_a * (double)p->sigma_a));
+  d.inv_var_b = p->sigma_b != 0.f ? (float)(1.0 / ((double)p->sigma_b * (double)p->sigma_b)) : 0.f;
+  d.C_thresh = p->C_thresh; d.Q_thresh = p->Q_thresh;
+  d.fx = p->fx; d.fy = p->fy; d.cx = p->cx; d.cy = p->cy;
+  d.u_lo = (float)p->pixel_border; d.u_hi = (float)(p->width - 1 - p->pixel_border);
+  d.v_lo = (float)p->pixel_border; d.v_hi = (float)(p->height - 1 - p->pixel_border);
+  d.z_eps = p->z_eps;
+  d.width = p->width > 0 ? p->width : 1;
+  return d;
+}
+
+}  // namespace m3r
+
+using namespace m3r;
+
+extern "C" size_t m3r_gn_workspace_bytes(int num_poses, int num_edges, int local_edges, int n) {
+  if (num_poses < 1 || num_edges < 0 || local_edges < 0 || n < 0) return 0;
+  return gn_layout(num_poses, num_edges, local_edges, n).total;
+}
+
+extern "C" int* m3r_gn_done_flag(void* workspace) {
+  return workspace ? &reinterpret_cast<GnHeader*>(workspace)->done : nullptr;
+}
+
+extern "C" double* m3r_gn_blocks(void* workspace, int num_poses, int num_edges, int local_edges,
+                                 int n) {
+  if (!workspace) return nullptr;
+  return ws_ptr<double>(workspace, gn_layout(num_poses, num_edges, local_edges, n).blocks);
+}
+
+extern "C" int m3r_gn_prepare(const float* Xs, const float* Cs, const int64_t* ii,
+                              const int64_t* jj, int num_poses, int n, int num_edges,
+                              int local_edges, void* workspace, size_t workspace_bytes,
+                              m3r_stream_t stream) {
+  if (num_poses < 1 || n <= 0 || num_edges <= 0 || local_edges < 0 || local_edges > num_edges)
+    return M3R_EINVAL;
+  if (!Xs || !Cs || !ii || !jj || !workspace) return M3R_EINVAL;
+  const GnLayout L = gn_layout(num_poses, num_edges, local_edges, n);
+  if (workspace_bytes < L.total) return M3R_EWORKSPACE;
+  cudaStream_t st = as_stream(stream);
+  gn_index_kernel<<<1, kIdxThreads, 0, st>>>(
+      ii, jj, num_edges, num_poses, L.P, ws_ptr<int64_t>(workspace, L.keys),
+      ws_ptr<int>(workspace, L.rank), ws_ptr<int>(workspace, L.ie), ws_ptr<int>(workspace, L.je),
+      ws_ptr<int>(workspace, L.row_ptr), ws_ptr<int>(workspace, L.adj),
+      ws_ptr<GnHeader>(workspace, L.hdr));
+  M3R_TRY(after_launch());
+  const size_t count = (size_t)num_poses * n;
+  const int grid = (int)((count + 255) / 256 < (size_t)(kNumSMs * 16) ? (count + 255) / 256
+                                                                       : (size_t)(kNumSMs * 16));
+  gn_pack_kernel<<<grid, 256, 0, st>>>(Xs, Cs, count, ws_ptr<float4>(workspace, L.xc));
+  return after_launch();
+}
+
+extern "C" int m3r_gn_accumulate(const m3r_gn_params* prm, const float* Twc,
+                                 const int64_t* idx_ii2jj, const uint8_t* valid_match,
+                                 const float* Q, int num_poses, int n, int num_edges,
+                                 int edge_begin, int edge_count, double* blocks, void* workspace,
+                                 size_t workspace_bytes, m3r_stream_t stream) {
+  if (!prm || num_poses < 1 || n <= 0 || num_edges <= 0 || edge_begin < 0 || edge_count < 0 ||
+      edge_begin + edge_count > num_edges || edge_count > 65535)
+    return M3R_EINVAL;
+  if (edge_count == 0) return M3R_OK;
+  if (!Twc || !idx_ii2jj || !valid_match || !Q || !blocks || !workspace) return M3R_EINVAL;
+  if (prm->sigma_a == 0.f) return M3R_EINVAL;
+  // the partial buffer is sized for `local_edges`; accept any slice up to that size
+  const GnLayout L = gn_layout(num_poses, num_edges, edge_count, n);  // offsets independent of edge_count
+  if (workspace_bytes < L.part + sizeof(float) * (size_t)edge_count * L.S * kGnPartStride)
+    return M3R_EWORKSPACE;
+  cudaStream_t st = as_stream(stream);
+  const GnDev d = make_dev_params(prm);
+  const GnHeader* hdr = ws_ptr<GnHeader>(workspace, L.hdr);
+  dim3 grid(L.S, edge_count);
+#define M3R_ACC(MODE)                                                                          \
+  gn_accum_kernel<MODE><<<grid, kAccThreads, 0, st>>>(                                         \
+      d, Twc, ws_ptr<float4>(workspace, L.xc), ws_ptr<int>(workspace, L.ie),                   \
+      ws_ptr<int>(workspace, L.je), idx_ii2jj, valid_match, Q, n, edge_begin, L.chunk, L.S,    \
+      ws_ptr<float>(workspace, L.part), hdr)
+  switch (prm->mode) {
+    case M3R_GN_RAYS: M3R_ACC(M3R_GN_RAYS); break;
+    case M3R_GN_CALIB: M3R_ACC(M3R_GN_CALIB); break;
+    case M3R_GN_POINTS: M3R_ACC(M3R_GN_POINTS); break;
+    default: return M3R_EINVAL;
+  }
+#undef M3R_ACC
+  M3R_TRY(after_launch());
+  gn_edge_finish_kernel<<<edge_count, 64, 0, st>>>(Twc, ws_ptr<int>(workspace, L.ie),
+                                                   ws_ptr<float>(workspace, L.part), edge_begin,
+                                                   L.S, blocks, hdr);
+  return after_launch();
+}
+
+extern "C" int m3r_gn_solve_step(float* Twc, const double* blocks, int num_poses, int num_edges,
+                                 float delta_thresh, float* dx, void* workspace,
+                                 size_t workspace_bytes, m3r_stream_t stream) {
+  if (num_poses < 2 || num_edges <= 0 || !Twc || !blocks || !dx || !workspace) return M3R_EINVAL;
+  const GnLayout L = gn_layout(num_poses, num_edges, 0, 0);  // offsets up to `x` need (N, M) only
+  if (workspace_bytes < L.xc) return M3R_EWORKSPACE;
+  return gn_solve_launch(Twc, blocks, num_poses, num_edges, delta_thresh, dx, workspace, L,
+                         as_stream(stream));
+}
+
+extern "C" int m3r_gauss_newton(const m3r_gn_params* prm, float* Twc, const float* Xs,
+                                const float* Cs, const int64_t* ii, const int64_t* jj,
+                                const int64_t* idx_ii2jj, const uint8_t* valid_match,
+                                const float* Q, int num_poses, int n, int num_edges, int max_iter,
+                                float delta_thresh, float* dx, void* workspace,
+                                size_t workspace_bytes, m3r_stream_t stream) {
+  if (!prm || num_poses < 2 || n <= 0 || num_edges <= 0 || max_iter < 0 || !dx) return M3R_EINVAL;
+  if (workspace_bytes < m3r_gn_workspace_bytes(num_poses, num_edges, num_edges, n))
+    return M3R_EWORKSPACE;
+  M3R_TRY(check_cuda(cudaMemsetAsync(dx, 0, sizeof(float) * 7 * (size_t)(num_poses - 1),
+                                     as_stream(stream))));
+  if (max_iter == 0) return M3R_OK;
+  M3R_TRY(m3r_gn_prepare(Xs, Cs, ii, jj, num_poses, n, num_edges, num_edges, workspace,
+                         workspace_bytes, stream));
+  double* blocks = m3r_gn_blocks(workspace, num_poses, num_edges, num_edges, n);
+  for (int it = 0; it < max_iter; it++) {
+    // edge slices of <= 65535 (grid.y limit)
+    for (int e0 = 0; e0 < num_edges; e0 += 32768) {
+      const int cnt = num_edges - e0 < 32768 ? num_edges - e0 : 32768;
+      M3R_TRY(m3r_gn_accumulate(prm, Twc, idx_ii2jj + (size_t)e0 * n, valid_match + (size_t)e0 * n,
+                                Q + (size_t)e0 * n, num_poses, n, num_edges, e0, cnt, blocks,
+                                workspace, workspace_bytes, stream));
+    }
+    M3R_TRY(m3r_gn_solve_step(Twc, blocks, num_poses, num_edges, delta_thresh, dx, workspace,
+                              workspace_bytes, stream));
+  }
+  return M3R_OK;
+}

@@ -1,0 +1,97 @@
+// m3r_prep.cu — fused prologue of match_iterative_proj (sm_100a).
+//
+// Replaces the PyTorch glue of matching.prep_for_iter_proj (reference matching.py:25-50) and
+// image.img_gradient (image.py:5-38): F.normalize -> permute -> 2x (reflect pad + depthwise
+// 3x3 conv) -> cat -> permute -> contiguous (six kernels, each a round trip through HBM) become
+// one pass: X11 (b,H,W,3) -> rays_img_with_grad (b,H,W,9).  The fp32 -> fp16 cast of the
+// descriptor image (matching.py:80) is the second kernel here.
+#include "m3r_common.cuh"
+
+namespace m3r {
+
+constexpr int kPrepTX = 32, kPrepTY = 8;
+
+__device__ __forceinline__ int reflect(int i, int n) {  // F.pad(mode="reflect"), pad = 1
+  if (i < 0) return -i;
+  if (i >= n) return 2 * n - 2 - i;
+  return i;
+}
+
+__global__ void __launch_bounds__(kPrepTX * kPrepTY)
+prep_rays_kernel(const float* __restrict__ X11, int H, int W, float* __restrict__ out) {
+  __shared__ float tile[kPrepTY + 2][kPrepTX + 2][3];
+  const int x0 = blockIdx.x * kPrepTX, y0 = blockIdx.y * kPrepTY;
+  const float* Xb = X11 + (size_t)blockIdx.z * H * W * 3;
+  const int tid = threadIdx.y * kPrepTX + threadIdx.x;
+  for (int idx = tid; idx < (kPrepTY + 2) * (kPrepTX + 2); idx += kPrepTX * kPrepTY) {
+    const int ty = idx / (kPrepTX + 2), tx = idx % (kPrepTX + 2);
+    const int y = reflect(min(y0 + ty - 1, H), H), x = reflect(min(x0 + tx - 1, W), W);
+    const float* p = Xb + ((size_t)min(y, H - 1) * W + min(x, W - 1)) * 3;
+    const float a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+    // F.normalize(dim=-1, eps=1e-12): v / max(|v|_2, eps)
+    const float nrm = fmaxf(sqrtf(a * a + b * b + c * c), 1e-12f);
+    tile[ty][tx][0] = a / nrm; tile[ty][tx][1] = b / nrm; tile[ty][tx][2] = c / nrm;
+  }
+  __syncthreads();
+  const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
+  if (x >= W || y >= H) return;
+  const int tx = threadIdx.x + 1, ty = threadIdx.y + 1;
+  float* o = out + (((size_t)blockIdx.z * H + y) * W + x) * 9;
+  const float k3 = 3.0f / 32.0f, k10 = 10.0f / 32.0f;  // (1/32)*[-3,0,3;-10,0,10;-3,0,3]
+#pragma unroll
+  for (int c = 0; c < 3; c++) {
+    const float tl = tile[ty - 1][tx - 1][c], tc = tile[ty - 1][tx][c], tr = tile[ty - 1][tx + 1][c];
+    const float ml = tile[ty][tx - 1][c], mr = tile[ty][tx + 1][c];
+    const float bl = tile[ty + 1][tx - 1][c], bc = tile[ty + 1][tx][c], br = tile[ty + 1][tx + 1][c];
+    o[c] = tile[ty][tx][c];
+    o[3 + c] = -k3 * tl + k3 * tr - k10 * ml + k10 * mr - k3 * bl + k3 * br;   // gx
+    o[6 + c] = -k3 * tl - k10 * tc - k3 * tr + k3 * bl + k10 * bc + k3 * br;   // gy
+  }
+}
+
+// fp32 -> fp16 (round to nearest even == Tensor.half()), 8 elements per thread.
+__global__ void __launch_bounds__(256)
+cast_f16_kernel(const float* __restrict__ src, size_t count8, size_t count, uint16_t* __restrict__ dst) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < count8; i += stride) {
+    const float4 a = ld_stream_f4(src + i * 8), b = ld_stream_f4(src + i * 8 + 4);
+    __half2 h0 = __floats2half2_rn(a.x, a.y), h1 = __floats2half2_rn(a.z, a.w);
+    __half2 h2 = __floats2half2_rn(b.x, b.y), h3 = __floats2half2_rn(b.z, b.w);
+    uint4 o;
+    o.x = *reinterpret_cast<uint32_t*>(&h0); o.y = *reinterpret_cast<uint32_t*>(&h1);
+    o.z = *reinterpret_cast<uint32_t*>(&h2); o.w = *reinterpret_cast<uint32_t*>(&h3);
+    reinterpret_cast<uint4*>(dst)[i] = o;
+  }
+  if (blockIdx.x == 0) {
+    for (size_t i = count8 * 8 + threadIdx.x; i < count; i += blockDim.x)
+      dst[i] = __half_as_ushort(__float2half_rn(src[i]));
+  }
+}
+
+}  // namespace m3r
+
+using namespace m3r;
+
+extern "C" int m3r_match_prep(const float* X11, const float* D11, int b, int H, int W, int F,
+                              float* rays_img_with_grad, uint16_t* D11h, m3r_stream_t stream) {
+  if (b < 0 || H < 2 || W < 2 || b > 65535) return M3R_EINVAL;
+  if (b == 0) return M3R_OK;
+  cudaStream_t st = as_stream(stream);
+  if (rays_img_with_grad) {
+    if (!X11) return M3R_EINVAL;
+    dim3 grid((W + kPrepTX - 1) / kPrepTX, (H + kPrepTY - 1) / kPrepTY, b);
+    prep_rays_kernel<<<grid, dim3(kPrepTX, kPrepTY), 0, st>>>(X11, H, W, rays_img_with_grad);
+    M3R_TRY(after_launch());
+  }
+  if (D11h) {
+    if (!D11 || F <= 0) return M3R_EINVAL;
+    const size_t count = (size_t)b * H * W * F;
+    const size_t count8 = count / 8;
+    size_t blocks = (count8 + 255) / 256;
+    if (blocks > (size_t)kNumSMs * 16) blocks = (size_t)kNumSMs * 16;
+    if (blocks < 1) blocks = 1;
+    cast_f16_kernel<<<(int)blocks, 256, 0, st>>>(D11, count8, count, D11h);
+    M3R_TRY(after_launch());
+  }
+  return M3R_OK;
+}

@@ -1,0 +1,386 @@
+"""mast3r_slam_backends — B200 (sm_100a) drop-in for MASt3R-SLAM's native extension.
+
+Same import name, callables, positional signatures and return arity as the reference pybind
+module (reference mast3r_slam/backend/src/gn.cpp:116-122, include/gn.h):
+
+    iter_proj, refine_matches, gauss_newton_rays, gauss_newton_calib, gauss_newton_points
+
+so `matching.match_iterative_proj` (matching.py:60,79) and `FactorGraph.solve_GN_rays/calib`
+(global_opt.py:140,190) call it unchanged.  Everything is executed by hand-written CUDA
+kernels in libm3r_b200.so, bound through its C ABI (include/m3r_b200.h) with ctypes; torch is
+used only to allocate outputs/workspace and to supply the current CUDA stream.  There is no
+CPU path: tensors must be CUDA tensors and a missing library is an ImportError.
+
+Additive entry points (not in the reference): pose_retr, match_prep, match_iter_proj_fused,
+match_refine_fused, track_ray_dist, gn_prepare / gn_accumulate / gn_solve_step /
+gauss_newton_sharded (edge-sharded multi-GPU solve), gn_blocks_reference_layout (tests).
+"""
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "..", "lib", "libm3r_b200.so")
+
+
+class _GNParams(C.Structure):
+    _fields_ = [("mode", C.c_int), ("sigma_a", C.c_float), ("sigma_b", C.c_float),
+                ("C_thresh", C.c_float), ("Q_thresh", C.c_float),
+                ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
+                ("height", C.c_int), ("width", C.c_int), ("pixel_border", C.c_int),
+                ("z_eps", C.c_float)]
+
+
+GN_RAYS, GN_CALIB, GN_POINTS = 0, 1, 2
+
+EXPORTS = [
+    "m3r_version", "m3r_error_string", "m3r_last_cuda_error", "m3r_launch_count",
+    "m3r_iter_proj", "m3r_refine_matches_f16", "m3r_refine_matches_f32", "m3r_match_prep",
+    "m3r_match_iter_proj_fused", "m3r_match_refine_fused", "m3r_pose_retr",
+    "m3r_gn_workspace_bytes", "m3r_gauss_newton", "m3r_gn_prepare", "m3r_gn_accumulate",
+    "m3r_gn_solve_step", "m3r_gn_done_flag", "m3r_gn_blocks", "m3r_track_workspace_bytes",
+    "m3r_track_ray_dist",
+]
+
+
+def _load():
+    path = os.path.abspath(_LIB_PATH)
+    if not os.path.exists(path):
+        raise ImportError(
+            f"mast3r_slam_backends: {path} not found. Build it with "
+            "`python mast3r-slam_b200/build.py` (nvcc, sm_100a). There is no CPU fallback.")
+    lib = C.CDLL(path)
+    vp, i32, f32, sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+    lib.m3r_error_string.restype = C.c_char_p
+    lib.m3r_error_string.argtypes = [i32]
+    lib.m3r_launch_count.restype = C.c_ulonglong
+    lib.m3r_iter_proj.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, f32, f32, vp, vp, vp]
+    lib.m3r_refine_matches_f16.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp]
+    lib.m3r_refine_matches_f32.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp]
+    lib.m3r_match_prep.argtypes = [vp, vp, i32, i32, i32, i32, vp, vp, vp]
+    lib.m3r_match_iter_proj_fused.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, f32, f32, f32,
+                                              vp, vp, vp, vp]
+    lib.m3r_match_refine_fused.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp]
+    lib.m3r_pose_retr.argtypes = [vp, vp, i32, i32, vp]
+    lib.m3r_gn_workspace_bytes.restype = sz
+    lib.m3r_gn_workspace_bytes.argtypes = [i32, i32, i32, i32]
+    gp = C.POINTER(_GNParams)
+    lib.m3r_gauss_newton.argtypes = [gp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32,
+                                     vp, vp, sz, vp]
+    lib.m3r_gn_prepare.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, vp, sz, vp]
+    lib.m3r_gn_accumulate.argtypes = [gp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, sz, vp]
+    lib.m3r_gn_solve_step.argtypes = [vp, vp, i32, i32, f32, vp, vp, sz, vp]
+    lib.m3r_gn_done_flag.restype = vp
+    lib.m3r_gn_done_flag.argtypes = [vp]
+    lib.m3r_gn_blocks.restype = vp
+    lib.m3r_gn_blocks.argtypes = [vp, i32, i32, i32, i32]
+    lib.m3r_track_workspace_bytes.restype = sz
+    lib.m3r_track_workspace_bytes.argtypes = [i32]
+    lib.m3r_track_ray_dist.argtypes = [vp, vp, vp, vp, i32, f32, f32, f32, i32, f32, f32, vp, vp,
+                                       vp, vp, sz, vp]
+    return lib
+
+
+_lib = _load()
+LIBRARY_PATH = os.path.abspath(_LIB_PATH)
+
+
+def launch_count():
+    """Kernels launched by libm3r_b200.so in this process (bench `gpu_launches`)."""
+    return int(_lib.m3r_launch_count())
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise RuntimeError(f"{what}: {_lib.m3r_error_string(rc).decode()} "
+                           f"(code {rc}, cudaError {_lib.m3r_last_cuda_error()})")
+
+
+def _stream(t):
+    return C.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+
+
+def _req(t, name, dtype=None, ndim=None):
+    """Reference checks contiguity only (gn.h:5); we also insist on CUDA + dtype + rank."""
+    if not isinstance(t, torch.Tensor):
+        raise RuntimeError(f"{name} must be a torch.Tensor")
+    if not t.is_contiguous():
+        raise RuntimeError(f"{name} must be contiguous")
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (mast3r_slam_backends has no CPU path)")
+    if dtype is not None and t.dtype != dtype:
+        raise RuntimeError(f"{name} must have dtype {dtype}, got {t.dtype}")
+    if ndim is not None and t.dim() != ndim:
+        raise RuntimeError(f"{name} must have {ndim} dimensions, got {t.dim()}")
+    return t
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+# --------------------------------------------------------------------------- matching
+
+def iter_proj(rays_img_with_grad, pts_3d_norm, p_init, max_iter, lambda_init, cost_thresh):
+    """-> [p_new (b,n,2) f32, converged (b,n) bool]   (gn.h:89-95)"""
+    img = _req(rays_img_with_grad, "rays_img_with_grad", torch.float32, 4)
+    pts = _req(pts_3d_norm, "pts_3d_norm", torch.float32, 3)
+    p0 = _req(p_init, "p_init", torch.float32, 3)
+    b, H, W, c = img.shape
+    if c != 9:
+        raise RuntimeError("rays_img_with_grad must have 9 channels")
+    n = p0.shape[1]
+    with torch.cuda.device(img.device):
+        p_new = torch.empty((b, n, 2), dtype=torch.float32, device=img.device)
+        conv = torch.empty((b, n), dtype=torch.bool, device=img.device)
+        _check(_lib.m3r_iter_proj(_ptr(img), _ptr(pts), _ptr(p0), b, H, W, n, int(max_iter),
+                                  float(lambda_init), float(cost_thresh), _ptr(p_new), _ptr(conv),
+                                  _stream(img)), "iter_proj")
+    return [p_new, conv]
+
+
+def refine_matches(D11, D21, p1, radius, dilation_max):
+    """-> [p1_new (b,n,2) i64]   (gn.h:112-117); D11/D21 float16 or float32."""
+    D11 = _req(D11, "D11", None, 4)
+    D21 = _req(D21, "D21", D11.dtype, 3)
+    p1 = _req(p1, "p1", torch.int64, 3)
+    b, H, W, F = D11.shape
+    n = p1.shape[1]
+    with torch.cuda.device(D11.device):
+        out = torch.empty_like(p1)
+        if D11.dtype == torch.float16:
+            fn = _lib.m3r_refine_matches_f16
+        elif D11.dtype == torch.float32:
+            fn = _lib.m3r_refine_matches_f32
+        else:
+            raise RuntimeError("refine_matches: D11 must be float16 or float32")
+        _check(fn(_ptr(D11), _ptr(D21), _ptr(p1), b, H, W, n, F, int(radius), int(dilation_max),
+                  _ptr(out), _stream(D11)), "refine_matches")
+    return [out]
+
+
+def match_prep(X11, D11=None):
+    """Fused prep_for_iter_proj (matching.py:25-50) + D11.half() (matching.py:80).
+    -> (rays_img_with_grad (b,H,W,9) f32, D11h (b,H,W,F) f16 or None)"""
+    X11 = _req(X11, "X11", torch.float32, 4)
+    b, H, W, _ = X11.shape
+    with torch.cuda.device(X11.device):
+        rays = torch.empty((b, H, W, 9), dtype=torch.float32, device=X11.device)
+        D11h, F = None, 0
+        if D11 is not None:
+            D11 = _req(D11, "D11", torch.float32, 4)
+            F = D11.shape[-1]
+            D11h = torch.empty(D11.shape, dtype=torch.float16, device=X11.device)
+        _check(_lib.m3r_match_prep(_ptr(X11), _ptr(D11), b, H, W, F, _ptr(rays), _ptr(D11h),
+                                   _stream(X11)), "match_prep")
+    return rays, D11h
+
+
+def match_iter_proj_fused(rays_img_with_grad, X11, X21, idx_init, max_iter, lambda_init,
+                          cost_thresh, dist_thresh, want_p_new=False):
+    """-> (p1 (b,n,2) i64, valid (b,n) bool[, p_new (b,n,2) f32])"""
+    img = _req(rays_img_with_grad, "rays_img_with_grad", torch.float32, 4)
+    X11 = _req(X11, "X11", torch.float32, 4)
+    X21 = _req(X21, "X21", torch.float32, 4)
+    b, H, W, _ = img.shape
+    n = H * W
+    if idx_init is not None:
+        idx_init = _req(idx_init, "idx_1_to_2_init", torch.int64, 2)
+    with torch.cuda.device(img.device):
+        p1 = torch.empty((b, n, 2), dtype=torch.int64, device=img.device)
+        valid = torch.empty((b, n), dtype=torch.bool, device=img.device)
+        p_new = torch.empty((b, n, 2), dtype=torch.float32, device=img.device) if want_p_new else None
+        _check(_lib.m3r_match_iter_proj_fused(
+            _ptr(img), _ptr(X11), _ptr(X21), _ptr(idx_init), b, H, W, int(max_iter),
+            float(lambda_init), float(cost_thresh), float(dist_thresh), _ptr(p1), _ptr(valid),
+            _ptr(p_new), _stream(img)), "match_iter_proj_fused")
+    return (p1, valid, p_new) if want_p_new else (p1, valid)
+
+
+def match_refine_fused(D11h, D21, p1, radius, dilation_max):
+    """-> idx_1_to_2 (b,n) i64"""
+    D11h = _req(D11h, "D11h", torch.float16, 4)
+    D21 = _req(D21, "D21", torch.float32)
+    p1 = _req(p1, "p1", torch.int64, 3)
+    b, H, W, F = D11h.shape
+    with torch.cuda.device(D11h.device):
+        idx = torch.empty((b, H * W), dtype=torch.int64, device=D11h.device)
+        _check(_lib.m3r_match_refine_fused(_ptr(D11h), _ptr(D21), _ptr(p1), b, H, W, F,
+                                           int(radius), int(dilation_max), _ptr(idx),
+                                           _stream(D11h)), "match_refine_fused")
+    return idx
+
+
+# --------------------------------------------------------------------------- Sim3 / GN
+
+def pose_retr(poses, dx, num_fix=1):
+    """In place: T_k <- Exp(dx_{k-num_fix}) * T_k   (pose_retr_kernel, gn_kernels.cu:415-453)"""
+    poses = _req(poses, "poses", torch.float32, 2)
+    dx = _req(dx, "dx", torch.float32, 2)
+    _check(_lib.m3r_pose_retr(_ptr(poses), _ptr(dx), poses.shape[0], int(num_fix), _stream(poses)),
+           "pose_retr")
+    return poses
+
+
+def _params(mode, sigma_a, sigma_b, C_thresh, Q_thresh, K=None, height=0, width=0,
+            pixel_border=0, z_eps=0.0):
+    p = _GNParams()
+    p.mode = mode
+    p.sigma_a, p.sigma_b = float(sigma_a), float(sigma_b)
+    p.C_thresh, p.Q_thresh = float(C_thresh), float(Q_thresh)
+    if K is not None:
+        Kc = K.detach().to("cpu", torch.float32)  # 4 scalars; the reference reads them on device
+        p.fx, p.fy, p.cx, p.cy = float(Kc[0, 0]), float(Kc[1, 1]), float(Kc[0, 2]), float(Kc[1, 2])
+    p.height, p.width, p.pixel_border, p.z_eps = int(height), int(width), int(pixel_border), float(z_eps)
+    return p
+
+
+def _gn_inputs(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q):
+    Twc = _req(Twc, "Twc", torch.float32, 2)
+    Xs = _req(Xs, "Xs", torch.float32, 3)
+    Cs = _req(Cs, "Cs", torch.float32)
+    ii = _req(ii, "ii", torch.int64, 1)
+    jj = _req(jj, "jj", torch.int64, 1)
+    idx = _req(idx_ii2jj, "idx_ii2jj", torch.int64, 2)
+    vm = _req(valid_match, "valid_match", torch.bool)
+    Q = _req(Q, "Q", torch.float32)
+    N, n = Xs.shape[0], Xs.shape[1]
+    if Twc.shape[0] != N or Twc.shape[1] != 8:
+        raise RuntimeError("Twc must be (num_poses, 8)")
+    return Twc, Xs, Cs, ii, jj, idx, vm, Q, N, n
+
+
+def _gauss_newton(prm, Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, max_iter, delta_thresh):
+    Twc, Xs, Cs, ii, jj, idx, vm, Q, N, n = _gn_inputs(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q)
+    M = ii.shape[0]
+    with torch.cuda.device(Twc.device):
+        dx = torch.empty((N - 1, 7), dtype=torch.float32, device=Twc.device)
+        nbytes = _lib.m3r_gn_workspace_bytes(N, M, M, n)
+        ws = torch.empty((nbytes,), dtype=torch.uint8, device=Twc.device)
+        _check(_lib.m3r_gauss_newton(C.byref(prm), _ptr(Twc), _ptr(Xs), _ptr(Cs), _ptr(ii), _ptr(jj),
+                                     _ptr(idx), _ptr(vm), _ptr(Q), N, n, M, int(max_iter),
+                                     float(delta_thresh), _ptr(dx), _ptr(ws), nbytes, _stream(Twc)),
+               "gauss_newton")
+    return [dx]
+
+
+def gauss_newton_rays(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, sigma_ray, sigma_dist,
+                      C_thresh, Q_thresh, max_iter, delta_thresh):
+    """-> [dx (N-1,7)]; Twc updated in place   (gn.h:45-55)"""
+    prm = _params(GN_RAYS, sigma_ray, sigma_dist, C_thresh, Q_thresh)
+    return _gauss_newton(prm, Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, max_iter, delta_thresh)
+
+
+def gauss_newton_calib(Twc, Xs, Cs, K, ii, jj, idx_ii2jj, valid_match, Q, height, width,
+                       pixel_border, z_eps, sigma_pixel, sigma_depth, C_thresh, Q_thresh, max_iter,
+                       delta_thresh):
+    """-> [dx (N-1,7)]; Twc updated in place   (gn.h:74-87)"""
+    _req(K, "K", torch.float32, 2)
+    prm = _params(GN_CALIB, sigma_pixel, sigma_depth, C_thresh, Q_thresh, K, height, width,
+                  pixel_border, z_eps)
+    return _gauss_newton(prm, Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, max_iter, delta_thresh)
+
+
+def gauss_newton_points(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, sigma_point, C_thresh,
+                        Q_thresh, max_iter, delta_thresh):
+    """-> [dx (N-1,7)]; Twc updated in place   (gn.h:22-31)"""
+    prm = _params(GN_POINTS, sigma_point, 0.0, C_thresh, Q_thresh)
+    return _gauss_newton(prm, Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, max_iter, delta_thresh)
+
+
+class GNSolver:
+    """Stepwise Gauss-Newton over a slice [edge_begin, edge_begin+edge_count) of the directed edge
+    list: prepare once, then per iteration accumulate() -> (exchange blocks) -> solve_step().
+    `ii`/`jj` are the FULL edge lists; idx/valid/Q are the LOCAL slice."""
+
+    def __init__(self, prm, Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_local, edge_begin=0):
+        (self.Twc, self.Xs, self.Cs, self.ii, self.jj, self.idx, self.vm, self.Q, self.N,
+         self.n) = _gn_inputs(Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_local)
+        self.prm = prm
+        self.M = self.ii.shape[0]
+        self.edge_begin = int(edge_begin)
+        self.Ml = self.idx.shape[0]
+        dev = Twc.device
+        with torch.cuda.device(dev):
+            self.nbytes = _lib.m3r_gn_workspace_bytes(self.N, self.M, self.Ml, self.n)
+            self.ws = torch.empty((self.nbytes,), dtype=torch.uint8, device=dev)
+            self.blocks = torch.zeros((self.M, 56), dtype=torch.float64, device=dev)
+            self.dx = torch.zeros((self.N - 1, 7), dtype=torch.float32, device=dev)
+            _check(_lib.m3r_gn_prepare(_ptr(self.Xs), _ptr(self.Cs), _ptr(self.ii), _ptr(self.jj),
+                                       self.N, self.n, self.M, self.Ml, _ptr(self.ws), self.nbytes,
+                                       _stream(Twc)), "gn_prepare")
+
+    def accumulate(self):
+        with torch.cuda.device(self.Twc.device):
+            _check(_lib.m3r_gn_accumulate(C.byref(self.prm), _ptr(self.Twc), _ptr(self.idx),
+                                          _ptr(self.vm), _ptr(self.Q), self.N, self.n, self.M,
+                                          self.edge_begin, self.Ml, _ptr(self.blocks), _ptr(self.ws),
+                                          self.nbytes, _stream(self.Twc)), "gn_accumulate")
+        return self.blocks
+
+    def solve_step(self, delta_thresh):
+        with torch.cuda.device(self.Twc.device):
+            _check(_lib.m3r_gn_solve_step(_ptr(self.Twc), _ptr(self.blocks), self.N, self.M,
+                                          float(delta_thresh), _ptr(self.dx), _ptr(self.ws),
+                                          self.nbytes, _stream(self.Twc)), "gn_solve_step")
+        return self.dx
+
+    def local_blocks(self):
+        return self.blocks[self.edge_begin:self.edge_begin + self.Ml]
+
+
+def gn_blocks_reference_layout(blocks):
+    """(M,56) f64 per-edge blocks -> Hs (4,M,7,7), gs (2,M,7) in the reference's layout
+    (gn_kernels.cu:1096-1137): Hs[0]=Hs[3]=S, Hs[1]=Hs[2]=-S, gs[0]=-v, gs[1]=v."""
+    S = blocks[:, :49].reshape(-1, 7, 7)
+    v = blocks[:, 49:56]
+    return torch.stack([S, -S, -S, S]), torch.stack([-v, v])
+
+
+def gauss_newton_sharded(prm, Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_local, edge_begin,
+                         max_iter, delta_thresh, group=None, edge_counts=None):
+    """Edge-sharded solve: each rank accumulates its contiguous slice of the directed edges, the
+    56-double per-edge blocks are exchanged with ONE all-gather per iteration (NCCL over NVLink),
+    then every rank runs the identical replicated assembly + Cholesky + retraction, so poses stay
+    bit-identical on all ranks — and identical to the single-GPU solve, because an edge's block
+    does not depend on which rank computed it."""
+    import torch.distributed as dist
+
+    solver = GNSolver(prm, Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_local, edge_begin)
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    for _ in range(int(max_iter)):
+        solver.accumulate()
+        if world > 1:
+            if edge_counts is not None and len(set(edge_counts)) == 1:
+                dist.all_gather_into_tensor(solver.blocks, solver.local_blocks().clone(), group=group)
+            else:
+                outs = list(solver.blocks.split(list(edge_counts)))
+                dist.all_gather(outs, solver.local_blocks().contiguous(), group=group)
+        solver.solve_step(delta_thresh)
+    return [solver.dx]
+
+
+# --------------------------------------------------------------------------- tracker
+
+def track_ray_dist(Xf, Xk, Qk, valid, T_CkCf, sigma_ray, sigma_dist, huber_k, max_iters, rel_error,
+                   delta_norm, want_cost=False):
+    """Whole opt_pose_ray_dist_sim3 loop (tracker.py:173-214) on the relative pose.
+    T_CkCf: (8,) f32 CUDA tensor updated in place.  -> status (4,) i32 CUDA tensor
+    [iterations, converged, cholesky_failed, 0] (and the per-iteration cost if requested)."""
+    Xf = _req(Xf, "Xf", torch.float32, 2)
+    Xk = _req(Xk, "Xk", torch.float32, 2)
+    Qk = _req(Qk, "Qk", torch.float32)
+    valid = _req(valid, "valid", torch.bool)
+    T = _req(T_CkCf, "T_CkCf", torch.float32)
+    n = Xf.shape[0]
+    with torch.cuda.device(Xf.device):
+        status = torch.zeros((4,), dtype=torch.int32, device=Xf.device)
+        cost = torch.zeros((max(int(max_iters), 1),), dtype=torch.float32, device=Xf.device) if want_cost else None
+        nbytes = _lib.m3r_track_workspace_bytes(n)
+        ws = torch.empty((nbytes,), dtype=torch.uint8, device=Xf.device)
+        _check(_lib.m3r_track_ray_dist(_ptr(Xf), _ptr(Xk), _ptr(Qk), _ptr(valid), n, float(sigma_ray),
+                                       float(sigma_dist), float(huber_k), int(max_iters),
+                                       float(rel_error), float(delta_norm), _ptr(T), _ptr(status),
+                                       _ptr(cost), _ptr(ws), nbytes, _stream(Xf)), "track_ray_dist")
+    return (status, cost) if want_cost else status
