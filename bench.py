@@ -1,0 +1,399 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200 hot path (BASELINE.json: "Gpix/s dense matching;
+GN-rays iters/s at 512x384").
+
+One "step" = one `match_iterative_proj` pass (prep + iter_proj max_iter 10 + refine_matches radius 3,
+dilation 5, 24-d descriptors) over a batch of synthetic 512x384 frame pairs (BASELINE configs[1]).
+`value`     : Gpix/s with inputs resident in HBM (CUDA events on the launching stream, max over ranks).
+`e2e`       : the same metric through the reference-facing call `mast3r_slam.matching.match_iterative_proj`
+              with HOST buffers: pinned H2D of X11/X21/D11/D21 and D2H of idx/valid inside the timed region.
+`roofline`  : dominant kernel (refine) — algorithmic 128 B/pixel / measured launch time vs measured HBM peak.
+`cpu_baseline`: the oracle port of the same call on the box's host cores, bounded sample.
+`extra`     : GN-rays iterations/s (BASELINE configs[2]) and the tracker solve, with their own rooflines.
+`--impl reference`: the CPU arm alone (the reference has no CPU code for its CUDA-only kernels, so this
+is the oracle port with all host threads), same metric/config/unit.
+
+Multi-GPU (torchrun, one rank per GPU): frame pairs are independent, so every rank matches its own
+batch with no data-path collective ("scaling": "weak"); `extra.gn_sharded` runs the edge-sharded
+Gauss-Newton (one NCCL all-gather of the per-edge blocks per iteration).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "mast3r-slam_b200"))
+
+H, W, FDIM = 384, 512, 24
+N_PIX = H * W
+MATCH = dict(max_iter=10, lambda_init=1e-8, convergence_thresh=1e-6, dist_thresh=0.1, radius=3,
+             dilation_max=5)
+# algorithmic bytes per unit
+B_ITER_PROJ, B_REFINE, B_MATCH_CALL = 65, 128, 225
+B_GN_POINT, B_TRACK_POINT = 45, 29
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_match_sample(b, threads):
+    """Oracle port of match_iterative_proj on `b` synthetic pairs -> seconds (bounded sample)."""
+    import torch
+    from oracle import matching as om
+    from oracle import oracle as orc
+    from tests import synth
+
+    orc.set_threads(threads)
+    torch.set_num_threads(threads)
+    m = synth.make_match_inputs(b, H, W, FDIM, seed=1235, device="cpu")
+    t0 = time.perf_counter()
+    om.match_iterative_proj(m["X11"], m["X21"], m["D11"], m["D21"])
+    return time.perf_counter() - t0
+
+
+def run_reference(args):
+    """CPU arm: rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    threads = os.cpu_count() or 1
+    b = 1
+    for _ in range(min(args.warmup, 1)):
+        cpu_match_sample(b, threads)
+    steps = max(1, min(args.steps, 3))
+    ts = [cpu_match_sample(b, threads) for _ in range(steps)]
+    t = sum(ts) / len(ts)
+    v = b * N_PIX / t / 1e9
+    sample = f"{b} frame pair(s) of {W}x{H} per step, {steps} step(s), oracle C port + torch-CPU glue"
+    print(json.dumps({
+        "impl": "reference", "metric": "dense matching throughput (match_iterative_proj)",
+        "value": v, "unit": "Gpix/s", "n_gpus": args.gpus, "steps": steps, "warmup": min(args.warmup, 1),
+        "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "match_iterative_proj 512x384, iter_proj max_iter 10 + refine_matches "
+                               "radius 3 dilation 5, 24-d desc (BASELINE configs[1])", "batch_pairs": b},
+        "cpu_baseline": {"value": v, "unit": "Gpix/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "Gpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=8, help="frame pairs per step per GPU")
+    ap.add_argument("--no-extra", action="store_true", help="skip the GN / tracker extras")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback "
+                         "(use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    import mast3r_slam_backends as be
+    from mast3r_slam import matching
+    from tests import synth
+
+    W_ = max(3, args.warmup)
+    K = args.steps
+    b = args.batch
+    peak, peak_kind = measured_peak()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---------------------------------------------------------------- inputs (resident in HBM)
+    m = synth.make_match_inputs(b, H, W, FDIM, seed=1235 + rank, device=dev)
+    X11, X21, D11, D21 = m["X11"], m["X21"], m["D11"], m["D21"]
+    in_bytes = sum(t.numel() * t.element_size() for t in (X11, X21, D11, D21))
+
+    def step_kernels(ev=None):
+        rays, D11h = be.match_prep(X11, D11)
+        if ev: ev[1].record()
+        p1, valid = be.match_iter_proj_fused(rays, X11, X21, None, MATCH["max_iter"], MATCH["lambda_init"],
+                                             MATCH["convergence_thresh"], MATCH["dist_thresh"])
+        if ev: ev[2].record()
+        idx = be.match_refine_fused(D11h, D21, p1, MATCH["radius"], MATCH["dilation_max"])
+        if ev: ev[3].record()
+        return idx, valid
+
+    for _ in range(W_):
+        step_kernels()
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(K)]
+    barrier()
+    sampler = ClockSampler(local).start() if rank == 0 else None
+    l0 = be.launch_count()
+    t_start = torch.cuda.Event(enable_timing=True); t_end = torch.cuda.Event(enable_timing=True)
+    t_start.record()
+    for k in range(K):
+        evs[k][0].record()
+        step_kernels(evs[k])
+    t_end.record()
+    barrier()
+    launches = be.launch_count() - l0
+    clocks = sampler.stop() if sampler else None
+    ms_total = max_over_ranks(t_start.elapsed_time(t_end))
+    ms_step = ms_total / K
+    value = world * b * N_PIX / (ms_step * 1e-3) / 1e9
+    k_ms = [sum(evs[k][i].elapsed_time(evs[k][i + 1]) for k in range(K)) / K for i in range(3)]
+    names = ["match_prep (2 launches)", "iter_proj_fused", "refine_fused"]
+    dom = max(range(3), key=lambda i: k_ms[i])
+    alg = {0: None, 1: B_ITER_PROJ, 2: B_REFINE}[dom]
+    achieved = (alg * b * N_PIX / (k_ms[dom] * 1e-3) / 1e9) if alg else None
+    roofline = {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": (achieved / peak) if achieved else None, "traffic": None,
+                "peak_kind": peak_kind, "algorithmic_bytes_per_pixel": alg,
+                "kernel_ms": {n: round(t, 4) for n, t in zip(names, k_ms)},
+                "kernels": {
+                    "iter_proj_fused": {"achieved": B_ITER_PROJ * b * N_PIX / (k_ms[1] * 1e-3) / 1e9,
+                                        "frac": B_ITER_PROJ * b * N_PIX / (k_ms[1] * 1e-3) / 1e9 / peak},
+                    "refine_fused": {"achieved": B_REFINE * b * N_PIX / (k_ms[2] * 1e-3) / 1e9,
+                                     "frac": B_REFINE * b * N_PIX / (k_ms[2] * 1e-3) / 1e9 / peak},
+                    "whole_call_225B": {"achieved": B_MATCH_CALL * b * N_PIX / (ms_step * 1e-3) / 1e9,
+                                        "frac": B_MATCH_CALL * b * N_PIX / (ms_step * 1e-3) / 1e9 / peak}}}
+
+    # ---------------------------------------------------------------- e2e through the plugin call
+    host = [t.cpu().pin_memory() for t in (X11, X21, D11, D21)]
+    dbuf = [torch.empty_like(t) for t in (X11, X21, D11, D21)]
+    idx_h = torch.empty((b, N_PIX), dtype=torch.int64).pin_memory()
+    val_h = torch.empty((b, N_PIX, 1), dtype=torch.bool).pin_memory()
+
+    def step_e2e():
+        for d, h in zip(dbuf, host):
+            d.copy_(h, non_blocking=True)
+        idx, valid = matching.match_iterative_proj(*dbuf)
+        idx_h.copy_(idx, non_blocking=True)
+        val_h.copy_(valid, non_blocking=True)
+
+    for _ in range(3):
+        step_e2e()
+    barrier()
+    Ke = max(3, min(K, 10))
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(Ke):
+        step_e2e()
+    e1.record()
+    barrier()
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1)) / Ke
+    e2e = {"value": world * b * N_PIX / (ms_e2e * 1e-3) / 1e9, "unit": "Gpix/s",
+           "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": idx_h.numel() * 8 + val_h.numel(),
+           "ms_per_step": ms_e2e, "call": "mast3r_slam.matching.match_iterative_proj"}
+    del host, dbuf
+
+    # ---------------------------------------------------------------- extras: GN rays, tracker
+    extra = {}
+    if not args.no_extra:
+        try:
+            extra.update(bench_gn(be, synth, dev, rank, world, peak, barrier, max_over_ranks))
+            extra.update(bench_tracker(be, synth, dev, peak))
+        except Exception as e:  # keep the headline line even if an extra fails
+            extra["error"] = repr(e)
+
+    # ---------------------------------------------------------------- CPU baseline (rank 0, N=1)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        threads = os.cpu_count() or 1
+        t = cpu_match_sample(2, threads)
+        cpu = {"value": 2 * N_PIX / t / 1e9, "unit": "Gpix/s", "cores": threads, "kind": "port",
+               "sample": f"2 frame pairs of {W}x{H}, one pass ({t:.1f} s): oracle C port of iter_proj + "
+                         "refine_matches (OpenMP) + torch-CPU glue"}
+
+    if rank == 0:
+        print(json.dumps({
+            "metric": "dense matching throughput (match_iterative_proj)", "value": value, "unit": "Gpix/s",
+            "n_gpus": world, "steps": K, "warmup": W_, "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "match_iterative_proj 512x384, iter_proj max_iter 10 + refine_matches "
+                                   "radius 3 dilation 5, 24-d desc (BASELINE configs[1])",
+                       "batch_pairs_per_gpu": b, "l2": f"inputs {in_bytes / 1e6:.0f} MB per step exceed the 126 MB L2",
+                       "parallelism": f"independent frame pairs x{world}"},
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
+            "cpu_baseline": cpu, "extra": extra}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def bench_gn(be, synth, dev, rank, world, peak, barrier, max_over_ranks):
+    """BASELINE configs[2]: gauss_newton_rays, 32 keyframes, 100 edges (200 directed), 512x384,
+    10 iterations (delta_thresh 0 so all run).  Single GPU: the drop-in call.  N GPUs: directed
+    edges sharded contiguously, per-edge blocks all-gathered each iteration."""
+    import torch
+    import torch.distributed as dist
+
+    g = synth.make_graph(N=32, seed=1236, device=dev)
+    M, n, N = g["M"], H * W, g["N"]
+    iters, reps = 10, 5
+    out = {}
+    if world == 1:
+        def run():
+            T = g["Twc"].clone()
+            be.gauss_newton_rays(T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
+                                 0.003, 10.0, 0.0, 1.5, iters, 0.0)
+            return T
+    else:
+        per = (M + world - 1) // world
+        e0, e1 = min(M, rank * per), min(M, (rank + 1) * per)
+        counts = [min(M, (r + 1) * per) - min(M, r * per) for r in range(world)]
+        prm = be._params(be.GN_RAYS, 0.003, 10.0, 0.0, 1.5)
+        sl = slice(e0, e1)
+        idx_l, val_l, Q_l = g["idx"][sl].contiguous(), g["valid"][sl].contiguous(), g["Q"][sl].contiguous()
+
+        def run():
+            T = g["Twc"].clone()
+            be.gauss_newton_sharded(prm, T, g["Xs"], g["Cs"], g["ii"], g["jj"], idx_l, val_l, Q_l, e0,
+                                    iters, 0.0, edge_counts=counts)
+            return T
+    for _ in range(3):
+        run()
+    barrier()
+    a = torch.cuda.Event(enable_timing=True); z = torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        run()
+    z.record()
+    barrier()
+    ms = max_over_ranks(a.elapsed_time(z)) / reps
+    out["gn_rays"] = {"workload": "gauss_newton_rays N=32, 200 directed edges, 512x384, 10 iterations "
+                                  "(BASELINE configs[2])" + (f", edge-sharded x{world}" if world > 1 else ""),
+                      "iters_per_s": iters / (ms * 1e-3), "ms_per_solve": ms}
+    if world == 1:
+        # accumulation kernel alone (the HBM-bound part): 45 B per (directed edge, point)
+        prm = be._params(be.GN_RAYS, 0.003, 10.0, 0.0, 1.5)
+        s = be.GNSolver(prm, g["Twc"].clone(), g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"])
+        for _ in range(3):
+            s.accumulate()
+        torch.cuda.synchronize()
+        a.record()
+        for _ in range(10):
+            s.accumulate()
+        z.record()
+        torch.cuda.synchronize()
+        ms_acc = a.elapsed_time(z) / 10
+        ach = B_GN_POINT * M * n / (ms_acc * 1e-3) / 1e9
+        a.record()
+        for _ in range(10):
+            s.solve_step(0.0)
+        z.record()
+        torch.cuda.synchronize()
+        out["gn_rays"].update({"accumulate_ms": ms_acc, "solve_step_ms": a.elapsed_time(z) / 10,
+                               "roofline": {"bound": "hbm", "kernel": "gn_accum_kernel<rays> (+edge finish)",
+                                            "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                                            "algorithmic_bytes_per_edge_point": B_GN_POINT}})
+    return out
+
+
+def bench_tracker(be, synth, dev, peak):
+    import torch
+
+    d = synth.make_tracker_inputs(seed=1234, device=dev)
+    ident = torch.tensor([0, 0, 0, 0, 0, 0, 1, 1], dtype=torch.float32, device=dev)
+
+    def run():
+        T = ident.clone()
+        return be.track_ray_dist(d["Xf"], d["Xk"], d["Qk"], d["valid"], T, 0.003, 10.0, 1.345, 50, 1e-3, 1e-3)
+    for _ in range(3):
+        st = run()
+    torch.cuda.synchronize()
+    its = int(st[0])
+    a = torch.cuda.Event(enable_timing=True); z = torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(20):
+        run()
+    z.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(z) / 20
+    ach = B_TRACK_POINT * N_PIX * its / (ms * 1e-3) / 1e9
+    return {"tracker": {"workload": "opt_pose_ray_dist_sim3 512x384, known Sim3 offset (BASELINE configs[0] on GPU)",
+                        "iterations": its, "ms_per_solve": ms, "iters_per_s": its / (ms * 1e-3),
+                        "roofline": {"bound": "hbm (L2-resident after pass 1: latency-bound)", "achieved": ach,
+                                     "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                                     "algorithmic_bytes_per_point": B_TRACK_POINT}}}
+
+
+if __name__ == "__main__":
+    main()

@@ -79,7 +79,7 @@ int m3r_iter_proj(const float* rays_img_with_grad, const float* pts_3d_norm,
  * accumulated in the reference's sequential fp16-rounded order and compared with
  * strict `>` starting from fp16 zero, so p1_new is bit-exact.
  *   D11 (b,H,W,F) f16 ; D21 (b,n,F) f16 ; p1 (b,n,2) i64 (u,v) ; p1_new (b,n,2) i64
- * F must be a multiple of 8 and <= 64 (MASt3R: 24). */
+ * F must be a multiple of 8 and <= 32 (MASt3R: 24). */
 int m3r_refine_matches_f16(const uint16_t* D11, const uint16_t* D21,
                            const int64_t* p1, int b, int H, int W, int n, int F,
                            int radius, int dilation_max, int64_t* p1_new,

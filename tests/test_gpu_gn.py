@@ -1,0 +1,284 @@
+"""GPU parity of the Sim3 Gauss-Newton entry points and the tracker solve (through the C ABI)
+against the CPU oracle and, when oracle/_ref is present, the UNMODIFIED reference extension.
+
+Bars (BASELINE.json north_star): Hessian blocks within 1e-4 relative error, pose updates within
+1e-5 in fp32.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from tests import synth
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+RAYS = dict(sigma_ray=0.003, sigma_dist=10.0, C_thresh=0.0, Q_thresh=1.5)  # base.yaml:35-50
+CALIB = dict(pixel_border=-10, z_eps=1e-6, sigma_pixel=1.0, sigma_depth=10.0, C_thresh=0.0, Q_thresh=1.5)
+BLOCK_RTOL = 1e-4
+DX_ATOL = 1e-5
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+def _small_graph(N=6, H=48, W=64, seed=1236, kf_ids=None, calib=False):
+    g = synth.make_graph(N=N, counts={1: None, 2: 3, "random": 1}, H=H, W=W, seed=seed, device=DEV,
+                         kf_ids=kf_ids)
+    if calib:
+        g["Xs"] = synth.constrain_points_to_ray(g["Xs"], H, W, g["K"])
+    return g
+
+
+def _prm(backends, orc, mode, g):
+    if mode == "rays":
+        return (backends._params(backends.GN_RAYS, RAYS["sigma_ray"], RAYS["sigma_dist"], 0.0, 1.5),
+                orc.make_params(orc.MODE_RAYS, RAYS["sigma_ray"], RAYS["sigma_dist"], 0.0, 1.5))
+    if mode == "calib":
+        return (backends._params(backends.GN_CALIB, 1.0, 10.0, 0.0, 1.5, g["K"], g["H"], g["W"], -10, 1e-6),
+                orc.make_params(orc.MODE_CALIB, 1.0, 10.0, 0.0, 1.5, _np(g["K"]), g["H"], g["W"], -10, 1e-6))
+    return (backends._params(backends.GN_POINTS, 0.05, 0.0, 0.0, 1.5),
+            orc.make_params(orc.MODE_POINTS, 0.05, 0.0, 0.0, 1.5))
+
+
+def _block_rel_err(a, b):
+    """Per-(7x7 or 7) block Frobenius relative error, normalised by the edge's own H scale."""
+    num = np.sqrt(((a - b) ** 2).reshape(a.shape[0], a.shape[1], -1).sum(-1))
+    den = np.sqrt((b ** 2).reshape(b.shape[0], b.shape[1], -1).sum(-1))
+    return num / np.maximum(den, 1e-30)
+
+
+@pytest.mark.parametrize("mode", ["rays", "calib", "points"])
+def test_blocks_vs_oracle(backends, orc, mode):
+    g = _small_graph(calib=(mode == "calib"))
+    prm, oprm = _prm(backends, orc, mode, g)
+    solver = backends.GNSolver(prm, g["Twc"].clone(), g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"],
+                               g["valid"], g["Q"])
+    blocks = solver.accumulate()
+    torch.cuda.synchronize()
+    Hs, gs = backends.gn_blocks_reference_layout(blocks)
+    _, ie, je, _, _ = orc.edge_rows(_np(g["ii"]), _np(g["jj"]))
+    _, _, Hs64, gs64 = orc.gn_blocks(oprm, _np(g["Twc"]), _np(g["Xs"]), _np(g["Cs"]), ie, je,
+                                     _np(g["idx"]), _np(g["valid"]), _np(g["Q"]), want64=True)
+    eh = _block_rel_err(_np(Hs), Hs64)
+    eg = _block_rel_err(_np(gs), gs64)
+    print(f"{mode}: H block rel err max {eh.max():.2e}, g rel err max {eg.max():.2e}")
+    assert np.isfinite(_np(Hs)).all() and np.abs(Hs64).max() > 0
+    assert eh.max() < BLOCK_RTOL
+    # gradients are sums with cancellation (residuals of both signs): bound them by the
+    # magnitude a 1e-4 relative error on the Hessian-weighted terms allows
+    assert eg.max() < 5e-3
+
+
+@pytest.mark.parametrize("mode", ["rays", "calib", "points"])
+def test_solve_vs_oracle(backends, orc, mode):
+    g = _small_graph(calib=(mode == "calib"), kf_ids=[3, 7, 8, 20, 21, 40])
+    prm, oprm = _prm(backends, orc, mode, g)
+    T_o, dx_o, its, hist = orc.gauss_newton(oprm, _np(g["Twc"]), _np(g["Xs"]), _np(g["Cs"]),
+                                            _np(g["ii"]), _np(g["jj"]), _np(g["idx"]),
+                                            _np(g["valid"]), _np(g["Q"]), 10, 0.0, history=True)
+    # first iteration: same linearisation point => dx is directly comparable
+    Twc = g["Twc"].clone()
+    solver = backends.GNSolver(prm, Twc, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"])
+    solver.accumulate()
+    dx1 = solver.solve_step(0.0).clone()
+    torch.cuda.synchronize()
+    d1 = np.abs(_np(dx1) - hist[0]).max()
+    print(f"{mode}: |dx_1 - oracle| max {d1:.2e} (|dx_1| max {np.abs(hist[0]).max():.2e})")
+    assert d1 < DX_ATOL
+    # whole solve through the drop-in entry point
+    Twc = g["Twc"].clone()
+    fn = dict(rays=lambda: backends.gauss_newton_rays(Twc, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"],
+                                                      g["valid"], g["Q"], 0.003, 10.0, 0.0, 1.5, 10, 0.0),
+              calib=lambda: backends.gauss_newton_calib(Twc, g["Xs"], g["Cs"], g["K"], g["ii"], g["jj"],
+                                                        g["idx"], g["valid"], g["Q"], g["H"], g["W"], -10,
+                                                        1e-6, 1.0, 10.0, 0.0, 1.5, 10, 0.0),
+              points=lambda: backends.gauss_newton_points(Twc, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"],
+                                                          g["valid"], g["Q"], 0.05, 0.0, 1.5, 10, 0.0))[mode]
+    (dx,) = fn()
+    torch.cuda.synchronize()
+    assert dx.shape == (g["N"] - 1, 7) and dx.dtype == torch.float32
+    dT = np.abs(_np(Twc) - T_o).max()
+    print(f"{mode}: final pose diff vs oracle {dT:.2e}, last |dx| {np.abs(_np(dx)).max():.2e}")
+    assert dT < 5e-5
+    assert np.array_equal(_np(Twc)[0], _np(g["Twc"])[0])  # gauge pose untouched
+    # the solve moved towards the ground truth
+    e0 = np.abs(_np(g["Twc"]) - _np(g["T_gt"])).max()
+    e1 = np.abs(_np(Twc) - _np(g["T_gt"])).max()
+    assert e1 < 0.5 * e0
+
+
+@pytest.mark.parametrize("mode", ["rays", "calib", "points"])
+def test_solve_vs_reference(backends, ref_ext, mode):
+    if ref_ext is None:
+        pytest.skip("oracle/_ref not built")
+    g = _small_graph(N=8, H=96, W=128, calib=(mode == "calib"), kf_ids=[0, 2, 5, 6, 9, 11, 12, 30])
+
+    def run(mod, iters):
+        Twc = g["Twc"].clone()
+        if mode == "rays":
+            out = mod.gauss_newton_rays(Twc, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"],
+                                        g["Q"], 0.003, 10.0, 0.0, 1.5, iters, 0.0)
+        elif mode == "calib":
+            out = mod.gauss_newton_calib(Twc, g["Xs"], g["Cs"], g["K"], g["ii"], g["jj"], g["idx"],
+                                         g["valid"], g["Q"], g["H"], g["W"], -10, 1e-6, 1.0, 10.0, 0.0,
+                                         1.5, iters, 0.0)
+        else:
+            out = mod.gauss_newton_points(Twc, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"],
+                                          g["Q"], 0.05, 0.0, 1.5, iters, 0.0)
+        torch.cuda.synchronize()
+        return Twc, out[0]
+
+    T_r1, dx_r1 = run(ref_ext, 1)
+    T_n1, dx_n1 = run(backends, 1)
+    d1 = float((dx_r1 - dx_n1).abs().max())
+    print(f"{mode}: |dx_1 - reference| max {d1:.2e} (|dx_1| max {float(dx_r1.abs().max()):.2e})")
+    assert d1 < DX_ATOL
+    assert float((T_r1 - T_n1).abs().max()) < DX_ATOL
+    T_r, dx_r = run(ref_ext, 10)
+    T_n, dx_n = run(backends, 10)
+    dT = float((T_r - T_n).abs().max())
+    print(f"{mode}: final pose diff vs reference after 10 iterations {dT:.2e}")
+    assert dT < 5e-5
+
+
+def test_rays_full_size_vs_reference_and_properties(backends, ref_ext):
+    """BASELINE config 3 shape at reduced edge count (N=8 keyframes, 512x384): dx parity with the
+    reference plus size-independent properties: symmetry of S, reverse-edge gradient
+    consistency, determinism (bit-identical reruns), early exit."""
+    g = synth.make_graph(N=8, counts={1: None, 2: 4, "random": 1}, seed=1236, device=DEV)
+    prm = backends._params(backends.GN_RAYS, 0.003, 10.0, 0.0, 1.5)
+    s1 = backends.GNSolver(prm, g["Twc"].clone(), g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"])
+    b1 = s1.accumulate().clone()
+    s2 = backends.GNSolver(prm, g["Twc"].clone(), g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"])
+    b2 = s2.accumulate().clone()
+    torch.cuda.synchronize()
+    assert torch.equal(b1, b2)  # fixed-order reductions
+    S = b1[:, :49].view(-1, 7, 7)
+    assert float((S - S.transpose(1, 2)).abs().max()) <= 1e-9 * float(S.abs().max())
+    ev = torch.linalg.eigvalsh(S)
+    assert float(ev.min()) > -1e-6 * float(ev.max())  # PSD
+    if ref_ext is not None:
+        Tr, Tn = g["Twc"].clone(), g["Twc"].clone()
+        (dxr,) = ref_ext.gauss_newton_rays(Tr, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"],
+                                           g["Q"], 0.003, 10.0, 0.0, 1.5, 1, 0.0)
+        torch.cuda.synchronize()
+        (dxn,) = backends.gauss_newton_rays(Tn, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"],
+                                            g["Q"], 0.003, 10.0, 0.0, 1.5, 1, 0.0)
+        torch.cuda.synchronize()
+        d = float((dxr - dxn).abs().max())
+        print(f"full-size rays: |dx_1 - reference| max {d:.2e}")
+        assert d < DX_ATOL
+    # early exit: a huge delta_thresh stops after the first iteration (the reference's `break`)
+    Ta, Tb = g["Twc"].clone(), g["Twc"].clone()
+    backends.gauss_newton_rays(Ta, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
+                               0.003, 10.0, 0.0, 1.5, 10, 1e9)
+    backends.gauss_newton_rays(Tb, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
+                               0.003, 10.0, 0.0, 1.5, 1, 0.0)
+    torch.cuda.synchronize()
+    assert torch.equal(Ta, Tb)
+
+
+def test_gn_edge_cases(backends, orc):
+    g = _small_graph()
+    # max_iter = 0: poses untouched, dx zeros
+    T = g["Twc"].clone()
+    (dx,) = backends.gauss_newton_rays(T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
+                                       0.003, 10.0, 0.0, 1.5, 0, 0.0)
+    assert torch.equal(T, g["Twc"]) and float(dx.abs().max()) == 0.0
+    # no valid correspondences => singular system => zero step, poses unchanged (gn_kernels.cu:142-150)
+    T = g["Twc"].clone()
+    (dx,) = backends.gauss_newton_rays(T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"],
+                                       torch.zeros_like(g["valid"]), g["Q"], 0.003, 10.0, 0.0, 1.5, 3, 0.0)
+    torch.cuda.synchronize()
+    assert torch.equal(T, g["Twc"]) and float(dx.abs().max()) == 0.0
+    # Q below threshold everywhere: same
+    T = g["Twc"].clone()
+    (dx,) = backends.gauss_newton_rays(T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"],
+                                       torch.ones_like(g["Q"]), 0.003, 10.0, 0.0, 1.5, 3, 0.0)
+    torch.cuda.synchronize()
+    assert torch.equal(T, g["Twc"])
+    # a two-keyframe graph with exact correspondences recovers a known Sim3 perturbation
+    g2 = synth.make_graph(N=2, counts={1: None}, H=48, W=64, seed=5, device=DEV, noise=0.0)
+    T = g2["Twc"].clone()
+    backends.gauss_newton_rays(T, g2["Xs"], g2["Cs"], g2["ii"], g2["jj"], g2["idx"], g2["valid"], g2["Q"],
+                               0.003, 10.0, 0.0, 1.5, 10, 1e-8)
+    torch.cuda.synchronize()
+    assert float((T - g2["T_gt"]).abs().max()) < 2e-2  # nearest-pixel correspondences bound this
+    assert float((T - g2["T_gt"]).abs().max()) < 0.5 * float((g2["Twc"] - g2["T_gt"]).abs().max())
+
+
+def test_pose_retr_vs_oracle(backends, orc):
+    gen = torch.Generator(device=DEV).manual_seed(11)
+    N = 300
+    T = synth.make_poses(N, 3, DEV)
+    dx = 0.05 * torch.randn((N - 1, 7), generator=gen, device=DEV)
+    # exercise the Taylor branches (gn_kernels.cu:306-314,350-373)
+    dx[0] = 0.0
+    dx[1, 3:6] = 1e-5
+    dx[2, 6] = 1e-8
+    dx[3, 3:6] = 0.0
+    dx[4, 3:6] = 1e-7; dx[4, 6] = 1e-7
+    exp = orc.pose_retr(_np(T), _np(dx), 1)
+    out = backends.pose_retr(T.clone(), dx, 1)
+    torch.cuda.synchronize()
+    assert np.array_equal(_np(out)[0], _np(T)[0])
+    assert np.abs(_np(out) - exp).max() < 2e-6
+    assert np.allclose(_np(out)[1], _np(T)[1], atol=0, rtol=0)  # retr(0) = identity, exactly
+
+
+# ---------------------------------------------------------------------------------- tracker
+
+def test_tracker_vs_reference_golden(backends):
+    """Fused tracker loop vs the iterates of the reference's own tracker.py (golden fixture made by
+    tests/golden/gen_tracker_golden.py from /root/reference)."""
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "tracker_ref.npz"))
+    sr, sd, hk, mi, re_, dn = z["cfg"]
+    for name in ("a", "b"):
+        H, W, seed = (int(v) for v in z[f"{name}_HW"])
+        d = synth.make_tracker_inputs(H, W, seed=seed, device="cpu")
+        T = torch.tensor([0, 0, 0, 0, 0, 0, 1, 1], dtype=torch.float32, device=DEV)
+        status, cost = backends.track_ray_dist(d["Xf"].to(DEV), d["Xk"].to(DEV), d["Qk"].to(DEV),
+                                               d["valid"].to(DEV), T, sr, sd, hk, int(mi), re_, dn,
+                                               want_cost=True)
+        torch.cuda.synchronize()
+        its, conv, fail, _ = status.tolist()
+        ref_costs = z[f"{name}_costs"]
+        assert fail == 0 and conv == 1
+        assert its == len(ref_costs)
+        assert np.allclose(_np(cost)[:its], ref_costs, rtol=2e-4)
+        assert np.abs(_np(T) - z[f"{name}_T_CkCf_out"][0]).max() < 2e-5
+
+
+def test_tracker_full_size_vs_oracle(backends):
+    from oracle import tracker as otrk
+
+    d = synth.make_tracker_inputs(seed=1234, device=DEV)
+    T = torch.tensor([0, 0, 0, 0, 0, 0, 1, 1], dtype=torch.float32, device=DEV)
+    status, cost = backends.track_ray_dist(d["Xf"], d["Xk"], d["Qk"], d["valid"], T, 0.003, 10.0, 1.345,
+                                           50, 1e-3, 1e-3, want_cost=True)
+    torch.cuda.synchronize()
+    hist = []
+    T_o, its_o, conv_o = otrk.opt_pose_ray_dist_sim3(
+        d["Xf"].cpu(), d["Xk"].cpu(), otrk.Sim3.Identity(1), d["Qk"].cpu(), d["valid"].cpu(), history=hist)
+    its, conv, fail, _ = status.tolist()
+    assert (its, conv, fail) == (its_o, int(conv_o), 0)
+    assert np.allclose(_np(cost)[:its], [h[0] for h in hist], rtol=2e-4)
+    assert np.abs(_np(T) - _np(T_o.data[0])).max() < 2e-5
+    # recovers the planted Sim3 (within 1e-3)
+    assert np.abs(_np(T) - _np(d["T_gt"])).max() < 1e-3
+
+
+def test_tracker_cholesky_failure_flag(backends):
+    """No valid points => H = 0 => not SPD: status.failed, pose untouched (the reference raises
+    from torch.linalg.cholesky and the caller treats it as a tracking failure, tracker.py:72-93)."""
+    d = synth.make_tracker_inputs(48, 64, seed=3, device=DEV)
+    T = torch.tensor([0.1, 0, 0, 0, 0, 0, 1, 1], dtype=torch.float32, device=DEV)
+    T0 = T.clone()
+    status = backends.track_ray_dist(d["Xf"], d["Xk"], d["Qk"], torch.zeros_like(d["valid"]), T, 0.003,
+                                     10.0, 1.345, 50, 1e-3, 1e-3)
+    torch.cuda.synchronize()
+    assert status.tolist()[2] == 1 and torch.equal(T, T0)

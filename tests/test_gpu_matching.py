@@ -1,0 +1,299 @@
+"""GPU parity of the dense-matching entry points (through the C ABI) against the CPU oracle and,
+when oracle/_ref is present, against the UNMODIFIED reference extension on the same device.
+
+Bars (BASELINE.json north_star): refine_matches indices bit-exact; iter_proj (u,v) within 1e-4 px
+with integer indices allowed to differ only at rounding-boundary pixels.
+"""
+import numpy as np
+import pytest
+import torch
+
+from tests import synth
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+CFG = dict(max_iter=10, lambda_init=1e-8, convergence_thresh=1e-6, dist_thresh=0.1, radius=3,
+           dilation_max=5)  # config/base.yaml:8-14
+PX_TOL = 1e-4  # px, BASELINE.json north_star
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+def _ref_prep(X11, X21, idx_init=None):
+    """matching.prep_for_iter_proj (matching.py:25-50) in plain torch."""
+    import torch.nn.functional as F
+
+    b, h, w, _ = X11.shape
+    rays = F.normalize(X11, dim=-1).permute(0, 3, 1, 2)
+    c = rays.shape[1]
+    gxk = (1.0 / 32.0) * torch.tensor([[-3.0, 0.0, 3.0], [-10.0, 0.0, 10.0], [-3.0, 0.0, 3.0]],
+                                      device=X11.device).repeat(c, 1, 1, 1)
+    gyk = (1.0 / 32.0) * torch.tensor([[-3.0, -10.0, -3.0], [0.0, 0.0, 0.0], [3.0, 10.0, 3.0]],
+                                      device=X11.device).repeat(c, 1, 1, 1)
+    pad = F.pad(rays, (1, 1, 1, 1), mode="reflect")
+    gx = F.conv2d(pad, gxk, groups=c)
+    gy = F.conv2d(pad, gyk, groups=c)
+    img = torch.cat((rays, gx, gy), 1).permute(0, 2, 3, 1).contiguous()
+    pts = F.normalize(X21.view(b, -1, 3), dim=-1)
+    if idx_init is None:
+        idx_init = torch.arange(h * w, device=X11.device)[None].repeat(b, 1)
+    p_init = torch.stack((idx_init % w, idx_init // w), -1).float()
+    return img, pts.contiguous(), p_init.contiguous()
+
+
+def _iter_proj_agreement(p_a, c_a, p_b, c_b, tol=PX_TOL):
+    """-> (#pixels with |dp| > tol, #converged flags differing, #integer index flips)."""
+    d = np.abs(p_a - p_b).max(-1)
+    far = int((d > tol).sum())
+    flips = int((np.trunc(p_a) != np.trunc(p_b)).any(-1).sum())
+    return far, int((c_a != c_b).sum()), flips, float(d.max())
+
+
+@pytest.mark.parametrize("b,H,W", [(1, 48, 64), (2, 96, 128)])
+def test_iter_proj_vs_oracle(backends, orc, b, H, W):
+    m = synth.make_match_inputs(b, H, W, 24, seed=1235, device=DEV)
+    img, pts, p0 = _ref_prep(m["X11"], m["X21"])
+    p_new, conv = backends.iter_proj(img, pts, p0, CFG["max_iter"], CFG["lambda_init"],
+                                     CFG["convergence_thresh"])
+    torch.cuda.synchronize()
+    assert p_new.shape == (b, H * W, 2) and p_new.dtype == torch.float32
+    assert conv.shape == (b, H * W) and conv.dtype == torch.bool
+    p_o, c_o = orc.iter_proj(_np(img), _np(pts), _np(p0), CFG["max_iter"], CFG["lambda_init"],
+                             CFG["convergence_thresh"])
+    far, dconv, flips, dmax = _iter_proj_agreement(_np(p_new), _np(conv), p_o, c_o)
+    n = b * H * W
+    # the oracle is compiled without FMA contraction: agreement is to rounding, and an LM
+    # accept/reject decision can flip on a tie; such pixels must be rare
+    assert far <= max(2, n // 2000), (far, dmax)
+    assert dconv <= max(2, n // 2000)
+    assert flips <= max(2, n // 2000)
+
+
+def test_iter_proj_vs_reference(backends, ref_ext):
+    if ref_ext is None:
+        pytest.skip("oracle/_ref not built")
+    H, W, b = synth.H0, synth.W0, 2
+    m = synth.make_match_inputs(b, H, W, 24, seed=1235, device=DEV)
+    img, pts, p0 = _ref_prep(m["X11"], m["X21"])
+    args = (img, pts, p0, CFG["max_iter"], CFG["lambda_init"], CFG["convergence_thresh"])
+    p_r, c_r = ref_ext.iter_proj(*args)
+    torch.cuda.synchronize()
+    p_n, c_n = backends.iter_proj(*args)
+    torch.cuda.synchronize()
+    far, dconv, flips, dmax = _iter_proj_agreement(_np(p_n), _np(c_n), _np(p_r), _np(c_r))
+    n = b * H * W
+    print(f"iter_proj vs reference: {far}/{n} pixels > {PX_TOL} px (max {dmax:.3g}), "
+          f"{dconv} converged flags differ, {flips} integer index flips")
+    assert far <= n // 5000, (far, dmax)
+    assert dconv <= n // 5000
+    assert flips <= n // 5000
+
+
+def test_iter_proj_identity_kat(backends):
+    """Identity warp: the target ray IS the ray image at the pixel => p stays put, converged."""
+    H, W = 48, 64
+    m = synth.make_match_inputs(1, H, W, 8, seed=7, device=DEV)
+    img, _, p0 = _ref_prep(m["X11"], m["X11"])
+    pts = img[..., :3].reshape(1, H * W, 3).contiguous()
+    p_new, conv = backends.iter_proj(img, pts, p0, 10, 1e-8, 1e-6)
+    inner = ((p0[..., 0] >= 1) & (p0[..., 0] <= W - 2) & (p0[..., 1] >= 1) & (p0[..., 1] <= H - 2))
+    # re-normalising an already unit ray may move its last bit, so allow a few ulps of drift
+    assert float((p_new[inner] - p0[inner]).abs().max()) < 1e-4
+    assert bool(conv[inner].all())
+
+
+def test_iter_proj_max_iter_zero_and_ragged(backends, orc):
+    """max_iter = 0 => clamped p_init, converged all false; n not a multiple of the
+    CTA size and n != H*W is safe (the reference has no bounds guard)."""
+    H, W = 48, 64
+    m = synth.make_match_inputs(1, H, W, 8, seed=9, device=DEV)
+    img, pts, p0 = _ref_prep(m["X11"], m["X21"])
+    n = 777
+    pts, p0 = pts[:, :n].contiguous(), (p0[:, :n] - 3.0).contiguous()
+    p_new, conv = backends.iter_proj(img, pts, p0, 0, 1e-8, 1e-6)
+    exp = torch.stack((p0[..., 0].clamp(1, W - 2), p0[..., 1].clamp(1, H - 2)), -1)
+    assert torch.equal(p_new, exp) and not bool(conv.any())
+    p_new, conv = backends.iter_proj(img, pts, p0, 10, 1e-8, 1e-6)
+    p_o, c_o = orc.iter_proj(_np(img), _np(pts), _np(p0), 10, 1e-8, 1e-6)
+    far, dconv, flips, _ = _iter_proj_agreement(_np(p_new), _np(conv), p_o, c_o)
+    assert far <= 2 and dconv <= 2
+    # empty batch / empty n
+    e = backends.iter_proj(img, pts[:, :0].contiguous(), p0[:, :0].contiguous(), 10, 1e-8, 1e-6)
+    assert e[0].shape == (1, 0, 2) and e[1].shape == (1, 0)
+
+
+def _refine_inputs(b, H, W, seed, F=24):
+    m = synth.make_match_inputs(b, H, W, F, seed=seed, device=DEV)
+    g = torch.Generator(device=DEV).manual_seed(seed + 1)
+    # start a few pixels off the truth, including positions near / outside the border window
+    p = m["p_star"].view(b, H * W, 2) + torch.randint(-4, 5, (b, H * W, 2), generator=g, device=DEV)
+    p1 = torch.stack((p[..., 0].clamp(0, W - 1), p[..., 1].clamp(0, H - 1)), -1).round().long()
+    return m["D11"].half().contiguous(), m["D21"].view(b, H * W, F).half().contiguous(), p1.contiguous()
+
+
+@pytest.mark.parametrize("b,H,W,F", [(1, 48, 64, 24), (2, 96, 128, 24), (1, 40, 56, 16), (1, 33, 47, 8)])
+def test_refine_matches_bit_exact_vs_oracle(backends, orc, b, H, W, F):
+    D11, D21, p1 = _refine_inputs(b, H, W, 1300 + F, F)
+    (out,) = backends.refine_matches(D11, D21, p1, CFG["radius"], CFG["dilation_max"])
+    torch.cuda.synchronize()
+    exp = orc.refine_matches(_np(D11), _np(D21), _np(p1), CFG["radius"], CFG["dilation_max"])
+    assert out.dtype == torch.int64 and out.shape == p1.shape
+    assert np.array_equal(_np(out), exp)
+    assert (_np(out) != _np(p1)).any()  # the search moved something
+
+
+def test_refine_matches_bit_exact_vs_reference_full_size(backends, ref_ext):
+    if ref_ext is None:
+        pytest.skip("oracle/_ref not built")
+    D11, D21, p1 = _refine_inputs(2, synth.H0, synth.W0, 1235)
+    (r,) = ref_ext.refine_matches(D11, D21, p1, CFG["radius"], CFG["dilation_max"])
+    torch.cuda.synchronize()
+    (o,) = backends.refine_matches(D11, D21, p1, CFG["radius"], CFG["dilation_max"])
+    torch.cuda.synchronize()
+    assert torch.equal(o, r)
+
+
+def test_refine_matches_f32_vs_oracle_and_reference(backends, orc, ref_ext):
+    b, H, W, F = 1, 48, 64, 24
+    D11, D21, p1 = _refine_inputs(b, H, W, 1400, F)
+    D11, D21 = D11.float().contiguous(), D21.float().contiguous()
+    (out,) = backends.refine_matches(D11, D21, p1, 3, 5)
+    exp = orc.refine_matches(_np(D11), _np(D21), _np(p1), 3, 5)
+    assert np.array_equal(_np(out), exp)
+    if ref_ext is not None:
+        (r,) = ref_ext.refine_matches(D11, D21, p1, 3, 5)
+        torch.cuda.synchronize()
+        assert torch.equal(out, r)
+
+
+def test_refine_matches_nonpositive_scores_kat(backends, ref_ext):
+    """the fp16 max starts at +0, so when every candidate score is <= 0 the input
+    coordinate is returned unchanged."""
+    b, H, W, F = 1, 32, 40, 24
+    g = torch.Generator(device=DEV).manual_seed(3)
+    D11 = torch.rand((b, H, W, F), generator=g, device=DEV).half()
+    D21 = (-torch.rand((b, H * W, F), generator=g, device=DEV)).half()
+    p1 = torch.stack(torch.meshgrid(torch.arange(W, device=DEV), torch.arange(H, device=DEV),
+                                    indexing="xy"), -1).reshape(1, H * W, 2).contiguous()
+    (out,) = backends.refine_matches(D11, D21, p1, 3, 5)
+    assert torch.equal(out, p1)
+    if ref_ext is not None:
+        (r,) = ref_ext.refine_matches(D11, D21, p1, 3, 5)
+        torch.cuda.synchronize()
+        assert torch.equal(r, p1)
+
+
+def test_refine_matches_planted_peak_kat(backends):
+    """A one-hot-ish descriptor planted at an offset reachable by the dilation schedule wins."""
+    H, W, F = 64, 64, 24
+    D11 = torch.zeros((1, H, W, F), device=DEV).half()
+    D11[..., 0] = 0.01
+    D11[0, 37, 29, 1] = 1.0  # (v, u) = (37, 29)
+    D21 = torch.zeros((1, 1, F), device=DEV).half()
+    D21[0, 0, 1] = 1.0
+    D21[0, 0, 0] = 0.5
+    p1 = torch.tensor([[[24, 32]]], device=DEV, dtype=torch.int64)  # (u,v): +5 in u and v
+    (out,) = backends.refine_matches(D11, D21, p1, 3, 5)
+    assert out.tolist() == [[[29, 37]]]
+
+
+def test_refine_ties_first_in_scan_order(backends, orc):
+    """Constant descriptors: every candidate ties; strict '>' keeps the first in-image candidate
+    in (u outer, v inner) scan order of the first dilation with a positive score."""
+    H, W, F = 40, 48, 24
+    D11 = torch.full((1, H, W, F), 0.25, device=DEV).half()
+    D21 = torch.full((1, H * W, F), 0.25, device=DEV).half()
+    p1 = torch.stack(torch.meshgrid(torch.arange(W, device=DEV), torch.arange(H, device=DEV),
+                                    indexing="xy"), -1).reshape(1, H * W, 2).contiguous()
+    (out,) = backends.refine_matches(D11, D21, p1, 3, 5)
+    exp = orc.refine_matches(_np(D11), _np(D21), _np(p1), 3, 5)
+    assert np.array_equal(_np(out), exp)
+
+
+def test_fused_prep_matches_torch_glue(backends):
+    b, H, W = 2, 96, 128
+    m = synth.make_match_inputs(b, H, W, 24, seed=21, device=DEV)
+    img_t, _, _ = _ref_prep(m["X11"], m["X21"])
+    rays, D11h = backends.match_prep(m["X11"], m["D11"])
+    torch.cuda.synchronize()
+    assert torch.equal(D11h, m["D11"].half())
+    assert torch.allclose(rays, img_t, rtol=0, atol=2e-6)
+    assert torch.equal(rays[..., :3], img_t[..., :3])
+
+
+def test_fused_match_equals_unfused_pipeline(backends):
+    """m3r_match_prep + m3r_match_iter_proj_fused + m3r_match_refine_fused == the reference
+    call sequence of matching.match_iterative_proj (matching.py:52-90) run through the plain
+    entry points, given the same ray image."""
+    b, H, W, F = 2, 96, 128, 24
+    m = synth.make_match_inputs(b, H, W, F, seed=33, device=DEV)
+    rays, D11h = backends.match_prep(m["X11"], m["D11"])
+    _, pts, p0 = _ref_prep(m["X11"], m["X21"])
+    # unfused
+    p_new, conv = backends.iter_proj(rays, pts, p0, CFG["max_iter"], CFG["lambda_init"],
+                                     CFG["convergence_thresh"])
+    p1 = p_new.long()
+    bi = torch.arange(b, device=DEV)[:, None].repeat(1, H * W)
+    d = torch.linalg.norm(m["X11"][bi, p1[..., 1], p1[..., 0], :].reshape(b, H, W, 3) - m["X21"], dim=-1)
+    valid = conv & (d < CFG["dist_thresh"]).view(b, -1)
+    (p1r,) = backends.refine_matches(m["D11"].half(), m["D21"].view(b, H * W, -1).half(), p1,
+                                     CFG["radius"], CFG["dilation_max"])
+    idx = p1r[..., 0] + W * p1r[..., 1]
+    # fused
+    p1_f, valid_f, p_new_f = backends.match_iter_proj_fused(
+        rays, m["X11"], m["X21"], None, CFG["max_iter"], CFG["lambda_init"],
+        CFG["convergence_thresh"], CFG["dist_thresh"], want_p_new=True)
+    idx_f = backends.match_refine_fused(D11h, m["D21"], p1_f, CFG["radius"], CFG["dilation_max"])
+    torch.cuda.synchronize()
+    # the fused kernel normalises X21 itself (x / max(|x|, eps)) — same expression as F.normalize
+    dpx = (p_new_f - p_new).abs().max(-1).values
+    assert int((dpx > PX_TOL).sum()) <= b * H * W // 2000
+    same = (p1_f == p1).all(-1)
+    assert float(same.float().mean()) > 0.999
+    assert torch.equal(idx_f[same], idx[same])
+    assert float((valid_f == valid).float().mean()) > 0.999
+
+
+def test_matching_full_size_properties(backends):
+    """BASELINE full size (512x384, b=2): size-independent properties of the matching path."""
+    b, H, W, F = 2, synth.H0, synth.W0, 24
+    m = synth.make_match_inputs(b, H, W, F, seed=1235, device=DEV)
+    rays, D11h = backends.match_prep(m["X11"], m["D11"])
+    p1, valid, p_new = backends.match_iter_proj_fused(
+        rays, m["X11"], m["X21"], None, CFG["max_iter"], CFG["lambda_init"],
+        CFG["convergence_thresh"], CFG["dist_thresh"], want_p_new=True)
+    idx = backends.match_refine_fused(D11h, m["D21"], p1, CFG["radius"], CFG["dilation_max"])
+    torch.cuda.synchronize()
+    # outputs stay inside the clamp box / image
+    assert float(p_new[..., 0].min()) >= 1 and float(p_new[..., 0].max()) <= W - 2
+    assert float(p_new[..., 1].min()) >= 1 and float(p_new[..., 1].max()) <= H - 2
+    assert int(idx.min()) >= 0 and int(idx.max()) < H * W
+    # the planted correspondence field is recovered where the solve converged
+    err = (p_new.view(b, H, W, 2) - m["p_star"]).norm(dim=-1).view(b, -1)
+    assert float(valid.float().mean()) > 0.8
+    assert float(err[valid].median()) < 0.5
+    # refinement moves at most radius * sum(dilations) = 3*15 px per axis from its start
+    u, v = idx % W, idx // W
+    assert int((u - p1[..., 0]).abs().max()) <= 45 and int((v - p1[..., 1]).abs().max()) <= 45
+    # idempotence of the warm start: feeding the result back as idx_init converges to the same place
+    p1b, validb, p_newb = backends.match_iter_proj_fused(
+        rays, m["X11"], m["X21"], p1[..., 0] + W * p1[..., 1], CFG["max_iter"], CFG["lambda_init"],
+        CFG["convergence_thresh"], CFG["dist_thresh"], want_p_new=True)
+    both = valid & validb
+    assert float((p_newb - p_new).norm(dim=-1)[both].median()) < 1e-2
+
+
+def test_usage_errors(backends):
+    img = torch.zeros((1, 8, 8, 9), device=DEV)
+    with pytest.raises(RuntimeError):
+        backends.iter_proj(img.permute(0, 2, 1, 3), torch.zeros((1, 4, 3), device=DEV),
+                           torch.zeros((1, 4, 2), device=DEV), 1, 1e-8, 1e-6)  # non-contiguous
+    with pytest.raises(RuntimeError):
+        backends.iter_proj(img.cpu(), torch.zeros((1, 4, 3)), torch.zeros((1, 4, 2)), 1, 1e-8, 1e-6)
+    with pytest.raises(RuntimeError):
+        backends.refine_matches(torch.zeros((1, 8, 8, 12), device=DEV).half(),
+                                torch.zeros((1, 4, 12), device=DEV).half(),
+                                torch.zeros((1, 4, 2), device=DEV, dtype=torch.int64), 3, 5)  # F % 8
