@@ -316,9 +316,8 @@ def bench_gn(be, synth, dev, rank, world, peak, barrier, max_over_ranks):
                                  0.003, 10.0, 0.0, 1.5, iters, 0.0)
             return T
     else:
-        per = (M + world - 1) // world
-        e0, e1 = min(M, rank * per), min(M, (rank + 1) * per)
-        counts = [min(M, (r + 1) * per) - min(M, r * per) for r in range(world)]
+        e0, cnt, counts = be.shard_edges(M, world, rank)
+        e1 = e0 + cnt
         prm = be._params(be.GN_RAYS, 0.003, 10.0, 0.0, 1.5)
         sl = slice(e0, e1)
         idx_l, val_l, Q_l = g["idx"][sl].contiguous(), g["valid"][sl].contiguous(), g["Q"][sl].contiguous()

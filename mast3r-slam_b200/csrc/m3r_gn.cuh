@@ -43,6 +43,7 @@ inline int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
 // so an edge's block is bit-identical whether the graph is solved on 1 GPU or sharded.
 inline void gn_splits(int n, int M, int& S, int& chunk) {
   const int unit = 1024;  // 256 threads x 4 points
+  if (n <= 0) { S = 1; chunk = unit; return; }  // layout queries that only need (N, M) offsets
   int want = (8 * 2 * kNumSMs + (M > 0 ? M : 1) - 1) / (M > 0 ? M : 1);  // ~8 waves of 2 CTA/SM
   if (want < 1) want = 1;
   if (want > 32) want = 32;
