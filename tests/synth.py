@@ -103,8 +103,10 @@ def make_match_inputs(b=1, H=H0, W=W0, Fdim=24, seed=1235, device="cpu", max_dis
     X11 = torch.stack([(u - K[0, 2]) / K[0, 0] * z, (v - K[1, 2]) / K[1, 1] * z, z], -1).contiguous()
     disp = smooth_noise((b, 2, H, W), 32.0 * W / W0, gen, device) * (max_disp * W / W0 / 2.5)
     disp = disp.clamp(-max_disp * W / W0, max_disp * W / W0)
-    pu = (u[None] + disp[:, 0]).clamp(2, W - 3)
-    pv = (v[None] + disp[:, 1]).clamp(2, H - 3)
+    # clamp bounds are deliberately non-integer: an exactly integer optimum would sit on the
+    # .long() truncation boundary of matching.py:68 and make the integer match index ill-posed
+    pu = (u[None] + disp[:, 0]).clamp(2.37, W - 3.37)
+    pv = (v[None] + disp[:, 1]).clamp(2.37, H - 3.37)
     grid = torch.stack([pu / (W - 1) * 2 - 1, pv / (H - 1) * 2 - 1], -1)
     samp = lambda img: F.grid_sample(img.permute(0, 3, 1, 2), grid, mode="bilinear",
                                      align_corners=True).permute(0, 2, 3, 1)
