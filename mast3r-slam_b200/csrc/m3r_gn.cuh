@@ -11,7 +11,8 @@
 //   part     : float[Ml*S*36] per-CTA partial sums of the LOCAL 28+7 normal-equation terms
 //   blocks   : double[M*56]  per-edge S (7x7) and v (7) after the adjoint transform
 //   A        : double[Dp*Dp] augmented normal matrix [H b; b^T 1], padded to 32
-//   x        : double[2*Dp]  forward-substituted rhs y, then the solution x
+//   x        : double[2*Dp]  the solution x (second half: scratch)
+//   flags    : int32[nb*nb + nb] tile-ready / x-block-ready epochs of the dataflow Cholesky
 #pragma once
 #include "m3r_common.cuh"
 
@@ -29,12 +30,13 @@ struct GnHeader {
 };
 
 struct GnLayout {
-  size_t hdr, ie, je, keys, rank, row_ptr, adj, xc, part, blocks, A, x, total;
+  size_t hdr, ie, je, keys, rank, row_ptr, adj, xc, part, blocks, A, x, flags, total;
   int P;       // sort size
   int S;       // point splits per edge
   int chunk;   // points per split
   int D;       // 7*(N-1)
   int Dp;      // padded dimension of the augmented system
+  int nflags;  // entries of `flags`
 };
 
 inline int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
@@ -72,7 +74,9 @@ inline GnLayout gn_layout(int N, int M, int Ml, int n) {
   L.adj = take(sizeof(int) * (size_t)2 * M);
   L.blocks = take(sizeof(double) * (size_t)M * kGnBlock);
   L.A = take(sizeof(double) * (size_t)L.Dp * L.Dp);
-  L.x = take(sizeof(double) * (size_t)2 * L.Dp);  // y (work) and x (solution)
+  L.x = take(sizeof(double) * (size_t)2 * L.Dp);
+  L.nflags = (L.Dp / kGnNB) * (L.Dp / kGnNB) + (L.Dp / kGnNB);
+  L.flags = take(sizeof(int) * (size_t)L.nflags);
   // n- and Ml-dependent arrays last: every offset above depends on (N, M) only, `xc` on
   // (N, M, n), and only the TOTAL depends on how many edges this process accumulates.
   L.xc = take(sizeof(float4) * (size_t)N * n);

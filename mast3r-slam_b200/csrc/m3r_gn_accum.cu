@@ -52,11 +52,13 @@ __device__ __forceinline__ int lower_bound_i64(const int64_t* a, int len, int64_
 
 __global__ void __launch_bounds__(kIdxThreads)
 gn_index_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, int M, int N, int P,
-                int64_t* keys, int* rank, int* ie, int* je, int* row_ptr, int* adj, GnHeader* hdr) {
+                int64_t* keys, int* rank, int* ie, int* je, int* row_ptr, int* adj, int* flags,
+                int nflags, GnHeader* hdr) {
   __shared__ int64_t skeys[kIdxSmemKeys];
   __shared__ int scan[kIdxThreads];
   const int tid = threadIdx.x;
   if (tid == 0) { hdr->done = 0; hdr->chol_fail = 0; hdr->iters = 0; hdr->pad = 0; }
+  for (int t = tid; t < nflags; t += kIdxThreads) flags[t] = 0;
   int64_t* buf = (P <= kIdxSmemKeys) ? skeys : keys;
   const int64_t kMax = 0x7fffffffffffffffLL;
   // 1. sorted keyframe ids  (torch::_unique(cat(ii,jj), sorted), gn_kernels.cu:161-164)
@@ -392,7 +394,7 @@ extern "C" int m3r_gn_prepare(const float* Xs, const float* Cs, const int64_t* i
       ii, jj, num_edges, num_poses, L.P, ws_ptr<int64_t>(workspace, L.keys),
       ws_ptr<int>(workspace, L.rank), ws_ptr<int>(workspace, L.ie), ws_ptr<int>(workspace, L.je),
       ws_ptr<int>(workspace, L.row_ptr), ws_ptr<int>(workspace, L.adj),
-      ws_ptr<GnHeader>(workspace, L.hdr));
+      ws_ptr<int>(workspace, L.flags), L.nflags, ws_ptr<GnHeader>(workspace, L.hdr));
   M3R_TRY(after_launch());
   const size_t count = (size_t)num_poses * n;
   const int grid = (int)((count + 255) / 256 < (size_t)(kNumSMs * 16) ? (count + 255) / 256

@@ -9,76 +9,192 @@
 // fp32->fp16 is innocuous for one + or * of fp16 operands: rn16(float(a) op float(b)) ==
 // the correctly rounded fp16 result == HADD2.RN / HMUL2.RN per lane.  Two candidates are
 // therefore scored at once in the two lanes of half2 registers (mul.rn/add.rn, which
-// ptxas may not fuse into an fma), 2 instructions per 2 MACs instead of the reference's
-// FMUL + F2F + FADD + F2F per MAC.  Scan order (u outer, v inner, dilation_max..1),
-// strict '>' and the fp16-zero initial maximum are kept.
+// ptxas may not fuse into an fma).
+//
+// What bounds this kernel (ncu, profiles/): not HBM.  Per (query, candidate) pair the exact
+// rounding chain needs F HMUL2-lanes + F HADD2-lanes; fp16x2 instructions issue on the
+// fma-heavy pipe only (one warp instruction per 2 cycles per SM sub-partition), and every
+// candidate is a 2F-byte gather through L1 (128 B/clk/SM).  At F = 24, 245 candidates per
+// query both floors are ~12 cycles per (warp, candidate) per SM — the kernel is balanced
+// between the fp16 pipe and the L1 data pipe; everything else (index arithmetic, bounds
+// tests, tie-breaking) is kept off the fma pipe:
+//   * the argmax keeps ONE signed 32-bit key per query, (score_fp16_bits << 16) |
+//     (0xFFFE - scan_index): a signed integer max then realises "strict > in (u outer,
+//     v inner) scan order"  in any evaluation order — negative scores have the
+//     sign bit set and lose against the initial +0, equal scores lose against an
+//     earlier scan index, and a maximum carried over from a previous dilation carries the
+//     tie field 0xFFFF so that no later tie can displace it;
+//   * candidates are therefore visited row-major (v outer) for L1 locality, by 2-D CTA tiles
+//     of 32x8 queries whose windows overlap;
+//   * interior windows (all (2r+1)^2 candidates inside the image) skip every bounds test.
+// Scores must not be NaN (a NaN never wins in the reference; its bit pattern would here).
 #include "m3r_common.cuh"
 
 namespace m3r {
 
-constexpr int kRefineThreads = 128;
+constexpr int kRefTX = 32, kRefTY = 8;
+constexpr int kRefineThreads = kRefTX * kRefTY;
+constexpr int kKeyInvalid = (int)0x80000000;
 
-__device__ __forceinline__ bool inside_image(int u, int v, int W, int H) {
-  return v >= 0 && v < H && u >= 0 && u < W;
-}
-
-// Score two candidates (A in the low lane, B in the high lane) against the query.
-// q2[k] holds (q_k, q_k).  F8 = F/8 uint4 words per descriptor.
+// Scores of two candidates (A -> low lane, B -> high lane) against the packed query
+// q[t] = (q_2t, q_2t+1).  F8 = F/8 uint4 words per descriptor.
 template <int F8>
-__device__ __forceinline__ __half2 score_pair(const uint4* __restrict__ ca,
-                                              const uint4* __restrict__ cb,
-                                              const __half2* q2) {
+__device__ __forceinline__ uint32_t score_pair(const uint4* __restrict__ ca,
+                                               const uint4* __restrict__ cb,
+                                               const uint32_t* q) {
+  uint4 a[F8], b[F8];
+#pragma unroll
+  for (int w = 0; w < F8; w++) { a[w] = __ldg(ca + w); b[w] = __ldg(cb + w); }
   __half2 acc = __float2half2_rn(0.f);
 #pragma unroll
   for (int w = 0; w < F8; w++) {
-    const uint4 a = __ldg(ca + w);
-    const uint4 b = __ldg(cb + w);
-    const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
-    const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
+    const uint32_t aw[4] = {a[w].x, a[w].y, a[w].z, a[w].w};
+    const uint32_t bw[4] = {b[w].x, b[w].y, b[w].z, b[w].w};
 #pragma unroll
     for (int t = 0; t < 4; t++) {
       const uint32_t lo = __byte_perm(aw[t], bw[t], 0x5410);  // (A_2t  , B_2t  )
       const uint32_t hi = __byte_perm(aw[t], bw[t], 0x7632);  // (A_2t+1, B_2t+1)
-      const int k = w * 8 + t * 2;
-      acc = __hadd2_rn(acc, __hmul2_rn(*reinterpret_cast<const __half2*>(&lo), q2[k]));
-      acc = __hadd2_rn(acc, __hmul2_rn(*reinterpret_cast<const __half2*>(&hi), q2[k + 1]));
+      const __half2 qq = *reinterpret_cast<const __half2*>(&q[w * 4 + t]);
+      acc = __hadd2_rn(acc, __hmul2_rn(*reinterpret_cast<const __half2*>(&lo), __low2half2(qq)));
+      acc = __hadd2_rn(acc, __hmul2_rn(*reinterpret_cast<const __half2*>(&hi), __high2half2(qq)));
     }
   }
-  return acc;
+  return *reinterpret_cast<uint32_t*>(&acc);
 }
 
-// Core search for one query.  D11b: descriptor image of this batch element (H,W,F) fp16.
-template <int F8>
-__device__ __forceinline__ void refine_query(const uint16_t* __restrict__ D11b,
-                                             const __half2* q2, int H, int W, int radius,
-                                             int dilation_max, long long& u0, long long& v0) {
-  constexpr int F = F8 * 8;
-  float max_score = 0.f;  // c10::Half() == +0
-  long long u_new = u0, v_new = v0;
-  const int side = 2 * radius + 1;
-  const int cnt = side * side;
-  for (int d = dilation_max; d > 0; d--) {
-    const int rd = radius * d;
-    for (int c = 0; c < cnt; c += 2) {
-      // candidate c -> (i = c / side outer = u, j = c % side inner = v)
-      const int ia = c / side, ja = c - ia * side;
-      const int cbi = c + 1;
-      const int ib = cbi / side, jb = cbi - ib * side;
-      const long long ua = u0 - rd + (long long)ia * d, va = v0 - rd + (long long)ja * d;
-      const long long ub = u0 - rd + (long long)ib * d, vb = v0 - rd + (long long)jb * d;
-      const bool oka = inside_image((int)ua, (int)va, W, H);
-      const bool okb = (cbi < cnt) && inside_image((int)ub, (int)vb, W, H);
-      if (!oka && !okb) continue;
-      const size_t offa = oka ? ((size_t)(int)va * W + (int)ua) * F : 0;
-      const size_t offb = okb ? ((size_t)(int)vb * W + (int)ub) * F : offa;
-      const __half2 s = score_pair<F8>(reinterpret_cast<const uint4*>(D11b + offa),
-                                       reinterpret_cast<const uint4*>(D11b + offb), q2);
-      const float sa = __low2float(s), sb = __high2float(s);
-      if (oka && sa > max_score) { max_score = sa; u_new = ua; v_new = va; }
-      if (okb && sb > max_score) { max_score = sb; u_new = ub; v_new = vb; }
+// key = (score bits << 16) | tie, as a signed int (see the header comment)
+__device__ __forceinline__ int key_lo(uint32_t s2, uint32_t tie) { return (int)__byte_perm(s2, tie, 0x1054); }
+__device__ __forceinline__ int key_hi(uint32_t s2, uint32_t tie) { return (int)__byte_perm(s2, tie, 0x3254); }
+
+// One dilation of the search for one query, window side S = 2R+1 known at compile time.
+// Candidates are visited row-major (c' = j*S + i), two per step; `best` is the running key.
+template <int F8, int R, bool CHECK>
+__device__ __forceinline__ void dilation_rows(const uint16_t* __restrict__ D11b, const uint32_t* q,
+                                              int H, int W, int d, int us, int vs, int& best) {
+  constexpr int S = 2 * R + 1, FB = F8 * 16;  // descriptor bytes
+  const char* base = reinterpret_cast<const char*>(D11b);
+  // byte offsets in wrap-around unsigned arithmetic: every offset that is dereferenced
+  // lies inside the image (< 2^31, checked at the entry point)
+  const unsigned cs = (unsigned)d * FB;               // step between window columns
+  const unsigned rs = (unsigned)d * (unsigned)W * FB; // step between window rows
+  const unsigned org = ((unsigned)vs * (unsigned)W + (unsigned)us) * FB;
+  unsigned um = 0, vm = 0;        // CHECK: validity bit per window column / row
+  if (CHECK) {
+#pragma unroll
+    for (int i = 0; i < S; i++) {
+      um |= (unsigned)((us + i * d) >= 0 && (us + i * d) < W) << i;
+      vm |= (unsigned)((vs + i * d) >= 0 && (vs + i * d) < H) << i;
     }
-    u0 = u_new; v0 = v_new;
   }
+  auto eval2 = [&](int ja, int ia, int jb, int ib, bool have_b) {
+    // scan index of (i, j) is i*S + j (u outer, v inner: matching_kernels.cu:52-53)
+    const uint32_t tie_a = 0xFFFEu - (uint32_t)(ia * S + ja);
+    const uint32_t tie_b = 0xFFFEu - (uint32_t)(ib * S + jb);
+    unsigned off_a = org + (unsigned)ja * rs + (unsigned)ia * cs;
+    unsigned off_b = org + (unsigned)jb * rs + (unsigned)ib * cs;
+    bool ok_a = true, ok_b = have_b;
+    if (CHECK) {
+      ok_a = ((um >> ia) & (vm >> ja) & 1u) != 0;
+      ok_b = have_b && ((um >> ib) & (vm >> jb) & 1u) != 0;
+      if (!ok_a && !ok_b) return;
+      if (!ok_a) off_a = ok_b ? off_b : 0;
+      if (!ok_b) off_b = off_a;
+    } else if (!have_b) {
+      off_b = off_a;
+    }
+    const uint32_t s2 = score_pair<F8>(reinterpret_cast<const uint4*>(base + off_a),
+                                       reinterpret_cast<const uint4*>(base + off_b), q);
+    const int ka = ok_a ? key_lo(s2, tie_a) : kKeyInvalid;
+    const int kb = ok_b ? key_hi(s2, tie_b) : kKeyInvalid;
+    best = max(best, max(ka, kb));
+  };
+  // row pairs (2 rows = 2S candidates = S pairs), then the last row (S odd)
+#pragma unroll 1
+  for (int jp = 0; jp < S / 2; jp++) {
+    const int j0 = 2 * jp;
+#pragma unroll
+    for (int c = 0; c < 2 * S; c += 2) {
+      const int ja = c / S, ia = c % S, jb = (c + 1) / S, ib = (c + 1) % S;  // compile time
+      eval2(j0 + ja, ia, j0 + jb, ib, true);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < S; i += 2) eval2(S - 1, i, S - 1, (i + 1 < S) ? i + 1 : i, i + 1 < S);
+}
+
+// Generic window side (radius != 3): same key logic, runtime loops, scan order.
+template <int F8>
+__device__ __forceinline__ void dilation_generic(const uint16_t* __restrict__ D11b, const uint32_t* q,
+                                                 int H, int W, int radius, int d, int us, int vs,
+                                                 int& best) {
+  constexpr int FB = F8 * 16;
+  const char* base = reinterpret_cast<const char*>(D11b);
+  const int side = 2 * radius + 1;
+  for (int i = 0; i < side; i++) {
+    const int u = us + i * d;
+    if (u < 0 || u >= W) continue;
+    for (int j = 0; j < side; j += 2) {
+      const int va = vs + j * d, vb = va + d;
+      const bool ok_a = va >= 0 && va < H;
+      const bool ok_b = (j + 1 < side) && vb >= 0 && vb < H;
+      if (!ok_a && !ok_b) continue;
+      unsigned off_a = ((unsigned)va * W + u) * FB, off_b = ((unsigned)vb * W + u) * FB;
+      if (!ok_a) off_a = off_b;
+      if (!ok_b) off_b = off_a;
+      const uint32_t s2 = score_pair<F8>(reinterpret_cast<const uint4*>(base + off_a),
+                                         reinterpret_cast<const uint4*>(base + off_b), q);
+      const uint32_t tie = 0xFFFEu - (uint32_t)(i * side + j);
+      const int ka = ok_a ? key_lo(s2, tie) : kKeyInvalid;
+      const int kb = ok_b ? key_hi(s2, tie - 1u) : kKeyInvalid;
+      best = max(best, max(ka, kb));
+    }
+  }
+}
+
+// Whole search for one query: dilation_max..1, each re-centred on the previous winner
+// (matching_kernels.cu:47-77).  q: packed fp16 query; (u0,v0) in/out.
+template <int F8>
+__device__ __forceinline__ void refine_query(const uint16_t* __restrict__ D11b, const uint32_t* q,
+                                             int H, int W, int radius, int dilation_max, int& u0,
+                                             int& v0) {
+  int best = 0x0000FFFF;  // score +0 (c10::Half() == 0), carried
+  const int side = 2 * radius + 1;
+  for (int d = dilation_max; d > 0; d--) {
+    const int us = u0 - radius * d, vs = v0 - radius * d;
+    best |= 0xFFFF;  // the running maximum now predates every candidate of this dilation
+    if (radius == 3) {
+      const bool interior = us >= 0 && us + 6 * d < W && vs >= 0 && vs + 6 * d < H;
+      if (interior) dilation_rows<F8, 3, false>(D11b, q, H, W, d, us, vs, best);
+      else dilation_rows<F8, 3, true>(D11b, q, H, W, d, us, vs, best);
+    } else {
+      dilation_generic<F8>(D11b, q, H, W, radius, d, us, vs, best);
+    }
+    const int tie = best & 0xFFFF;
+    if (tie != 0xFFFF) {
+      const int sidx = 0xFFFE - tie;
+      const int i = sidx / side, j = sidx - i * side;
+      u0 = us + i * d; v0 = vs + j * d;
+    }
+  }
+}
+
+// Query index of this thread.  When the queries form the H x W grid (n == H*W) CTAs are
+// 32x8 pixel tiles so that neighbouring queries' windows share L1 lines; otherwise 1-D.
+__device__ __forceinline__ int query_index(int n, int W, int tiles_x, bool tiled) {
+  if (!tiled) {
+    const int k = blockIdx.x * kRefineThreads + threadIdx.x;
+    return k < n ? k : -1;
+  }
+  const int tx = blockIdx.x % tiles_x, ty = blockIdx.x / tiles_x;
+  const int x = tx * kRefTX + (threadIdx.x & (kRefTX - 1));
+  const int y = ty * kRefTY + (threadIdx.x / kRefTX);
+  return (x < W && y * W + x < n) ? y * W + x : -1;
+}
+
+// p1 coordinates outside int32 cannot be inside the image; clamp them far outside so that
+// 32-bit window arithmetic stays exact (the reference truncates long -> int, H3).
+__device__ __forceinline__ int clamp_coord(long long c) {
+  return c < -(1 << 20) ? -(1 << 20) : (c > (1 << 20) ? (1 << 20) : (int)c);
 }
 
 // Plain form: D21 already fp16, output (u,v) pairs.
@@ -86,28 +202,25 @@ template <int F8>
 __global__ void __launch_bounds__(kRefineThreads)
 refine_f16_kernel(const uint16_t* __restrict__ D11, const uint16_t* __restrict__ D21,
                   const int64_t* __restrict__ p1, int H, int W, int n, int radius,
-                  int dilation_max, int64_t* __restrict__ p1_new) {
+                  int dilation_max, int tiles_x, int tiled, int64_t* __restrict__ p1_new) {
   constexpr int F = F8 * 8;
-  const int k = blockIdx.x * kRefineThreads + threadIdx.x;
-  if (k >= n) return;
+  const int k = query_index(n, W, tiles_x, tiled != 0);
+  if (k < 0) return;
   const size_t bk = (size_t)blockIdx.y * n + k;
-  __half2 q2[F];
+  uint32_t q[F / 2];
   const uint4* qp = reinterpret_cast<const uint4*>(D21 + bk * F);
 #pragma unroll
   for (int w = 0; w < F8; w++) {
     const uint4 qv = ld_stream_u4(qp + w);
-    const uint32_t qw[4] = {qv.x, qv.y, qv.z, qv.w};
-#pragma unroll
-    for (int t = 0; t < 4; t++) {
-      const __half2 h = *reinterpret_cast<const __half2*>(&qw[t]);
-      q2[w * 8 + t * 2] = __low2half2(h);
-      q2[w * 8 + t * 2 + 1] = __high2half2(h);
-    }
+    q[w * 4 + 0] = qv.x; q[w * 4 + 1] = qv.y; q[w * 4 + 2] = qv.z; q[w * 4 + 3] = qv.w;
   }
   const longlong2 p = __ldg(reinterpret_cast<const longlong2*>(p1) + bk);
-  long long u0 = p.x, v0 = p.y;
-  refine_query<F8>(D11 + (size_t)blockIdx.y * H * W * F, q2, H, W, radius, dilation_max, u0, v0);
-  longlong2 o; o.x = u0; o.y = v0;
+  int u0 = clamp_coord(p.x), v0 = clamp_coord(p.y);
+  const int u_in = u0, v_in = v0;
+  refine_query<F8>(D11 + (size_t)blockIdx.y * H * W * F, q, H, W, radius, dilation_max, u0, v0);
+  longlong2 o;  // unchanged coordinates are returned as given (even outside int32)
+  o.x = (u0 == u_in) ? p.x : (long long)u0;
+  o.y = (v0 == v_in) ? p.y : (long long)v0;
   reinterpret_cast<longlong2*>(p1_new)[bk] = o;
 }
 
@@ -116,35 +229,37 @@ template <int F8>
 __global__ void __launch_bounds__(kRefineThreads)
 refine_fused_kernel(const uint16_t* __restrict__ D11h, const float* __restrict__ D21,
                     const int64_t* __restrict__ p1, int H, int W, int radius,
-                    int dilation_max, int64_t* __restrict__ idx_out) {
+                    int dilation_max, int tiles_x, int64_t* __restrict__ idx_out) {
   constexpr int F = F8 * 8;
   const int n = H * W;
-  const int k = blockIdx.x * kRefineThreads + threadIdx.x;
-  if (k >= n) return;
+  const int k = query_index(n, W, tiles_x, true);
+  if (k < 0) return;
   const size_t bk = (size_t)blockIdx.y * n + k;
-  __half2 q2[F];
+  uint32_t q[F / 2];
   const float4* qp = reinterpret_cast<const float4*>(D21 + bk * F);
 #pragma unroll
   for (int w = 0; w < F / 4; w++) {
     const float4 qv = ld_stream_f4(qp + w);
-    q2[w * 4 + 0] = __half2half2(__float2half_rn(qv.x));
-    q2[w * 4 + 1] = __half2half2(__float2half_rn(qv.y));
-    q2[w * 4 + 2] = __half2half2(__float2half_rn(qv.z));
-    q2[w * 4 + 3] = __half2half2(__float2half_rn(qv.w));
+    const __half2 h0 = __floats2half2_rn(qv.x, qv.y), h1 = __floats2half2_rn(qv.z, qv.w);
+    q[w * 2 + 0] = *reinterpret_cast<const uint32_t*>(&h0);
+    q[w * 2 + 1] = *reinterpret_cast<const uint32_t*>(&h1);
   }
   const longlong2 p = __ldg(reinterpret_cast<const longlong2*>(p1) + bk);
-  long long u0 = p.x, v0 = p.y;
+  int u0 = clamp_coord(p.x), v0 = clamp_coord(p.y);
+  const int u_in = u0, v_in = v0;
   if (radius > 0)
-    refine_query<F8>(D11h + (size_t)blockIdx.y * n * F, q2, H, W, radius, dilation_max, u0, v0);
-  idx_out[bk] = u0 + (long long)W * v0;  // pixel_to_lin, matching.py:13-15
+    refine_query<F8>(D11h + (size_t)blockIdx.y * n * F, q, H, W, radius, dilation_max, u0, v0);
+  const long long uo = (u0 == u_in) ? p.x : (long long)u0;
+  const long long vo = (v0 == v_in) ? p.y : (long long)v0;
+  idx_out[bk] = uo + (long long)W * vo;  // pixel_to_lin, matching.py:13-15
 }
 
 // <float> instantiation of the reference: sequential fp32 accumulate (FFMA), max from FLT_MIN.
-__global__ void __launch_bounds__(kRefineThreads)
+__global__ void __launch_bounds__(128)
 refine_f32_kernel(const float* __restrict__ D11, const float* __restrict__ D21,
                   const int64_t* __restrict__ p1, int H, int W, int n, int F, int radius,
                   int dilation_max, int64_t* __restrict__ p1_new) {
-  const int k = blockIdx.x * kRefineThreads + threadIdx.x;
+  const int k = blockIdx.x * 128 + threadIdx.x;
   if (k >= n) return;
   const size_t bk = (size_t)blockIdx.y * n + k;
   const float* q = D21 + bk * F;
@@ -158,7 +273,7 @@ refine_f32_kernel(const float* __restrict__ D11, const float* __restrict__ D21,
     for (int i = 0; i < diam; i += d) {
       for (int j = 0; j < diam; j += d) {
         const long long u = u0 - rd + i, v = v0 - rd + j;
-        if (inside_image((int)u, (int)v, W, H)) {
+        if ((int)v >= 0 && (int)v < H && (int)u >= 0 && (int)u < W) {
           const float* c = D11b + ((size_t)(int)v * W + (int)u) * F;
           float score = 0.f;
           for (int t = 0; t < F; t++) score = fmaf(__ldg(q + t), __ldg(c + t), score);
@@ -185,18 +300,27 @@ using namespace m3r;
     default: return M3R_EINVAL;                      \
   }
 
+static bool refine_args_ok(int b, int H, int W, int F, int radius) {
+  if (b < 0 || H <= 0 || W <= 0 || F <= 0 || (F % 8) != 0 || F > 32 || radius < 0 || radius > 100 ||
+      b > 65535)
+    return false;
+  return (long long)H * W * F * 2 < (1LL << 31);  // 32-bit byte offsets inside one image
+}
+
 extern "C" int m3r_refine_matches_f16(const uint16_t* D11, const uint16_t* D21,
                                       const int64_t* p1, int b, int H, int W, int n, int F,
                                       int radius, int dilation_max, int64_t* p1_new,
                                       m3r_stream_t stream) {
-  if (b < 0 || n < 0 || H <= 0 || W <= 0 || F <= 0 || (F % 8) != 0 || F > 32 || radius < 0 ||
-      b > 65535)
-    return M3R_EINVAL;
+  if (!refine_args_ok(b, H, W, F, radius) || n < 0) return M3R_EINVAL;
   if (b == 0 || n == 0) return M3R_OK;
   if (!D11 || !D21 || !p1 || !p1_new) return M3R_EINVAL;
-  dim3 grid((n + kRefineThreads - 1) / kRefineThreads, b);
+  const int tiled = (n == H * W) ? 1 : 0;
+  const int tiles_x = (W + kRefTX - 1) / kRefTX;
+  const int ctas = tiled ? tiles_x * ((H + kRefTY - 1) / kRefTY)
+                         : (n + kRefineThreads - 1) / kRefineThreads;
+  dim3 grid(ctas, b);
   M3R_DISPATCH_F8(F / 8, (refine_f16_kernel<F8><<<grid, kRefineThreads, 0, as_stream(stream)>>>(
-                             D11, D21, p1, H, W, n, radius, dilation_max, p1_new)));
+                             D11, D21, p1, H, W, n, radius, dilation_max, tiles_x, tiled, p1_new)));
   return after_launch();
 }
 
@@ -204,14 +328,13 @@ extern "C" int m3r_match_refine_fused(const uint16_t* D11h, const float* D21,
                                       const int64_t* p1, int b, int H, int W, int F, int radius,
                                       int dilation_max, int64_t* idx_1_to_2,
                                       m3r_stream_t stream) {
-  if (b < 0 || H <= 0 || W <= 0 || F <= 0 || (F % 8) != 0 || F > 32 || radius < 0 || b > 65535)
-    return M3R_EINVAL;
+  if (!refine_args_ok(b, H, W, F, radius)) return M3R_EINVAL;
   if (b == 0) return M3R_OK;
   if (!D11h || !D21 || !p1 || !idx_1_to_2) return M3R_EINVAL;
-  const int n = H * W;
-  dim3 grid((n + kRefineThreads - 1) / kRefineThreads, b);
+  const int tiles_x = (W + kRefTX - 1) / kRefTX;
+  dim3 grid(tiles_x * ((H + kRefTY - 1) / kRefTY), b);
   M3R_DISPATCH_F8(F / 8, (refine_fused_kernel<F8><<<grid, kRefineThreads, 0, as_stream(stream)>>>(
-                             D11h, D21, p1, H, W, radius, dilation_max, idx_1_to_2)));
+                             D11h, D21, p1, H, W, radius, dilation_max, tiles_x, idx_1_to_2)));
   return after_launch();
 }
 
@@ -221,8 +344,8 @@ extern "C" int m3r_refine_matches_f32(const float* D11, const float* D21, const 
   if (b < 0 || n < 0 || H <= 0 || W <= 0 || F <= 0 || radius < 0 || b > 65535) return M3R_EINVAL;
   if (b == 0 || n == 0) return M3R_OK;
   if (!D11 || !D21 || !p1 || !p1_new) return M3R_EINVAL;
-  dim3 grid((n + kRefineThreads - 1) / kRefineThreads, b);
-  refine_f32_kernel<<<grid, kRefineThreads, 0, as_stream(stream)>>>(D11, D21, p1, H, W, n, F,
-                                                                    radius, dilation_max, p1_new);
+  dim3 grid((n + 127) / 128, b);
+  refine_f32_kernel<<<grid, 128, 0, as_stream(stream)>>>(D11, D21, p1, H, W, n, F, radius,
+                                                         dilation_max, p1_new);
   return after_launch();
 }
