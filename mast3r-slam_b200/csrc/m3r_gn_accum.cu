@@ -219,6 +219,41 @@ __device__ __forceinline__ void point_terms(const GnDev& prm, const float* R, co
 constexpr int kAccThreads = 256;
 constexpr int kAccUnroll = 4;
 
+// T_ij = T_i^-1 T_j in fp32 like the reference (relSim3), then as a 3x4 affine map.
+__device__ __forceinline__ void edge_transform(const float* __restrict__ Twc, int ix, int jx,
+                                               float* R, float* t) {
+  float Ti[8], Tj[8], qij[4], sij;
+#pragma unroll
+  for (int k = 0; k < 8; k++) { Ti[k] = __ldg(Twc + ix * 8 + k); Tj[k] = __ldg(Twc + jx * 8 + k); }
+  rel_sim3<float>(Ti, Ti + 3, Ti[7], Tj, Tj + 3, Tj[7], t, qij, sij);
+#pragma unroll
+  for (int c = 0; c < 3; c++) {
+    float ev[3] = {0.f, 0.f, 0.f}, col[3];
+    ev[c] = 1.f;
+    act_so3<float>(qij, ev, col);
+    R[0 + c] = sij * col[0]; R[3 + c] = sij * col[1]; R[6 + c] = sij * col[2];
+  }
+}
+
+// two-stage fixed-order reduction: warp shuffle tree, then 8 warps summed in order
+__device__ __forceinline__ void block_reduce_store(const float* h, const float* g,
+                                                   float* __restrict__ dst) {
+  __shared__ float red[kAccThreads / 32][kGnPartStride];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 28; k++) { const float v = warp_sum(h[k]); if (lane == 0) red[warp][k] = v; }
+#pragma unroll
+  for (int k = 0; k < 7; k++) { const float v = warp_sum(g[k]); if (lane == 0) red[warp][28 + k] = v; }
+  __syncthreads();
+  if (threadIdx.x < 35) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < kAccThreads / 32; w++) s += red[w][threadIdx.x];
+    dst[threadIdx.x] = s;
+  }
+}
+
+// Generic accumulation kernel (any n, any alignment): register-staged loads.
 template <int MODE>
 __global__ void __launch_bounds__(kAccThreads, 2)
 gn_accum_kernel(const GnDev prm, const float* __restrict__ Twc, const float4* __restrict__ xc,
@@ -230,21 +265,8 @@ gn_accum_kernel(const GnDev prm, const float* __restrict__ Twc, const float4* __
   const int el = blockIdx.y, split = blockIdx.x;
   const int e = edge_begin + el;
   const int ix = ie[e], jx = je[e];
-  // T_ij = T_i^-1 T_j in fp32 like the reference (relSim3), then as a 3x4 affine map.
   float R[9], t[3];
-  {
-    float Ti[8], Tj[8], qij[4], sij;
-#pragma unroll
-    for (int k = 0; k < 8; k++) { Ti[k] = __ldg(Twc + ix * 8 + k); Tj[k] = __ldg(Twc + jx * 8 + k); }
-    rel_sim3<float>(Ti, Ti + 3, Ti[7], Tj, Tj + 3, Tj[7], t, qij, sij);
-#pragma unroll
-    for (int c = 0; c < 3; c++) {
-      float ev[3] = {0.f, 0.f, 0.f}, col[3];
-      ev[c] = 1.f;
-      act_so3<float>(qij, ev, col);
-      R[0 + c] = sij * col[0]; R[3 + c] = sij * col[1]; R[6 + c] = sij * col[2];
-    }
-  }
+  edge_transform(Twc, ix, jx, R, t);
   float h[28], g[7];
 #pragma unroll
   for (int k = 0; k < 28; k++) h[k] = 0.f;
@@ -280,21 +302,134 @@ gn_accum_kernel(const GnDev prm, const float* __restrict__ Twc, const float4* __
     for (int u = 0; u < kAccUnroll; u++)
       point_terms<MODE>(prm, R, t, xi[u], xj[u], ind[u], qv[u], vm[u], h, g);
   }
+  block_reduce_store(h, g, part + ((size_t)el * S + split) * kGnPartStride);
+}
 
-  // two-stage fixed-order reduction: warp shuffle tree, then 8 warps summed in order
-  __shared__ float red[kAccThreads / 32][kGnPartStride];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-  for (int k = 0; k < 28; k++) { const float v = warp_sum(h[k]); if (lane == 0) red[warp][k] = v; }
-#pragma unroll
-  for (int k = 0; k < 7; k++) { const float v = warp_sum(g[k]); if (lane == 0) red[warp][28 + k] = v; }
-  __syncthreads();
-  if (threadIdx.x < 35) {
-    float s = 0.f;
-#pragma unroll
-    for (int w = 0; w < kAccThreads / 32; w++) s += red[w][threadIdx.x];
-    part[((size_t)el * S + split) * kGnPartStride + threadIdx.x] = s;
+// ------------------------------------------------------------------------------------
+// Streaming form of the same pass (used whenever n % 16 == 0 and the streams are 16-B
+// aligned): the four per-edge streams of a 1024-point stage — Xj/Cj (16 B), idx (8 B),
+// Q (4 B), valid (1 B) = 29 B/point — are fetched by the bulk-copy engine
+// (cp.async.bulk global -> shared, completion on an mbarrier) three stages ahead, so HBM
+// stays busy independently of the register file; only the irregular Xi/Ci gather is a
+// register load, issued one stage ahead of its use.  Point -> thread mapping, arithmetic and
+// reduction order are identical to gn_accum_kernel, so both produce the same bits.
+// ------------------------------------------------------------------------------------
+constexpr int kStagePts = kAccThreads * kAccUnroll;  // 1024
+constexpr int kStages = 3;
+constexpr int kOffIdx = kStagePts * 16, kOffQ = kOffIdx + kStagePts * 8, kOffVm = kOffQ + kStagePts * 4;
+constexpr int kStageBytes = kOffVm + kStagePts;      // 29 KB
+constexpr int kAccSmemBytes = kStages * kStageBytes;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+                 "selp.u32 %0, 1, 0, p;\n}" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kAccThreads, 2)
+gn_accum_stream_kernel(const GnDev prm, const float* __restrict__ Twc, const float4* __restrict__ xc,
+                       const int* __restrict__ ie, const int* __restrict__ je,
+                       const int64_t* __restrict__ idx, const uint8_t* __restrict__ vmatch,
+                       const float* __restrict__ Q, int n, int edge_begin, int chunk, int S,
+                       float* __restrict__ part, const GnHeader* __restrict__ hdr) {
+  extern __shared__ __align__(128) unsigned char stage_mem[];
+  __shared__ uint64_t full[kStages];
+  if (hdr->done) return;
+  const int tid = threadIdx.x;
+  const int el = blockIdx.y, split = blockIdx.x;
+  const int e = edge_begin + el;
+  const int ix = ie[e], jx = je[e];
+  const float4* xi_base = xc + (size_t)ix * n;
+  const float4* xj_base = xc + (size_t)jx * n;
+  const int64_t* idx_e = idx + (size_t)el * n;
+  const uint8_t* vm_e = vmatch + (size_t)el * n;
+  const float* q_e = Q + (size_t)el * n;
+  const int p_begin = split * chunk;
+  const int p_end = min(n, p_begin + chunk);
+  const int T = (p_end - p_begin + kStagePts - 1) / kStagePts;
+
+  auto issue = [&](int st) {  // one thread: arm the barrier, start the four copies of stage st
+    const int p0 = p_begin + st * kStagePts;
+    const uint32_t cnt = (uint32_t)min(kStagePts, p_end - p0);
+    unsigned char* buf = stage_mem + (st % kStages) * kStageBytes;
+    uint64_t* bar = &full[st % kStages];
+    mbar_expect_tx(bar, cnt * 29u);
+    bulk_g2s(buf, xj_base + p0, cnt * 16u, bar);
+    bulk_g2s(buf + kOffIdx, idx_e + p0, cnt * 8u, bar);
+    bulk_g2s(buf + kOffQ, q_e + p0, cnt * 4u, bar);
+    bulk_g2s(buf + kOffVm, vm_e + p0, cnt, bar);
+  };
+  if (tid == 0) {
+    for (int s = 0; s < kStages; s++) mbar_init(&full[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    for (int st = 0; st < kStages && st < T; st++) issue(st);
   }
+  float R[9], t[3];
+  edge_transform(Twc, ix, jx, R, t);
+  float h[28], g[7];
+#pragma unroll
+  for (int k = 0; k < 28; k++) h[k] = 0.f;
+#pragma unroll
+  for (int k = 0; k < 7; k++) g[k] = 0.f;
+  __syncthreads();  // barriers initialised
+
+  // slot of this thread's u-th point inside a stage, -1 when past the end of the split
+  auto slot_of = [&](int st, int u) {
+    const int sl = u * kAccThreads + tid;
+    return (p_begin + st * kStagePts + sl < p_end) ? sl : -1;
+  };
+  float4 xi_nxt[kAccUnroll];
+  int ind_nxt[kAccUnroll];  // gathered pixel (0 for invalid matches, gn_kernels.cu:913-914)
+  auto gather = [&](int st) {
+    const unsigned char* buf = stage_mem + (st % kStages) * kStageBytes;
+#pragma unroll
+    for (int u = 0; u < kAccUnroll; u++) {
+      const int sl = slot_of(st, u);
+      const bool vm = sl >= 0 && buf[kOffVm + (sl < 0 ? 0 : sl)] != 0;
+      ind_nxt[u] = vm ? (int)reinterpret_cast<const long long*>(buf + kOffIdx)[sl] : 0;
+      xi_nxt[u] = __ldg(xi_base + ind_nxt[u]);
+    }
+  };
+  mbar_wait(&full[0], 0);
+  gather(0);
+  for (int it = 0; it < T; it++) {
+    float4 xi[kAccUnroll];
+    int ind[kAccUnroll];
+#pragma unroll
+    for (int u = 0; u < kAccUnroll; u++) { xi[u] = xi_nxt[u]; ind[u] = ind_nxt[u]; }
+    if (it + 1 < T) {
+      mbar_wait(&full[(it + 1) % kStages], ((it + 1) / kStages) & 1);
+      gather(it + 1);
+    }
+    const unsigned char* buf = stage_mem + (it % kStages) * kStageBytes;
+#pragma unroll
+    for (int u = 0; u < kAccUnroll; u++) {
+      const int sl = slot_of(it, u);
+      const int s0 = sl < 0 ? 0 : sl;  // past-the-end lanes re-read slot 0 with weight 0
+      const bool vm = sl >= 0 && buf[kOffVm + s0] != 0;
+      const float qv = sl >= 0 ? reinterpret_cast<const float*>(buf + kOffQ)[s0] : -3.0e38f;
+      const float4 xj = reinterpret_cast<const float4*>(buf)[s0];
+      point_terms<MODE>(prm, R, t, xi[u], xj, (long long)ind[u], qv, vm, h, g);
+    }
+    __syncthreads();  // every thread is done with stage `it`: its buffer may be refilled
+    if (tid == 0 && it + kStages < T) issue(it + kStages);
+  }
+  block_reduce_store(h, g, part + ((size_t)el * S + split) * kGnPartStride);
 }
 
 // Per edge: sum the S partials (fp64, fixed order), apply the adjoint of T_i once:
@@ -422,11 +557,29 @@ extern "C" int m3r_gn_accumulate(const m3r_gn_params* prm, const float* Twc,
   const GnDev d = make_dev_params(prm);
   const GnHeader* hdr = ws_ptr<GnHeader>(workspace, L.hdr);
   dim3 grid(L.S, edge_count);
+  // streaming (bulk-copy) form when every stage of every stream is 16-B aligned
+  const bool stream_ok = (n % 16 == 0) && ((uintptr_t)idx_ii2jj % 16 == 0) &&
+                         ((uintptr_t)valid_match % 16 == 0) && ((uintptr_t)Q % 16 == 0);
+  if (stream_ok) {  // > 48 KB of dynamic shared memory is an opt-in, per device
+    const void* fn = prm->mode == M3R_GN_RAYS    ? (const void*)gn_accum_stream_kernel<M3R_GN_RAYS>
+                     : prm->mode == M3R_GN_CALIB ? (const void*)gn_accum_stream_kernel<M3R_GN_CALIB>
+                                                 : (const void*)gn_accum_stream_kernel<M3R_GN_POINTS>;
+    M3R_TRY(check_cuda(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            kAccSmemBytes)));
+  }
 #define M3R_ACC(MODE)                                                                          \
-  gn_accum_kernel<MODE><<<grid, kAccThreads, 0, st>>>(                                         \
-      d, Twc, ws_ptr<float4>(workspace, L.xc), ws_ptr<int>(workspace, L.ie),                   \
-      ws_ptr<int>(workspace, L.je), idx_ii2jj, valid_match, Q, n, edge_begin, L.chunk, L.S,    \
-      ws_ptr<float>(workspace, L.part), hdr)
+  do {                                                                                         \
+    if (stream_ok)                                                                             \
+      gn_accum_stream_kernel<MODE><<<grid, kAccThreads, kAccSmemBytes, st>>>(                  \
+          d, Twc, ws_ptr<float4>(workspace, L.xc), ws_ptr<int>(workspace, L.ie),               \
+          ws_ptr<int>(workspace, L.je), idx_ii2jj, valid_match, Q, n, edge_begin, L.chunk,     \
+          L.S, ws_ptr<float>(workspace, L.part), hdr);                                         \
+    else                                                                                       \
+      gn_accum_kernel<MODE><<<grid, kAccThreads, 0, st>>>(                                     \
+          d, Twc, ws_ptr<float4>(workspace, L.xc), ws_ptr<int>(workspace, L.ie),               \
+          ws_ptr<int>(workspace, L.je), idx_ii2jj, valid_match, Q, n, edge_begin, L.chunk,     \
+          L.S, ws_ptr<float>(workspace, L.part), hdr);                                         \
+  } while (0)
   switch (prm->mode) {
     case M3R_GN_RAYS: M3R_ACC(M3R_GN_RAYS); break;
     case M3R_GN_CALIB: M3R_ACC(M3R_GN_CALIB); break;

@@ -79,3 +79,323 @@ gn_assemble_kernel(const double* __restrict__ blocks, const int* __restrict__ ie
   }
 }
 
+
+// ---------------------------------------------------------------------------------
+// Tile-dataflow Cholesky (left-looking), NB = 32, one 64-thread CTA per tile task.
+// ---------------------------------------------------------------------------------
+constexpr int kCholThreads = 64;
+
+__device__ __forceinline__ int ld_acquire(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release(int* p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// All threads of the CTA return once *f == epoch (written by another CTA of this launch;
+// the cooperative launch guarantees that CTA is resident, so the spin terminates).
+__device__ __forceinline__ void wait_flag(const int* f, int epoch) {
+  if (threadIdx.x == 0) {
+    while (ld_acquire(f) != epoch) __nanosleep(32);
+  }
+  __syncthreads();
+}
+// Publish: every thread's global writes so far become visible to whoever acquires *f.
+__device__ __forceinline__ void post_flag(int* f, int epoch) {
+  __syncthreads();
+  if (threadIdx.x == 0) { __threadfence(); st_release(f, epoch); }
+}
+
+struct CholArgs {
+  double* A; int Dp, D, nb;
+  int* flags;      // [nb*nb] tile (i,j) ready, then [nb] x block ready
+  double* x;       // [Dp] solution of the normal equations (before the sign flip)
+  float* Twc; float* dx; int N; float delta_thresh;
+  GnHeader* hdr;
+};
+
+// global tile (bi,bj) -> shared [32][33], L2-coherent loads (tiles are written by other SMs)
+__device__ __forceinline__ void load_tile(const double* __restrict__ A, int Dp, int bi, int bj,
+                                          double (*s)[NB + 1]) {
+  const double* src = A + (size_t)bi * NB * Dp + (size_t)bj * NB;
+  for (int idx = threadIdx.x; idx < NB * NB / 2; idx += kCholThreads) {
+    const int r = idx / (NB / 2), c2 = (idx % (NB / 2)) * 2;
+    const double2 v = __ldcg(reinterpret_cast<const double2*>(src + (size_t)r * Dp + c2));
+    s[r][c2] = v.x; s[r][c2 + 1] = v.y;
+  }
+}
+
+// In-place Cholesky of the 32x32 tile in `s` by warp 0 (lane r owns row r in registers).
+// Rows whose global index is >= D (augmented rhs row, padding) take pivot 1.
+__device__ __forceinline__ void potrf_tile(double (*s)[NB + 1], double* col, int g0, int D,
+                                           GnHeader* hdr) {
+  const int r = threadIdx.x;
+  if (r < NB) {
+    double a[NB];
+#pragma unroll
+    for (int c = 0; c < NB; c++) a[c] = s[r][c];
+#pragma unroll
+    for (int c = 0; c < NB; c++) {
+      const double d = __shfl_sync(0xffffffffu, a[c], c);
+      double p;
+      if (g0 + c >= D) p = 1.0;
+      else if (d > 0.0) p = sqrt(d);
+      else { p = 1.0; if (r == 0) hdr->chol_fail = 1; }
+      const double l = (r == c) ? p : a[c] / p;
+      a[c] = l;
+      col[r] = l;
+      __syncwarp();
+#pragma unroll
+      for (int c2 = c + 1; c2 < NB; c2++)
+        if (r >= c2) a[c2] = fma(-l, col[c2], a[c2]);
+      __syncwarp();
+    }
+#pragma unroll
+    for (int c = 0; c < NB; c++) s[r][c] = (c <= r) ? a[c] : 0.0;
+  }
+}
+
+// X <- X * Ljj^-T for the 32x32 tile X in `sx` (lane r owns row r), Ljj in `sl`.
+__device__ __forceinline__ void trsm_tile(double (*sx)[NB + 1], const double (*sl)[NB + 1],
+                                          double* dinv) {
+  const int r = threadIdx.x;
+  if (r < NB) {
+    dinv[r] = 1.0 / sl[r][r];
+    __syncwarp();
+    double a[NB];
+#pragma unroll
+    for (int c = 0; c < NB; c++) a[c] = sx[r][c];
+#pragma unroll
+    for (int c = 0; c < NB; c++) {
+      const double xv = a[c] * dinv[c];
+      a[c] = xv;
+#pragma unroll
+      for (int c2 = c + 1; c2 < NB; c2++) a[c2] = fma(-xv, sl[c2][c], a[c2]);
+    }
+#pragma unroll
+    for (int c = 0; c < NB; c++) sx[r][c] = a[c];
+  }
+}
+
+// Tile (i,j), i >= j:  A_ij <- (A_ij - sum_{k<j} L_ik L_jk^T) [chol | * L_jj^-T], then flag it.
+__device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, int epoch,
+                                               double (*sA)[NB + 1], double (*sB)[NB + 1],
+                                               double* sv) {
+  const int tid = threadIdx.x;
+  const int ty = tid >> 3, tx = tid & 7;  // 4x4 micro-tile: rows ty+8x, cols tx+8y
+  double acc[4][4];
+#pragma unroll
+  for (int x = 0; x < 4; x++)
+#pragma unroll
+    for (int y = 0; y < 4; y++) acc[x][y] = 0.0;
+  for (int k = 0; k < j; k++) {
+    wait_flag(a.flags + i * a.nb + k, epoch);
+    if (i != j) wait_flag(a.flags + j * a.nb + k, epoch);
+    load_tile(a.A, a.Dp, i, k, sA);
+    if (i != j) load_tile(a.A, a.Dp, j, k, sB);
+    __syncthreads();
+    const double (*sR)[NB + 1] = (i != j) ? sB : sA;
+#pragma unroll 8
+    for (int m = 0; m < NB; m++) {
+      double li[4], lj[4];
+#pragma unroll
+      for (int x = 0; x < 4; x++) { li[x] = sA[ty + 8 * x][m]; lj[x] = sR[tx + 8 * x][m]; }
+#pragma unroll
+      for (int x = 0; x < 4; x++)
+#pragma unroll
+        for (int y = 0; y < 4; y++) acc[x][y] = fma(li[x], lj[y], acc[x][y]);
+    }
+    __syncthreads();
+  }
+  // own tile (assembled by the previous launch; nobody else touches it before the flag)
+  double* dst = a.A + (size_t)i * NB * a.Dp + (size_t)j * NB;
+#pragma unroll
+  for (int x = 0; x < 4; x++)
+#pragma unroll
+    for (int y = 0; y < 4; y++) {
+      const int r = ty + 8 * x, c = tx + 8 * y;
+      sA[r][c] = __ldcg(dst + (size_t)r * a.Dp + c) - acc[x][y];
+    }
+  __syncthreads();
+  if (i == j) {
+    potrf_tile(sA, sv, j * NB, a.D, a.hdr);
+  } else {
+    wait_flag(a.flags + j * a.nb + j, epoch);
+    load_tile(a.A, a.Dp, j, j, sB);
+    __syncthreads();
+    trsm_tile(sA, sB, sv);
+  }
+  __syncthreads();
+  for (int idx = tid; idx < NB * NB; idx += kCholThreads) {
+    const int r = idx / NB, c = idx % NB;
+    dst[(size_t)r * a.Dp + c] = sA[r][c];
+  }
+  post_flag(a.flags + i * a.nb + j, epoch);
+}
+
+// Back substitution for block column c (L^T x = y, y^T = row D of L):
+//   x_c = L_cc^-T ( y_c - sum_{m>c} L_mc^T x_m ),  entries with global index >= D are 0.
+__device__ __forceinline__ void chol_back_task(const CholArgs& a, int c, int epoch,
+                                               double (*sA)[NB + 1], double* sx, double* sred) {
+  const int tid = threadIdx.x, t = tid & 31, half = tid >> 5;
+  int* xflags = a.flags + a.nb * a.nb;
+  wait_flag(a.flags + (a.nb - 1) * a.nb + c, epoch);  // row D of L (and, transitively, column c)
+  double s = 0.0;
+  for (int m = a.nb - 1; m > c; m--) {
+    wait_flag(xflags + m, epoch);
+    if (tid < NB) sx[tid] = __ldcg(a.x + m * NB + tid);
+    __syncthreads();
+    const double* Lmc = a.A + (size_t)m * NB * a.Dp + (size_t)c * NB;
+#pragma unroll 4
+    for (int r = half * 16; r < half * 16 + 16; r++)
+      s = fma(__ldcg(Lmc + (size_t)r * a.Dp + t), sx[r], s);
+    __syncthreads();
+  }
+  if (half == 1) sred[t] = s;
+  load_tile(a.A, a.Dp, c, c, sA);
+  __syncthreads();
+  if (tid < NB) {
+    const int g = c * NB + t;
+    double rhs = (g < a.D) ? __ldcg(a.A + (size_t)a.D * a.Dp + g) - (s + sred[t]) : 0.0;
+    const double dinv = 1.0 / sA[t][t];
+    double xo = 0.0;
+#pragma unroll
+    for (int k = NB - 1; k >= 0; k--) {
+      double xk = __shfl_sync(0xffffffffu, rhs * dinv, k);
+      if (c * NB + k >= a.D) xk = 0.0;
+      if (t == k) xo = xk;
+      if (t < k) rhs = fma(-sA[k][t], xk, rhs);
+    }
+    a.x[g] = xo;
+  }
+  post_flag(xflags + c, epoch);
+}
+
+// dx = -x (zeros on failure), retract, |dx| test  (gn_kernels.cu:1209-1222) — one CTA.
+__device__ __forceinline__ void gn_update_block(float* __restrict__ Twc, const double* __restrict__ x,
+                                                int N, int D, float delta_thresh,
+                                                float* __restrict__ dx, GnHeader* hdr, float* red) {
+  const int nthr = blockDim.x, tid = threadIdx.x;
+  const bool fail = *reinterpret_cast<volatile int*>(&hdr->chol_fail) != 0;
+  float ss = 0.f;
+  for (int i = tid; i < D; i += nthr) {
+    const float v = fail ? 0.f : (float)(-__ldcg(x + i));
+    dx[i] = v;
+    ss += v * v;
+  }
+  __syncthreads();  // dx visible to the retraction below (same CTA)
+  for (int p = 1 + tid; p < N; p += nthr) {
+    float pose[8], xi[7];
+#pragma unroll
+    for (int m = 0; m < 8; m++) pose[m] = Twc[p * 8 + m];
+#pragma unroll
+    for (int m = 0; m < 7; m++) xi[m] = dx[(p - 1) * 7 + m];
+    retr_sim3_f(xi, pose);
+#pragma unroll
+    for (int m = 0; m < 8; m++) Twc[p * 8 + m] = pose[m];
+  }
+  ss = warp_sum(ss);
+  if ((tid & 31) == 0) red[tid >> 5] = ss;
+  __syncthreads();
+  if (tid == 0) {
+    float tot = 0.f;
+    for (int w = 0; w < (nthr + 31) / 32; w++) tot += red[w];
+    hdr->iters += 1;
+    if (sqrtf(tot) < delta_thresh) hdr->done = 1;
+  }
+}
+
+__global__ void __launch_bounds__(kCholThreads)
+chol_dataflow_kernel(const CholArgs a) {
+  if (a.hdr->done) return;
+  __shared__ double sA[NB][NB + 1];
+  __shared__ double sB[NB][NB + 1];
+  __shared__ double sv[NB], sred[NB];
+  __shared__ float red[kCholThreads / 32];
+  const int epoch = a.hdr->iters + 1;
+  const int G = gridDim.x, cta = blockIdx.x;
+  // tiles in column-major order; every dependency of a tile precedes it in this order and
+  // every CTA walks its tiles in this order, so the earliest unfinished tile can always run
+  int t = 0;
+  for (int j = 0; j < a.nb; j++)
+    for (int i = j; i < a.nb; i++, t++)
+      if (t % G == cta) chol_tile_task(a, i, j, epoch, sA, sB, sv);
+  // block columns of the back substitution, last to first (all after every tile)
+  for (int c = a.nb - 1; c >= 0; c--)
+    if (c % G == cta) {
+      chol_back_task(a, c, epoch, sA, sv, sred);
+      if (c == 0) {  // x complete: this CTA finishes the iteration
+        __syncthreads();
+        gn_update_block(a.Twc, a.x, a.N, a.D, a.delta_thresh, a.dx, a.hdr, red);
+      }
+    }
+}
+
+// standalone retraction (m3r_pose_retr)
+__global__ void pose_retr_kernel(float* __restrict__ poses, const float* __restrict__ dx,
+                                 int num_poses, int num_fix) {
+  const int p = num_fix + blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= num_poses) return;
+  float pose[8], xi[7];
+#pragma unroll
+  for (int m = 0; m < 8; m++) pose[m] = poses[p * 8 + m];
+#pragma unroll
+  for (int m = 0; m < 7; m++) xi[m] = dx[(p - num_fix) * 7 + m];
+  retr_sim3_f(xi, pose);
+#pragma unroll
+  for (int m = 0; m < 8; m++) poses[p * 8 + m] = pose[m];
+}
+
+// Co-resident CTA capacity of the device for the dataflow kernel (its CTAs spin on each
+// other's flags, so the grid must never exceed it).
+static int chol_max_ctas() {
+  static int cached = 0;
+  if (cached) return cached;
+  int dev = 0, sms = kNumSMs, per_sm = 1;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, chol_dataflow_kernel, kCholThreads, 0);
+  if (per_sm < 1) per_sm = 1;
+  if (per_sm > 4) per_sm = 4;
+  cached = sms * per_sm;
+  return cached;
+}
+
+int gn_solve_launch(float* Twc, const double* blocks, int N, int M, float delta_thresh, float* dx,
+                    void* ws, const GnLayout& L, cudaStream_t st) {
+  GnHeader* hdr = ws_ptr<GnHeader>(ws, L.hdr);
+  double* A = ws_ptr<double>(ws, L.A);
+  const int D = L.D, Dp = L.Dp, nb = Dp / NB;
+  gn_assemble_kernel<<<N, 64, 0, st>>>(blocks, ws_ptr<int>(ws, L.ie), ws_ptr<int>(ws, L.je),
+                                       ws_ptr<int>(ws, L.row_ptr), ws_ptr<int>(ws, L.adj), M, N, D,
+                                       Dp, A, hdr);
+  M3R_TRY(after_launch());
+  CholArgs a;
+  a.A = A; a.Dp = Dp; a.D = D; a.nb = nb;
+  a.flags = ws_ptr<int>(ws, L.flags);
+  a.x = ws_ptr<double>(ws, L.x);
+  a.Twc = Twc; a.dx = dx; a.N = N; a.delta_thresh = delta_thresh; a.hdr = hdr;
+  const int tiles = nb * (nb + 1) / 2;
+  int grid = chol_max_ctas();
+  if (grid > tiles) grid = tiles;
+  void* args[] = {&a};
+  const cudaError_t e = cudaLaunchCooperativeKernel((const void*)chol_dataflow_kernel, dim3(grid),
+                                                    dim3(kCholThreads), args, 0, st);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  return check_cuda(e);
+}
+
+}  // namespace m3r
+
+using namespace m3r;
+
+extern "C" int m3r_pose_retr(float* poses, const float* dx, int num_poses, int num_fix,
+                             m3r_stream_t stream) {
+  if (num_poses < 0 || num_fix < 0 || !poses || !dx) return M3R_EINVAL;
+  const int cnt = num_poses - num_fix;
+  if (cnt <= 0) return M3R_OK;
+  pose_retr_kernel<<<(cnt + 127) / 128, 128, 0, as_stream(stream)>>>(poses, dx, num_poses, num_fix);
+  return after_launch();
+}
