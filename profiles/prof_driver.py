@@ -1,6 +1,6 @@
 """Short single-GPU driver for ncu captures: one warm pass + a few passes of every hot-path
 kernel at the BASELINE sizes (matching b=8 512x384; GN rays N=32, 200 directed edges; tracker).
-Usage: python profiles/prof_driver.py [match|gn|calib|track|all] [reps]"""
+Usage: python profiles/prof_driver.py [match|gn|track|all] [reps] [gn_iters]"""
 import os
 import sys
 
@@ -15,6 +15,7 @@ from tests import synth  # noqa: E402
 
 what = sys.argv[1] if len(sys.argv) > 1 else "all"
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+gn_iters = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 dev = torch.device("cuda", 0)
 H, W = 384, 512
 if what in ("match", "all"):
@@ -27,7 +28,7 @@ if what in ("gn", "all"):
     for _ in range(reps):
         T = g["Twc"].clone()
         be.gauss_newton_rays(T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
-                             0.003, 10.0, 0.0, 1.5, 3, 0.0)
+                             0.003, 10.0, 0.0, 1.5, gn_iters, 0.0)
     torch.cuda.synchronize()
 if what in ("track", "all"):
     d = synth.make_tracker_inputs(seed=1234, device=dev)
