@@ -202,6 +202,11 @@ int* m3r_gn_done_flag(void* workspace);
 /* Device pointer (inside workspace) of the per-edge block buffer (num_edges*56 doubles). */
 double* m3r_gn_blocks(void* workspace, int num_poses, int num_edges, int local_edges, int n);
 
+/* Diagnostics: when device_buf != NULL, every later m3r_gn_solve_step records a timeline of
+ * its tile tasks (4 x u64 per task: {kind<<32 | i<<16 | j, t_begin, t_inputs_ready, t_end},
+ * globaltimer ns) into device_buf (capacity_tasks entries).  NULL switches it off (default). */
+void m3r_debug_chol_trace(unsigned long long* device_buf, int capacity_tasks);
+
 /* ------------------------------------------------------------------------- *
  * Two-frame tracker solve
  * ------------------------------------------------------------------------- */

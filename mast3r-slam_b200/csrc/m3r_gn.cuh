@@ -11,7 +11,7 @@
 //   part     : float[Ml*S*36] per-CTA partial sums of the LOCAL 28+7 normal-equation terms
 //   blocks   : double[M*56]  per-edge S (7x7) and v (7) after the adjoint transform
 //   A        : double[Dp*Dp] augmented normal matrix [H b; b^T 1], padded to 32
-//   x        : double[2*Dp]  the solution x (second half: scratch)
+//   x        : double[3*Dp]  the solution x, 1/diag(L), scratch sink
 //   flags    : int32[nb*nb + nb] tile-ready / x-block-ready epochs of the dataflow Cholesky
 #pragma once
 #include "m3r_common.cuh"
@@ -74,7 +74,7 @@ inline GnLayout gn_layout(int N, int M, int Ml, int n) {
   L.adj = take(sizeof(int) * (size_t)2 * M);
   L.blocks = take(sizeof(double) * (size_t)M * kGnBlock);
   L.A = take(sizeof(double) * (size_t)L.Dp * L.Dp);
-  L.x = take(sizeof(double) * (size_t)2 * L.Dp);
+  L.x = take(sizeof(double) * (size_t)3 * L.Dp);
   L.nflags = (L.Dp / kGnNB) * (L.Dp / kGnNB) + (L.Dp / kGnNB);
   L.flags = take(sizeof(int) * (size_t)L.nflags);
   // n- and Ml-dependent arrays last: every offset above depends on (N, M) only, `xc` on

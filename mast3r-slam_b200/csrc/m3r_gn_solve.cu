@@ -108,13 +108,31 @@ __device__ __forceinline__ void post_flag(int* f, int epoch) {
   if (threadIdx.x == 0) { __threadfence(); st_release(f, epoch); }
 }
 
+// Optional timeline of the dataflow kernel (diagnostics; set by m3r_debug_chol_trace): per
+// task 4 x u64 = {kind<<32 | i<<16 | j, t_begin, t_inputs_ready, t_end} in globaltimer ns.
+static unsigned long long* g_chol_trace = nullptr;
+static int g_chol_trace_cap = 0;
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t;
+}
+
 struct CholArgs {
   double* A; int Dp, D, nb;
   int* flags;      // [nb*nb] tile (i,j) ready, then [nb] x block ready
-  double* x;       // [Dp] solution of the normal equations (before the sign flip)
+  double* x;       // [Dp] solution of the normal equations (before the sign flip), then [Dp] 1/diag(L)
   float* Twc; float* dx; int N; float delta_thresh;
   GnHeader* hdr;
+  unsigned long long* trace; int trace_cap;
 };
+
+__device__ __forceinline__ void trace_put(const CholArgs& a, int slot, int kind, int i, int j,
+                                          unsigned long long t0, unsigned long long t1) {
+  if (a.trace && threadIdx.x == 0 && slot < a.trace_cap) {
+    unsigned long long* p = a.trace + 4 * (size_t)slot;
+    p[0] = ((unsigned long long)kind << 32) | ((unsigned long long)i << 16) | (unsigned long long)j;
+    p[1] = t0; p[2] = t1; p[3] = gtimer();
+  }
+}
 
 // global tile (bi,bj) -> shared [32][33], L2-coherent loads (tiles are written by other SMs)
 __device__ __forceinline__ void load_tile(const double* __restrict__ A, int Dp, int bi, int bj,
@@ -128,9 +146,17 @@ __device__ __forceinline__ void load_tile(const double* __restrict__ A, int Dp, 
 }
 
 // In-place Cholesky of the 32x32 tile in `s` by warp 0 (lane r owns row r in registers).
-// Rows whose global index is >= D (augmented rhs row, padding) take pivot 1.
+// Rows whose global index is >= D (augmented rhs row, padding) take pivot 1.  The pivot is
+// formed as d * rsqrt(d) and the column is scaled by rsqrt(d) (no fp64 sqrt + divide on the
+// 32-step dependent chain: 71 vs 171 cycles, profiles/micro/fp64_lat.cu); 1/pivot is kept in
+// `dinv_g` for the TRSM and the back-substitution.  Fully unrolled (registers need static
+// indices): ~40 KB of straight-line code that every SM fetches cold (each tile task runs on
+// another SM): measured 12.6 us per POTRF in the kernel (m3r_debug_chol_trace) vs 4.7 us warm
+// (profiles/micro/potrf_lat.cu).  Tried and rejected (profiles/r1j_chol_notes.md): a compact
+// shifted-register loop (no cold fetch, but 14.8 us), pre-warming the bodies on idle CTAs
+// (27 CTAs fetching at once delayed the first column by 20 us).
 __device__ __forceinline__ void potrf_tile(double (*s)[NB + 1], double* col, int g0, int D,
-                                           GnHeader* hdr) {
+                                           double* __restrict__ dinv_g, GnHeader* hdr) {
   const int r = threadIdx.x;
   if (r < NB) {
     double a[NB];
@@ -139,13 +165,13 @@ __device__ __forceinline__ void potrf_tile(double (*s)[NB + 1], double* col, int
 #pragma unroll
     for (int c = 0; c < NB; c++) {
       const double d = __shfl_sync(0xffffffffu, a[c], c);
-      double p;
-      if (g0 + c >= D) p = 1.0;
-      else if (d > 0.0) p = sqrt(d);
-      else { p = 1.0; if (r == 0) hdr->chol_fail = 1; }
-      const double l = (r == c) ? p : a[c] / p;
+      const bool unit = (g0 + c >= D) || !(d > 0.0);
+      if (r == 0 && g0 + c < D && !(d > 0.0)) hdr->chol_fail = 1;
+      const double y = unit ? 1.0 : rsqrt(d);
+      const double l = (r == c) ? (unit ? 1.0 : d * y) : a[c] * y;
       a[c] = l;
       col[r] = l;
+      if (r == c) dinv_g[g0 + c] = y;
       __syncwarp();
 #pragma unroll
       for (int c2 = c + 1; c2 < NB; c2++)
@@ -159,10 +185,10 @@ __device__ __forceinline__ void potrf_tile(double (*s)[NB + 1], double* col, int
 
 // X <- X * Ljj^-T for the 32x32 tile X in `sx` (lane r owns row r), Ljj in `sl`.
 __device__ __forceinline__ void trsm_tile(double (*sx)[NB + 1], const double (*sl)[NB + 1],
-                                          double* dinv) {
+                                          double* dinv, const double* __restrict__ dinv_g) {
   const int r = threadIdx.x;
   if (r < NB) {
-    dinv[r] = 1.0 / sl[r][r];
+    dinv[r] = __ldcg(dinv_g + r);
     __syncwarp();
     double a[NB];
 #pragma unroll
@@ -182,8 +208,9 @@ __device__ __forceinline__ void trsm_tile(double (*sx)[NB + 1], const double (*s
 // Tile (i,j), i >= j:  A_ij <- (A_ij - sum_{k<j} L_ik L_jk^T) [chol | * L_jj^-T], then flag it.
 __device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, int epoch,
                                                double (*sA)[NB + 1], double (*sB)[NB + 1],
-                                               double* sv) {
+                                               double* sv, int slot) {
   const int tid = threadIdx.x;
+  const unsigned long long t_begin = a.trace ? gtimer() : 0ull;
   const int ty = tid >> 3, tx = tid & 7;  // 4x4 micro-tile: rows ty+8x, cols tx+8y
   double acc[4][4];
 #pragma unroll
@@ -219,13 +246,15 @@ __device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, 
       sA[r][c] = __ldcg(dst + (size_t)r * a.Dp + c) - acc[x][y];
     }
   __syncthreads();
+  unsigned long long t_ready = a.trace ? gtimer() : 0ull;
   if (i == j) {
-    potrf_tile(sA, sv, j * NB, a.D, a.hdr);
+    potrf_tile(sA, sv, j * NB, a.D, a.x + a.Dp, a.hdr);
   } else {
     wait_flag(a.flags + j * a.nb + j, epoch);
+    if (a.trace) t_ready = gtimer();
     load_tile(a.A, a.Dp, j, j, sB);
     __syncthreads();
-    trsm_tile(sA, sB, sv);
+    trsm_tile(sA, sB, sv, a.x + a.Dp + j * NB);
   }
   __syncthreads();
   for (int idx = tid; idx < NB * NB; idx += kCholThreads) {
@@ -233,13 +262,16 @@ __device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, 
     dst[(size_t)r * a.Dp + c] = sA[r][c];
   }
   post_flag(a.flags + i * a.nb + j, epoch);
+  trace_put(a, slot, i == j ? 0 : 1, i, j, t_begin, t_ready);
 }
 
 // Back substitution for block column c (L^T x = y, y^T = row D of L):
 //   x_c = L_cc^-T ( y_c - sum_{m>c} L_mc^T x_m ),  entries with global index >= D are 0.
 __device__ __forceinline__ void chol_back_task(const CholArgs& a, int c, int epoch,
-                                               double (*sA)[NB + 1], double* sx, double* sred) {
+                                               double (*sA)[NB + 1], double* sx, double* sred,
+                                               int slot) {
   const int tid = threadIdx.x, t = tid & 31, half = tid >> 5;
+  const unsigned long long t_begin = a.trace ? gtimer() : 0ull;
   int* xflags = a.flags + a.nb * a.nb;
   wait_flag(a.flags + (a.nb - 1) * a.nb + c, epoch);  // row D of L (and, transitively, column c)
   double s = 0.0;
@@ -253,13 +285,14 @@ __device__ __forceinline__ void chol_back_task(const CholArgs& a, int c, int epo
       s = fma(__ldcg(Lmc + (size_t)r * a.Dp + t), sx[r], s);
     __syncthreads();
   }
+  const unsigned long long t_ready = a.trace ? gtimer() : 0ull;
   if (half == 1) sred[t] = s;
   load_tile(a.A, a.Dp, c, c, sA);
   __syncthreads();
   if (tid < NB) {
     const int g = c * NB + t;
     double rhs = (g < a.D) ? __ldcg(a.A + (size_t)a.D * a.Dp + g) - (s + sred[t]) : 0.0;
-    const double dinv = 1.0 / sA[t][t];
+    const double dinv = __ldcg(a.x + a.Dp + g);
     double xo = 0.0;
 #pragma unroll
     for (int k = NB - 1; k >= 0; k--) {
@@ -271,6 +304,7 @@ __device__ __forceinline__ void chol_back_task(const CholArgs& a, int c, int epo
     a.x[g] = xo;
   }
   post_flag(xflags + c, epoch);
+  trace_put(a, slot, 2, c, c, t_begin, t_ready);
 }
 
 // dx = -x (zeros on failure), retract, |dx| test  (gn_kernels.cu:1209-1222) — one CTA.
@@ -321,11 +355,11 @@ chol_dataflow_kernel(const CholArgs a) {
   int t = 0;
   for (int j = 0; j < a.nb; j++)
     for (int i = j; i < a.nb; i++, t++)
-      if (t % G == cta) chol_tile_task(a, i, j, epoch, sA, sB, sv);
+      if (t % G == cta) chol_tile_task(a, i, j, epoch, sA, sB, sv, t);
   // block columns of the back substitution, last to first (all after every tile)
   for (int c = a.nb - 1; c >= 0; c--)
     if (c % G == cta) {
-      chol_back_task(a, c, epoch, sA, sv, sred);
+      chol_back_task(a, c, epoch, sA, sv, sred, t + c);
       if (c == 0) {  // x complete: this CTA finishes the iteration
         __syncthreads();
         gn_update_block(a.Twc, a.x, a.N, a.D, a.delta_thresh, a.dx, a.hdr, red);
@@ -377,6 +411,7 @@ int gn_solve_launch(float* Twc, const double* blocks, int N, int M, float delta_
   a.flags = ws_ptr<int>(ws, L.flags);
   a.x = ws_ptr<double>(ws, L.x);
   a.Twc = Twc; a.dx = dx; a.N = N; a.delta_thresh = delta_thresh; a.hdr = hdr;
+  a.trace = g_chol_trace; a.trace_cap = g_chol_trace_cap;
   const int tiles = nb * (nb + 1) / 2;
   int grid = chol_max_ctas();
   if (grid > tiles) grid = tiles;
@@ -390,6 +425,11 @@ int gn_solve_launch(float* Twc, const double* blocks, int N, int M, float delta_
 }  // namespace m3r
 
 using namespace m3r;
+
+extern "C" void m3r_debug_chol_trace(unsigned long long* device_buf, int capacity_tasks) {
+  g_chol_trace = device_buf;
+  g_chol_trace_cap = device_buf ? capacity_tasks : 0;
+}
 
 extern "C" int m3r_pose_retr(float* poses, const float* dx, int num_poses, int num_fix,
                              m3r_stream_t stream) {

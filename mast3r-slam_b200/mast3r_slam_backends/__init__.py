@@ -40,7 +40,7 @@ EXPORTS = [
     "m3r_match_iter_proj_fused", "m3r_match_refine_fused", "m3r_pose_retr",
     "m3r_gn_workspace_bytes", "m3r_gauss_newton", "m3r_gn_prepare", "m3r_gn_accumulate",
     "m3r_gn_solve_step", "m3r_gn_done_flag", "m3r_gn_blocks", "m3r_track_workspace_bytes",
-    "m3r_track_ray_dist",
+    "m3r_track_ray_dist", "m3r_debug_chol_trace",
 ]
 
 
@@ -75,6 +75,8 @@ def _load():
     lib.m3r_gn_done_flag.argtypes = [vp]
     lib.m3r_gn_blocks.restype = vp
     lib.m3r_gn_blocks.argtypes = [vp, i32, i32, i32, i32]
+    lib.m3r_debug_chol_trace.argtypes = [vp, i32]
+    lib.m3r_debug_chol_trace.restype = None
     lib.m3r_track_workspace_bytes.restype = sz
     lib.m3r_track_workspace_bytes.argtypes = [i32]
     lib.m3r_track_ray_dist.argtypes = [vp, vp, vp, vp, i32, f32, f32, f32, i32, f32, f32, vp, vp,

@@ -1,0 +1,49 @@
+"""Timeline of the tile-dataflow Cholesky (m3r_debug_chol_trace) for a GN-rays graph.
+Usage (GPU box): python profiles/chol_trace.py [N] [out.txt]"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "mast3r-slam_b200"))
+import torch  # noqa: E402
+
+import mast3r_slam_backends as be  # noqa: E402
+from tests import synth  # noqa: E402
+
+N = int(sys.argv[1]) if len(sys.argv) > 1 else 32
+dev = torch.device("cuda", 0)
+H, W = (384, 512) if N <= 64 else (48, 64)
+counts = None if N == 32 else {1: None, 2: N - 2, 5: N - 5, "random": N // 4}
+g = synth.make_graph(N=N, counts=counts, H=H, W=W, seed=1236, device=dev)
+prm = be._params(be.GN_RAYS, 0.003, 10.0, 0.0, 1.5)
+s = be.GNSolver(prm, g["Twc"].clone(), g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"])
+for _ in range(3):
+    s.accumulate(); s.solve_step(0.0)
+torch.cuda.synchronize()
+nb = (7 * (N - 1) + 1 + 31) // 32
+cap = nb * (nb + 1) // 2 + nb
+buf = torch.zeros((cap, 4), dtype=torch.int64, device=dev)
+be._lib.m3r_debug_chol_trace(buf.data_ptr(), cap)
+s.accumulate()
+torch.cuda.synchronize()
+a = torch.cuda.Event(enable_timing=True); z = torch.cuda.Event(enable_timing=True)
+a.record(); s.solve_step(0.0); z.record()
+torch.cuda.synchronize()
+be._lib.m3r_debug_chol_trace(None, 0)
+t = buf.cpu().numpy()
+t0 = t[t[:, 1] > 0, 1].min()
+lines = [f"N={N} nb={nb} solve_step {a.elapsed_time(z) * 1e3:.1f} us (event); kernel span "
+         f"{(t[:, 3].max() - t0) / 1e3:.1f} us"]
+kinds = {0: "potrf", 1: "trsm ", 2: "back "}
+order = sorted(range(cap), key=lambda r: t[r, 3])
+for r in order:
+    k, i, j = int(t[r, 0] >> 32), int((t[r, 0] >> 16) & 0xFFFF), int(t[r, 0] & 0xFFFF)
+    if nb > 16 and not (k != 1 or i == j + 1):
+        continue
+    lines.append(f"{kinds[k]} ({i:3d},{j:3d}) begin {(t[r, 1] - t0) / 1e3:8.2f}  ready {(t[r, 2] - t0) / 1e3:8.2f}  "
+                 f"end {(t[r, 3] - t0) / 1e3:8.2f}  work {(t[r, 3] - t[r, 2]) / 1e3:6.2f} us")
+out = "\n".join(lines)
+print(out)
+if len(sys.argv) > 2:
+    open(sys.argv[2], "w").write(out + "\n")

@@ -131,6 +131,7 @@ def gn_case(N, counts, calib, seed):
     run(ref)(Ta); run(be)(Tb)
     torch.cuda.synchronize()
     r["pose_max_abs_diff"] = float((Ta - Tb).abs().max())
+    r["pose_max_abs_update"] = float((Tb - g["Twc"]).abs().max())  # the solve did move the poses
     r["iters_per_s_ref"] = iters / (r["ref"]["median_ms"] * 1e-3)
     r["iters_per_s_b200"] = iters / (r["b200"]["median_ms"] * 1e-3)
     r["speedup"] = r["ref"]["median_ms"] / r["b200"]["median_ms"]
