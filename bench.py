@@ -38,6 +38,18 @@ B_ITER_PROJ, B_REFINE, B_MATCH_CALL = 65, 128, 225
 B_GN_POINT, B_TRACK_POINT = 45, 29
 
 
+def ncu_traffic(kernel, scale=1.0):
+    """DRAM bytes per launch of `kernel` from the committed ncu capture (profiles/traffic.json),
+    scaled when the bench batch differs from the captured one; None if not captured."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(p) as f:
+            v = json.load(f).get(kernel)
+        return None if v is None else float(v) * scale
+    except OSError:
+        return None
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -147,6 +159,7 @@ def main():
     ap.add_argument("--batch", type=int, default=8, help="frame pairs per step per GPU")
     ap.add_argument("--no-extra", action="store_true", help="skip the GN / tracker extras")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-large", action="store_true", help="skip BASELINE configs[4] (N=512, 8192 directed edges)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -225,8 +238,12 @@ def main():
     alg = {0: None, 1: B_ITER_PROJ, 2: B_REFINE}[dom]
     achieved = (alg * b * N_PIX / (k_ms[dom] * 1e-3) / 1e9) if alg else None
     roofline = {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": (achieved / peak) if achieved else None, "traffic": None,
+                "frac": (achieved / peak) if achieved else None, "traffic": ncu_traffic(names[dom], b / 8.0),
                 "peak_kind": peak_kind, "algorithmic_bytes_per_pixel": alg,
+                "algorithmic_bytes_per_launch": (alg * b * N_PIX) if alg else None,
+                "note": "refine_matches is bound by on-chip pipes, not HBM: ncu shows the fp16x2 (fma-heavy) pipe "
+                        "71 % and the L1 data pipe 77 % busy (profiles/r1g_ncu_digest.md); its exact fp16 "
+                        "rounding chain admits no tensor-core form (DESIGN.md 4.2)",
                 "kernel_ms": {n: round(t, 4) for n, t in zip(names, k_ms)},
                 "kernels": {
                     "iter_proj_fused": {"achieved": B_ITER_PROJ * b * N_PIX / (k_ms[1] * 1e-3) / 1e9,
@@ -270,7 +287,11 @@ def main():
     if not args.no_extra:
         try:
             extra.update(bench_gn(be, synth, dev, rank, world, peak, barrier, max_over_ranks))
-            extra.update(bench_tracker(be, synth, dev, peak))
+            if world == 1:
+                extra.update(bench_gn_calib(be, synth, dev))
+                extra.update(bench_tracker(be, synth, dev, peak))
+            if not args.no_large:
+                extra.update(bench_gn_large(be, synth, dev, rank, world, peak, barrier, max_over_ranks))
         except Exception as e:  # keep the headline line even if an extra fails
             extra["error"] = repr(e)
 
@@ -337,6 +358,14 @@ def bench_gn(be, synth, dev, rank, world, peak, barrier, max_over_ranks):
     z.record()
     barrier()
     ms = max_over_ranks(a.elapsed_time(z)) / reps
+    if world > 1:  # the sharded solve must reproduce the single-GPU poses bit for bit
+        T_sh = run()
+        T_one = g["Twc"].clone()
+        be.gauss_newton_rays(T_one, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
+                             0.003, 10.0, 0.0, 1.5, iters, 0.0)
+        same = torch.tensor([1 if torch.equal(T_sh, T_one) else 0], device=dev)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        out["gn_rays_sharded_equals_single_gpu"] = bool(same.item())
     out["gn_rays"] = {"workload": "gauss_newton_rays N=32, 200 directed edges, 512x384, 10 iterations "
                                   "(BASELINE configs[2])" + (f", edge-sharded x{world}" if world > 1 else ""),
                       "iters_per_s": iters / (ms * 1e-3), "ms_per_solve": ms}
@@ -360,10 +389,82 @@ def bench_gn(be, synth, dev, rank, world, peak, barrier, max_over_ranks):
         z.record()
         torch.cuda.synchronize()
         out["gn_rays"].update({"accumulate_ms": ms_acc, "solve_step_ms": a.elapsed_time(z) / 10,
-                               "roofline": {"bound": "hbm", "kernel": "gn_accum_kernel<rays> (+edge finish)",
+                               "roofline": {"bound": "hbm", "kernel": "gn_accum_stream_kernel<rays> (+edge finish)",
                                             "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                                            "algorithmic_bytes_per_edge_point": B_GN_POINT}})
+                                            "algorithmic_bytes_per_edge_point": B_GN_POINT,
+                                            "traffic": ncu_traffic("gn_accum_stream_kernel<rays>")}})
     return out
+
+
+def bench_gn_calib(be, synth, dev):
+    """BASELINE configs[3]: gauss_newton_calib, 64 keyframes, 200 edges (400 directed), TUM fr1
+    intrinsics scaled to 512x384, pixel + log-depth residuals, 10 iterations."""
+    import torch
+
+    g = synth.make_graph(N=64, counts={1: None, 2: 62, 5: 59, "random": 16}, seed=1237, device=dev)
+    Xs = synth.constrain_points_to_ray(g["Xs"], H, W, g["K"])
+    iters, reps = 10, 5
+
+    def run():
+        T = g["Twc"].clone()
+        be.gauss_newton_calib(T, Xs, g["Cs"], g["K"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
+                              H, W, -10, 1e-6, 1.0, 10.0, 0.0, 1.5, iters, 0.0)
+    for _ in range(2):
+        run()
+    torch.cuda.synchronize()
+    a = torch.cuda.Event(enable_timing=True); z = torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        run()
+    z.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(z) / reps
+    return {"gn_calib": {"workload": f"gauss_newton_calib N=64, {g['M']} directed edges, 512x384, 10 iterations "
+                                     "(BASELINE configs[3])", "iters_per_s": iters / (ms * 1e-3),
+                         "ms_per_solve": ms}}
+
+
+def bench_gn_large(be, synth, dev, rank, world, peak, barrier, max_over_ranks):
+    """BASELINE configs[4]: 512 keyframes, 4096 edges (8192 directed), edge-sharded over the ranks;
+    each rank generates only its own edge streams on the device (20.9 GB in total)."""
+    import torch
+
+    N, iters = 512, 3
+    K = synth.intrinsics(H, W, dev)
+    T_gt = synth.make_poses(N, 1238, dev)
+    Xs = synth.render_pointmaps(T_gt, H, W, K)
+    gen = synth._gen(1238 + 7, dev)
+    Cs = (1.0 + torch.exp(0.5 + 0.5 * synth.smooth_noise((N, 1, H, W), 4.0, gen, dev).view(N, H * W, 1))).contiguous()
+    counts = {1: None, 2: None, 3: None, 4: None, 5: None, 6: None, 7: None}
+    counts["random"] = 4096 - sum(N - k for k in range(1, 8))
+    ii_u, jj_u = synth.make_edges(N, counts, 1238)
+    ii_d = torch.cat([ii_u, jj_u]); jj_d = torch.cat([jj_u, ii_u])
+    M = ii_d.shape[0]
+    e0, cnt, ecounts = be.shard_edges(M, world, rank)
+    idx, valid, Q = synth.edge_streams(T_gt, Xs, ii_d[e0:e0 + cnt], jj_d[e0:e0 + cnt], H, W, K, 1238 + 13 + rank)
+    T0 = synth.perturb_poses(T_gt, 1238 + 29)
+    prm = be._params(be.GN_RAYS, 0.003, 10.0, 0.0, 1.5)
+    ii_g, jj_g = ii_d.to(dev), jj_d.to(dev)
+
+    def run():
+        T = T0.clone()
+        be.gauss_newton_sharded(prm, T, Xs, Cs, ii_g, jj_g, idx, valid, Q, e0, iters, 0.0, edge_counts=ecounts)
+        return T
+    run()
+    barrier()
+    a = torch.cuda.Event(enable_timing=True); z = torch.cuda.Event(enable_timing=True)
+    a.record()
+    run()
+    z.record()
+    barrier()
+    ms = max_over_ranks(a.elapsed_time(z))
+    per_iter = ms / iters
+    return {"gn_large": {"workload": f"gauss_newton_rays N=512, {M} directed edges, 512x384, {iters} iterations, "
+                                     f"edge-sharded x{world} (BASELINE configs[4])",
+                         "iters_per_s": iters / (ms * 1e-3), "ms_per_iteration": per_iter,
+                         "edges_per_rank": ecounts,
+                         "algorithmic_GB_per_iteration": B_GN_POINT * M * N_PIX / 1e9,
+                         "achieved_GBps_aggregate_incl_solve": B_GN_POINT * M * N_PIX / (per_iter * 1e-3) / 1e9}}
 
 
 def bench_tracker(be, synth, dev, peak):
