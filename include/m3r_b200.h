@@ -225,6 +225,21 @@ int m3r_track_ray_dist(const float* Xf, const float* Xk, const float* Qk,
                        float* T_CkCf, int* status, float* cost, void* workspace,
                        size_t workspace_bytes, m3r_stream_t stream);
 
+/* Calibrated twin: FrameTracker.opt_pose_calib_sim3 (tracker.py:216-266 with
+ * geometry.project_calib, geometry.py:63-104): residuals [u - u_k, v - v_k, log z - log z_k]
+ * with u = fx x/z + cx, weights sigma_pixel (x2) / sigma_depth, validity
+ * valid & valid_meas_k & (pixel_border < u < width-1-pixel_border, same for v) & (z > z_eps).
+ *   Xf (n,3) f32: the frame's points, already gathered by the match index and ray-constrained ;
+ *   meas_k (n,3) f32 = [u_k, v_k, log z_k] and valid_meas_k (n,1) u8 as built by
+ *   FrameTracker.get_points_poses (tracker.py:143-152) ; everything else as above. */
+int m3r_track_calib(const float* Xf, const float* meas_k, const float* Qk,
+                    const uint8_t* valid, const uint8_t* valid_meas_k, int n, float fx,
+                    float fy, float cx, float cy, int height, int width, int pixel_border,
+                    float z_eps, float sigma_pixel, float sigma_depth, float huber_k,
+                    int max_iters, float rel_error, float delta_norm, float* T_CkCf,
+                    int* status, float* cost, void* workspace, size_t workspace_bytes,
+                    m3r_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

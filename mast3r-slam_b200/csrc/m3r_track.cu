@@ -27,10 +27,15 @@ namespace m3r {
 constexpr int kTrkThreads = 256;
 constexpr int kTrkVals = 36;  // 28 H + 7 g + 1 cost
 
+constexpr int kTrkRays = 0, kTrkCalib = 1;
+
 struct TrackArgs {
   const float* Xf; const float* Xk; const float* Qk; const uint8_t* valid;
+  // calib mode: Xk is meas_k (n,3) = [u, v, log z_k], valid_meas (n) its validity
+  const uint8_t* valid_meas;
+  float fx, fy, cx, cy, u_lo, u_hi, v_lo, v_hi, z_eps;
   int n;
-  float inv_var_ray, inv_var_dist, huber_k;
+  float inv_var_ray, inv_var_dist, huber_k;  // calib: 1/sigma_pixel^2, 1/sigma_depth^2
   int max_iters; float rel_error, delta_norm;
   float* T;      // (8) in/out
   int* status;   // (4)
@@ -62,8 +67,9 @@ __device__ __forceinline__ void trk_row(float* h, float* g, float& cost, float w
   cost = fmaf(w * e, e, cost);
 }
 
+template <int MODE>
 __global__ void __launch_bounds__(kTrkThreads)
-track_ray_dist_kernel(const TrackArgs a) {
+track_kernel(const TrackArgs a) {
   cg::grid_group grid = cg::this_grid();
   __shared__ float red[kTrkThreads / 32][kTrkVals];
   __shared__ double tot[kTrkVals];
@@ -102,26 +108,51 @@ track_ray_dist_kernel(const TrackArgs a) {
       const float Px = fmaf(R[0], fx, fmaf(R[1], fy, fmaf(R[2], fz, T[0])));
       const float Py = fmaf(R[3], fx, fmaf(R[4], fy, fmaf(R[5], fz, T[1])));
       const float Pz = fmaf(R[6], fx, fmaf(R[7], fy, fmaf(R[8], fz, T[2])));
-      const float n2k = kx * kx + ky * ky + kz * kz;
-      const float nk_inv = rsqrtf(n2k);
-      const float n2 = Px * Px + Py * Py + Pz * Pz;
-      const float n_inv = rsqrtf(n2);
-      const float nrm = n2 * n_inv;
-      const float rx = Px * n_inv, ry = Py * n_inv, rz = Pz * n_inv;
-      // e = h(x) - z
-      const float e0 = rx - kx * nk_inv, e1 = ry - ky * nk_inv, e2 = rz - kz * nk_inv;
-      const float e3 = nrm - n2k * nk_inv;
-      const float wc_ray = ok ? q * a.inv_var_ray : 0.f;
-      const float wc_dist = ok ? q * a.inv_var_dist : 0.f;
-      const float w0 = huber_weight(wc_ray, e0, a.huber_k), w1 = huber_weight(wc_ray, e1, a.huber_k);
-      const float w2 = huber_weight(wc_ray, e2, a.huber_k), w3 = huber_weight(wc_dist, e3, a.huber_k);
-      const float dxx = n_inv - rx * rx * n_inv, dyy = n_inv - ry * ry * n_inv;
-      const float dzz = n_inv - rz * rz * n_inv;
-      const float dxy = -rx * ry * n_inv, dxz = -rx * rz * n_inv, dyz = -ry * rz * n_inv;
-      { const float J[7] = {dxx, dxy, dxz, 0.f, rz, -ry, 0.f}; trk_row<0x37u>(h, g, cost, w0, e0, J); }
-      { const float J[7] = {dxy, dyy, dyz, -rz, 0.f, rx, 0.f}; trk_row<0x2Fu>(h, g, cost, w1, e1, J); }
-      { const float J[7] = {dxz, dyz, dzz, ry, -rx, 0.f, 0.f}; trk_row<0x1Fu>(h, g, cost, w2, e2, J); }
-      { const float J[7] = {rx, ry, rz, 0.f, 0.f, 0.f, nrm}; trk_row<0x47u>(h, g, cost, w3, e3, J); }
+      if (MODE == kTrkRays) {
+        const float n2k = kx * kx + ky * ky + kz * kz;
+        const float nk_inv = rsqrtf(n2k);
+        const float n2 = Px * Px + Py * Py + Pz * Pz;
+        const float n_inv = rsqrtf(n2);
+        const float nrm = n2 * n_inv;
+        const float rx = Px * n_inv, ry = Py * n_inv, rz = Pz * n_inv;
+        // e = h(x) - z
+        const float e0 = rx - kx * nk_inv, e1 = ry - ky * nk_inv, e2 = rz - kz * nk_inv;
+        const float e3 = nrm - n2k * nk_inv;
+        const float wc_ray = ok ? q * a.inv_var_ray : 0.f;
+        const float wc_dist = ok ? q * a.inv_var_dist : 0.f;
+        const float w0 = huber_weight(wc_ray, e0, a.huber_k), w1 = huber_weight(wc_ray, e1, a.huber_k);
+        const float w2 = huber_weight(wc_ray, e2, a.huber_k), w3 = huber_weight(wc_dist, e3, a.huber_k);
+        const float dxx = n_inv - rx * rx * n_inv, dyy = n_inv - ry * ry * n_inv;
+        const float dzz = n_inv - rz * rz * n_inv;
+        const float dxy = -rx * ry * n_inv, dxz = -rx * rz * n_inv, dyz = -ry * rz * n_inv;
+        { const float J[7] = {dxx, dxy, dxz, 0.f, rz, -ry, 0.f}; trk_row<0x37u>(h, g, cost, w0, e0, J); }
+        { const float J[7] = {dxy, dyy, dyz, -rz, 0.f, rx, 0.f}; trk_row<0x2Fu>(h, g, cost, w1, e1, J); }
+        { const float J[7] = {dxz, dyz, dzz, ry, -rx, 0.f, 0.f}; trk_row<0x1Fu>(h, g, cost, w2, e2, J); }
+        { const float J[7] = {rx, ry, rz, 0.f, 0.f, 0.f, nrm}; trk_row<0x47u>(h, g, cost, w3, e3, J); }
+      } else {
+        // project_calib (geometry.py:63-104): pz = [u, v, log z], r = meas - pz  =>  e = pz - meas
+        const bool valid_z = Pz > a.z_eps;
+        const float u = (a.fx * Px + a.cx * Pz) / Pz, v = (a.fy * Py + a.cy * Pz) / Pz;
+        const bool in_img = (u > a.u_lo) && (u < a.u_hi) && (v > a.v_lo) && (v < a.v_hi);
+        const bool ok2 = ok && valid_z && in_img && (a.valid_meas[p] != 0);
+        const float zinv = 1.0f / Pz;
+        const float logz = valid_z ? logf(Pz) : 0.f;
+        const float xz = Px * zinv, yz = Py * zinv;
+        const float e0 = u - kx, e1 = v - ky, e2 = logz - kz;
+        const float wc_pix = ok2 ? q * a.inv_var_ray : 0.f;
+        const float wc_dep = ok2 ? q * a.inv_var_dist : 0.f;
+        if (ok2) {  // weight-0 rows are skipped (0 * inf would poison the sums when z == 0)
+          const float w0 = huber_weight(wc_pix, e0, a.huber_k), w1 = huber_weight(wc_pix, e1, a.huber_k);
+          const float w2 = huber_weight(wc_dep, e2, a.huber_k);
+          { const float J[7] = {a.fx * zinv, 0.f, -a.fx * xz * zinv, -a.fx * xz * yz,
+                                a.fx * (1.f + xz * xz), -a.fx * yz, 0.f};
+            trk_row<0x3Du>(h, g, cost, w0, e0, J); }
+          { const float J[7] = {0.f, a.fy * zinv, -a.fy * yz * zinv, -a.fy * (1.f + yz * yz),
+                                a.fy * xz * yz, a.fy * xz, 0.f};
+            trk_row<0x3Eu>(h, g, cost, w1, e1, J); }
+          { const float J[7] = {0.f, 0.f, zinv, yz, -xz, 0.f, 1.f}; trk_row<0x5Cu>(h, g, cost, w2, e2, J); }
+        }
+      }
     }
 #pragma unroll
     for (int k = 0; k < 28; k++) { const float v = warp_sum(h[k]); if (lane == 0) red[warp][k] = v; }
@@ -210,17 +241,33 @@ track_ray_dist_kernel(const TrackArgs a) {
   }
 }
 
-static int track_grid_size() {
-  static int cached = 0;
+static int track_grid_size(int mode) {
+  static int cache[2] = {0, 0};
+  int& cached = cache[mode];
   if (cached) return cached;
   int dev = 0, sms = kNumSMs, per_sm = 1;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_ray_dist_kernel, kTrkThreads, 0);
+  if (mode == kTrkRays)
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel<kTrkRays>, kTrkThreads, 0);
+  else
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel<kTrkCalib>, kTrkThreads, 0);
   if (per_sm < 1) per_sm = 1;
   if (per_sm > 2) per_sm = 2;
   cached = sms * per_sm;
   return cached;
+}
+
+static int track_launch(int mode, TrackArgs& a, size_t workspace_bytes, cudaStream_t st) {
+  int grid = track_grid_size(mode);
+  const int need = (a.n + kTrkThreads - 1) / kTrkThreads;
+  if (grid > need) grid = need;
+  if (workspace_bytes < sizeof(float) * 2 * (size_t)grid * kTrkVals) return M3R_EWORKSPACE;
+  void* args[] = {&a};
+  const void* fn = mode == kTrkRays ? (const void*)track_kernel<kTrkRays> : (const void*)track_kernel<kTrkCalib>;
+  cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kTrkThreads), args, 0, st);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  return check_cuda(e);
 }
 
 }  // namespace m3r
@@ -240,19 +287,36 @@ extern "C" int m3r_track_ray_dist(const float* Xf, const float* Xk, const float*
   if (n <= 0 || max_iters < 0 || !Xf || !Xk || !Qk || !valid || !T_CkCf || !status || !workspace)
     return M3R_EINVAL;
   if (sigma_ray == 0.f || sigma_dist == 0.f) return M3R_EINVAL;
-  int grid = track_grid_size();
-  const int need = (n + kTrkThreads - 1) / kTrkThreads;
-  if (grid > need) grid = need;
-  if (workspace_bytes < sizeof(float) * 2 * (size_t)grid * kTrkVals) return M3R_EWORKSPACE;
   TrackArgs a;
   a.Xf = Xf; a.Xk = Xk; a.Qk = Qk; a.valid = valid; a.n = n;
   a.inv_var_ray = (float)(1.0 / ((double)sigma_ray * sigma_ray));
   a.inv_var_dist = (float)(1.0 / ((double)sigma_dist * sigma_dist));
   a.huber_k = huber_k; a.max_iters = max_iters; a.rel_error = rel_error; a.delta_norm = delta_norm;
   a.T = T_CkCf; a.status = status; a.cost = cost; a.part = static_cast<float*>(workspace);
-  void* args[] = {&a};
-  cudaError_t e = cudaLaunchCooperativeKernel((const void*)track_ray_dist_kernel, dim3(grid),
-                                              dim3(kTrkThreads), args, 0, as_stream(stream));
-  g_launch_count.fetch_add(1, std::memory_order_relaxed);
-  return check_cuda(e);
+  a.valid_meas = nullptr;
+  return track_launch(kTrkRays, a, workspace_bytes, as_stream(stream));
+}
+
+extern "C" int m3r_track_calib(const float* Xf, const float* meas_k, const float* Qk,
+                               const uint8_t* valid, const uint8_t* valid_meas_k, int n, float fx,
+                               float fy, float cx, float cy, int height, int width,
+                               int pixel_border, float z_eps, float sigma_pixel, float sigma_depth,
+                               float huber_k, int max_iters, float rel_error, float delta_norm,
+                               float* T_CkCf, int* status, float* cost, void* workspace,
+                               size_t workspace_bytes, m3r_stream_t stream) {
+  if (n <= 0 || max_iters < 0 || !Xf || !meas_k || !Qk || !valid || !valid_meas_k || !T_CkCf ||
+      !status || !workspace)
+    return M3R_EINVAL;
+  if (sigma_pixel == 0.f || sigma_depth == 0.f) return M3R_EINVAL;
+  TrackArgs a;
+  a.Xf = Xf; a.Xk = meas_k; a.Qk = Qk; a.valid = valid; a.valid_meas = valid_meas_k; a.n = n;
+  a.fx = fx; a.fy = fy; a.cx = cx; a.cy = cy;
+  a.u_lo = (float)pixel_border; a.u_hi = (float)(width - 1 - pixel_border);
+  a.v_lo = (float)pixel_border; a.v_hi = (float)(height - 1 - pixel_border);
+  a.z_eps = z_eps;
+  a.inv_var_ray = (float)(1.0 / ((double)sigma_pixel * sigma_pixel));
+  a.inv_var_dist = (float)(1.0 / ((double)sigma_depth * sigma_depth));
+  a.huber_k = huber_k; a.max_iters = max_iters; a.rel_error = rel_error; a.delta_norm = delta_norm;
+  a.T = T_CkCf; a.status = status; a.cost = cost; a.part = static_cast<float*>(workspace);
+  return track_launch(kTrkCalib, a, workspace_bytes, as_stream(stream));
 }

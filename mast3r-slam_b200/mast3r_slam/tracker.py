@@ -39,3 +39,22 @@ class FrameTracker:
             print("max iters reached 0")
         T_CkCf = type(T_WCk)(rel.view(T_WCk.data.shape))
         return T_WCk * T_CkCf, T_CkCf
+
+    def opt_pose_calib_sim3(self, Xf, Xk, T_WCf, T_WCk, Qk, valid, meas_k, valid_meas_k, K, img_size):
+        """Calibrated twin (tracker.py:216-266): pixel + log-depth residuals against meas_k.
+        Same contract as opt_pose_ray_dist_sim3; Xk is unused by the solve, as in the reference."""
+        cfg = self.cfg
+        T_CkCf = T_WCk.inv() * T_WCf
+        rel = T_CkCf.data.reshape(8).to(torch.float32).contiguous().clone()
+        status = _be.track_calib(Xf.contiguous(), meas_k.contiguous(), Qk.contiguous(), valid.contiguous(),
+                                 valid_meas_k.contiguous(), K, img_size, rel, cfg["sigma_pixel"],
+                                 cfg["sigma_depth"], cfg["pixel_border"], cfg["depth_eps"], cfg["huber"],
+                                 cfg["max_iters"], cfg["rel_error"], cfg["delta_norm"])
+        iters, converged, failed, _ = status.tolist()
+        self.last_status = dict(iterations=iters, converged=bool(converged))
+        if failed:
+            raise RuntimeError("opt_pose_calib_sim3: normal equations not positive definite")
+        if not converged and iters == cfg["max_iters"]:
+            print("max iters reached 0")
+        T_CkCf = type(T_WCk)(rel.view(T_WCk.data.shape))
+        return T_WCk * T_CkCf, T_CkCf

@@ -40,7 +40,7 @@ EXPORTS = [
     "m3r_match_iter_proj_fused", "m3r_match_refine_fused", "m3r_pose_retr",
     "m3r_gn_workspace_bytes", "m3r_gauss_newton", "m3r_gn_prepare", "m3r_gn_accumulate",
     "m3r_gn_solve_step", "m3r_gn_done_flag", "m3r_gn_blocks", "m3r_track_workspace_bytes",
-    "m3r_track_ray_dist", "m3r_debug_chol_trace",
+    "m3r_track_ray_dist", "m3r_track_calib", "m3r_debug_chol_trace",
 ]
 
 
@@ -81,6 +81,8 @@ def _load():
     lib.m3r_track_workspace_bytes.argtypes = [i32]
     lib.m3r_track_ray_dist.argtypes = [vp, vp, vp, vp, i32, f32, f32, f32, i32, f32, f32, vp, vp,
                                        vp, vp, sz, vp]
+    lib.m3r_track_calib.argtypes = [vp, vp, vp, vp, vp, i32, f32, f32, f32, f32, i32, i32, i32, f32,
+                                    f32, f32, f32, i32, f32, f32, vp, vp, vp, vp, sz, vp]
     return lib
 
 
@@ -420,4 +422,30 @@ def track_ray_dist(Xf, Xk, Qk, valid, T_CkCf, sigma_ray, sigma_dist, huber_k, ma
                                        float(sigma_dist), float(huber_k), int(max_iters),
                                        float(rel_error), float(delta_norm), _ptr(T), _ptr(status),
                                        _ptr(cost), _ptr(ws), nbytes, _stream(Xf)), "track_ray_dist")
+    return (status, cost) if want_cost else status
+
+
+def track_calib(Xf, meas_k, Qk, valid, valid_meas_k, K, img_size, T_CkCf, sigma_pixel, sigma_depth,
+                pixel_border, z_eps, huber_k, max_iters, rel_error, delta_norm, want_cost=False):
+    """Whole opt_pose_calib_sim3 loop (tracker.py:216-266) on the relative pose; arguments as
+    track_ray_dist plus meas_k (n,3) f32, valid_meas_k (n,1) bool, K (3,3), img_size (h, w)."""
+    Xf = _req(Xf, "Xf", torch.float32, 2)
+    meas_k = _req(meas_k, "meas_k", torch.float32, 2)
+    Qk = _req(Qk, "Qk", torch.float32)
+    valid = _req(valid, "valid", torch.bool)
+    valid_meas_k = _req(valid_meas_k, "valid_meas_k", torch.bool)
+    T = _req(T_CkCf, "T_CkCf", torch.float32)
+    Kc = K.detach().to("cpu", torch.float32)
+    n = Xf.shape[0]
+    with torch.cuda.device(Xf.device):
+        status = torch.zeros((4,), dtype=torch.int32, device=Xf.device)
+        cost = torch.zeros((max(int(max_iters), 1),), dtype=torch.float32, device=Xf.device) if want_cost else None
+        nbytes = _lib.m3r_track_workspace_bytes(n)
+        ws = torch.empty((nbytes,), dtype=torch.uint8, device=Xf.device)
+        _check(_lib.m3r_track_calib(_ptr(Xf), _ptr(meas_k), _ptr(Qk), _ptr(valid), _ptr(valid_meas_k), n,
+                                    float(Kc[0, 0]), float(Kc[1, 1]), float(Kc[0, 2]), float(Kc[1, 2]),
+                                    int(img_size[0]), int(img_size[1]), int(pixel_border), float(z_eps),
+                                    float(sigma_pixel), float(sigma_depth), float(huber_k), int(max_iters),
+                                    float(rel_error), float(delta_norm), _ptr(T), _ptr(status), _ptr(cost),
+                                    _ptr(ws), nbytes, _stream(Xf)), "track_calib")
     return (status, cost) if want_cost else status

@@ -208,3 +208,69 @@ def opt_pose_ray_dist_sim3(Xf, Xk, T_CkCf, Qk, valid, sigma_ray=0.003, sigma_dis
             break
         old_cost = new_cost
     return T_CkCf, its, conv
+
+
+def project_calib(P, K, img_size, border=0, z_eps=0.0):  # geometry.py:63-104
+    """-> pz (..,3) = [u, v, log z], dpz_dP (..,3,3), valid (..,1)."""
+    b = P.shape[:-1]
+    p = (K.repeat(*b, 1, 1) @ P[..., None]).squeeze(-1)
+    p = p / p[..., 2:3]
+    p = p[..., :2]
+    u, v = p.split([1, 1], dim=-1)
+    x, y, z = P.split([1, 1, 1], dim=-1)
+    valid_u = (u > border) & (u < img_size[1] - 1 - border)
+    valid_v = (v > border) & (v < img_size[0] - 1 - border)
+    valid_z = z > z_eps
+    valid = valid_u & valid_v & valid_z
+    logz = torch.log(z)
+    logz[torch.logical_not(valid_z)] = 0.0
+    pz = torch.cat((p, logz), dim=-1)
+    fx, fy = K[..., 0, 0], K[..., 1, 1]
+    z_inv = 1.0 / z[..., 0]
+    J = torch.zeros(*b + (3, 3), device=P.device, dtype=P.dtype)
+    J[..., 0, 0] = fx
+    J[..., 1, 1] = fy
+    J[..., 0, 2] = -fx * x[..., 0] * z_inv
+    J[..., 1, 2] = -fy * y[..., 0] * z_inv
+    J *= z_inv[..., None, None]
+    J[..., 2, 2] = z_inv
+    return pz, J, valid
+
+
+def calib_measurements(Xk, img_size, depth_eps):  # tracker.py:143-152 (get_points_poses)
+    """Xk (n,3) already ray-constrained -> meas_k (n,3) = [u, v, log z_k], valid_meas_k (n,1)."""
+    h, w = img_size
+    u, v = torch.meshgrid(torch.arange(w), torch.arange(h), indexing="xy")
+    uv = torch.stack((u, v), dim=-1).to(Xk.dtype).view(-1, 2)
+    meas = torch.cat((uv, torch.log(Xk[..., 2:3])), dim=-1)
+    valid = Xk[..., 2:3] > depth_eps
+    meas[~valid.repeat(1, 3)] = 0.0
+    return meas, valid
+
+
+def opt_pose_calib_sim3(Xf, T_CkCf, Qk, valid, meas_k, valid_meas_k, K, img_size, sigma_pixel=1.0,
+                        sigma_depth=10.0, pixel_border=-10, depth_eps=1e-6, huber_k=1.345,
+                        max_iters=50, rel_error=1e-3, delta_norm=1e-3, history=None):
+    """tracker.py:216-266 on the RELATIVE pose.  -> (T_CkCf, iterations, converged)."""
+    sqrt_info_pixel = 1.0 / sigma_pixel * valid * torch.sqrt(Qk)
+    sqrt_info_depth = 1.0 / sigma_depth * valid * torch.sqrt(Qk)
+    sqrt_info = torch.cat((sqrt_info_pixel.repeat(1, 2), sqrt_info_depth), 1)
+    old_cost = float("inf")
+    its, conv = 0, False
+    for step in range(max_iters):
+        Xf_Ck, dX_dT = act_sim3_jac(T_CkCf, Xf)
+        pz, dpz_dX, valid_proj = project_calib(Xf_Ck, K, img_size, pixel_border, depth_eps)
+        sqrt_info2 = (valid_proj & valid_meas_k) * sqrt_info
+        r = meas_k - pz
+        J = -dpz_dX @ dX_dT
+        tau, new_cost, _, _ = solve(sqrt_info2, r, J, huber_k)
+        T_CkCf = T_CkCf.retr(tau)
+        its = step + 1
+        if history is not None:
+            history.append((new_cost, tau.clone(), T_CkCf.data.clone()))
+        rel_dec = math.fabs((old_cost - new_cost) / old_cost)
+        if rel_dec < rel_error or float(torch.linalg.norm(tau)) < delta_norm:
+            conv = True
+            break
+        old_cost = new_cost
+    return T_CkCf, its, conv

@@ -81,6 +81,40 @@ def main():
         out[f"{name}_taus"] = torch.cat([h[1] for h in hist]).numpy()
         out[f"{name}_T_gt"] = d["T_gt"].numpy()
         print(name, "iterations", len(hist), "T_CkCf", T_CkCf.data.numpy().round(5))
+    # calibrated twin: the reference's opt_pose_calib_sim3 (tracker.py:216-266) with the measurement
+    # construction of get_points_poses (:143-152) done by the reference's own geometry helpers
+    from mast3r_slam import geometry as ref_geom
+
+    for name, (H, W, seed) in {"ca": (48, 64, 1234), "cb": (96, 128, 77)}.items():
+        d = synth.make_tracker_calib_inputs(H, W, seed=seed, device="cpu")
+        q = torch.tensor([0.05, 0.02, -0.03, 1.0])
+        T_WCk = otrk.Sim3(torch.cat([torch.tensor([0.3, -0.1, 0.2]), q / q.norm(), torch.tensor([1.1])])[None])
+        T_WCf = otrk.Sim3(T_WCk.data.clone())
+        uv_k = ref_geom.get_pixel_coords(1, (H, W), device="cpu", dtype=torch.float32).view(-1, 2)
+        meas_k = torch.cat((uv_k, torch.log(d["Xk"][..., 2:3])), dim=-1)
+        valid_meas_k = d["Xk"][..., 2:3] > config["tracking"]["depth_eps"]
+        meas_k[~valid_meas_k.repeat(1, 3)] = 0.0
+        hist = []
+        orig_solve = trk.solve
+
+        def spy(sqrt_info, r, J):
+            tau, cost = orig_solve(sqrt_info, r, J)
+            hist.append((cost, tau.clone()))
+            return tau, cost
+
+        trk.solve = spy
+        T_WCf_new, T_CkCf = trk.opt_pose_calib_sim3(d["Xf"], d["Xk"], T_WCf, T_WCk, d["Qk"], d["valid"],
+                                                     meas_k, valid_meas_k, d["K"], (H, W))
+        trk.solve = orig_solve
+        out[f"{name}_HW"] = np.array([H, W, seed])
+        out[f"{name}_T_WCk"] = T_WCk.data.numpy()
+        out[f"{name}_T_WCf_out"] = T_WCf_new.data.numpy()
+        out[f"{name}_T_CkCf_out"] = T_CkCf.data.numpy()
+        out[f"{name}_costs"] = np.array([h[0] for h in hist], np.float64)
+        out[f"{name}_taus"] = torch.cat([h[1] for h in hist]).numpy()
+        print(name, "iterations", len(hist), "T_CkCf", T_CkCf.data.numpy().round(5))
+    out["cfg_calib"] = np.array([config["tracking"][k] for k in
+                                 ("sigma_pixel", "sigma_depth", "pixel_border", "depth_eps")], np.float64)
     out["cfg"] = np.array([config["tracking"][k] for k in
                            ("sigma_ray", "sigma_dist", "huber", "max_iters", "rel_error", "delta_norm")],
                           np.float64)

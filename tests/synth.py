@@ -263,3 +263,21 @@ def make_tracker_inputs(H=H0, W=W0, seed=1234, device="cpu", noise=1e-3):
     Qk = (1.0 + torch.exp(0.7 + 0.5 * smooth_noise((1, 1, H, W), 4.0 * W / W0, gen, device).view(n, 1))).contiguous()
     valid = Qk > 1.5
     return dict(Xf=Xf, Xk=Xk, Qk=Qk, valid=valid, T_gt=T_gt)
+
+
+def make_tracker_calib_inputs(H=H0, W=W0, seed=1234, device="cpu", noise=1e-3):
+    """Calibrated twin of make_tracker_inputs (tracker.py:131-154 with use_calib): both pointmaps
+    are ray-constrained (X = z K^-1 [u,v,1]); the frame's points are the keyframe's surface seen
+    from a pose offset by T_gt, matched by identity correspondences."""
+    d = make_tracker_inputs(H, W, seed, device, noise)
+    K = intrinsics(H, W, device)
+    Xk = constrain_points_to_ray(d["Xk"][None], H, W, K)[0].contiguous()
+    Xf = sim3_inv_act(d["T_gt"][None], Xk)
+    gen = _gen(seed + 5, device)
+    Xf = (Xf * (1.0 + noise * torch.randn((Xf.shape[0], 1), generator=gen, device=device))).contiguous()
+    u, v = pixel_grid(H, W, device)
+    meas = torch.cat([u.reshape(-1, 1), v.reshape(-1, 1), torch.log(Xk[:, 2:3])], -1).contiguous()
+    valid_meas = Xk[:, 2:3] > 1e-6
+    meas = torch.where(valid_meas.expand(-1, 3), meas, torch.zeros_like(meas)).contiguous()
+    return dict(Xf=Xf, Xk=Xk, Qk=d["Qk"], valid=d["valid"], meas_k=meas, valid_meas_k=valid_meas, K=K,
+                T_gt=d["T_gt"], H=H, W=W)

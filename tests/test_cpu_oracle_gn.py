@@ -281,6 +281,32 @@ def test_tracker_restatement_vs_reference_golden():
         assert np.abs(T.data.numpy()[0] - z[f"{name}_T_gt"]).max() < 1e-3
 
 
+def test_calib_tracker_restatement_vs_reference_golden():
+    """oracle.tracker.opt_pose_calib_sim3 vs the iterates of the reference's own
+    FrameTracker.opt_pose_calib_sim3 (golden made by tests/golden/gen_tracker_golden.py)."""
+    import torch
+    from oracle import tracker as otrk
+    from tests import synth
+
+    z = np.load(os.path.join(GOLD, "tracker_ref.npz"))
+    _, _, hk, mi, re_, dn = z["cfg"]
+    sp, sdp, border, zeps = z["cfg_calib"]
+    for name in ("ca", "cb"):
+        H, W, seed = (int(v) for v in z[f"{name}_HW"])
+        d = synth.make_tracker_calib_inputs(H, W, seed=seed, device="cpu")
+        meas, vmeas = otrk.calib_measurements(d["Xk"], (H, W), zeps)
+        assert torch.equal(meas, d["meas_k"]) and torch.equal(vmeas, d["valid_meas_k"])
+        hist = []
+        T, its, conv = otrk.opt_pose_calib_sim3(d["Xf"], otrk.Sim3.Identity(1), d["Qk"], d["valid"], meas, vmeas,
+                                                d["K"], (H, W), sp, sdp, int(border), zeps, hk, int(mi), re_, dn,
+                                                history=hist)
+        assert its == len(z[f"{name}_costs"]) and conv
+        assert np.allclose([h[0] for h in hist], z[f"{name}_costs"], rtol=1e-4)
+        assert np.allclose(torch.cat([h[1] for h in hist]).numpy(), z[f"{name}_taus"], atol=2e-6)
+        assert np.allclose(T.data.numpy(), z[f"{name}_T_CkCf_out"], atol=2e-6)
+        assert np.abs(T.data.numpy()[0] - d["T_gt"].numpy()).max() < 1e-3
+
+
 def test_sim3_shim_matches_c_oracle(orc):
     import torch
     from oracle import tracker as otrk

@@ -273,6 +273,63 @@ def test_tracker_full_size_vs_oracle(backends):
     assert np.abs(_np(T) - _np(d["T_gt"])).max() < 1e-3
 
 
+def test_calib_tracker_vs_reference_golden(backends):
+    """m3r_track_calib vs the iterates of the reference's own opt_pose_calib_sim3."""
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "tracker_ref.npz"))
+    _, _, hk, mi, re_, dn = z["cfg"]
+    sp, sdp, border, zeps = z["cfg_calib"]
+    for name in ("ca", "cb"):
+        H, W, seed = (int(v) for v in z[f"{name}_HW"])
+        d = synth.make_tracker_calib_inputs(H, W, seed=seed, device="cpu")
+        T = torch.tensor([0, 0, 0, 0, 0, 0, 1, 1], dtype=torch.float32, device=DEV)
+        status, cost = backends.track_calib(d["Xf"].to(DEV), d["meas_k"].to(DEV), d["Qk"].to(DEV),
+                                            d["valid"].to(DEV), d["valid_meas_k"].to(DEV), d["K"], (H, W), T,
+                                            sp, sdp, int(border), zeps, hk, int(mi), re_, dn, want_cost=True)
+        torch.cuda.synchronize()
+        its, conv, fail, _ = status.tolist()
+        ref_costs = z[f"{name}_costs"]
+        assert fail == 0 and conv == 1 and its == len(ref_costs)
+        # the converged cost (~1e-2) is the sum of squared fp32 rounding residue of u - u_k with
+        # u ~ 1e2 px (ulp 8e-6): absolute floor 5e-5 on top of the relative bar
+        assert np.allclose(_np(cost)[:its], ref_costs, rtol=2e-4, atol=5e-5)
+        assert np.abs(_np(T) - z[f"{name}_T_CkCf_out"][0]).max() < 2e-5
+
+
+def test_calib_tracker_full_size_vs_oracle_and_mirror(backends):
+    """512x384: kernel vs the CPU restatement; and the host mirror FrameTracker.opt_pose_calib_sim3
+    (reference signature) returns T_WCk * T_CkCf.  A band of points behind the camera / outside
+    the border exercises the validity gates."""
+    from mast3r_slam.sim3 import Sim3
+    from mast3r_slam.tracker import FrameTracker
+    from oracle import tracker as otrk
+
+    d = synth.make_tracker_calib_inputs(seed=1234, device=DEV)
+    Xf = d["Xf"].clone()
+    Xf[:4096, 2] = -1.0            # behind the camera: valid_z fails
+    Xf[4096:8192, 0] += 50.0       # projects far outside the border
+    vm = d["valid_meas_k"].clone(); vm[8192:12288] = False
+    T = torch.tensor([0, 0, 0, 0, 0, 0, 1, 1], dtype=torch.float32, device=DEV)
+    status, cost = backends.track_calib(Xf, d["meas_k"], d["Qk"], d["valid"], vm, d["K"], (d["H"], d["W"]), T,
+                                        1.0, 10.0, -10, 1e-6, 1.345, 50, 1e-3, 1e-3, want_cost=True)
+    torch.cuda.synchronize()
+    hist = []
+    T_o, its_o, conv_o = otrk.opt_pose_calib_sim3(Xf.cpu(), otrk.Sim3.Identity(1), d["Qk"].cpu(), d["valid"].cpu(),
+                                                  d["meas_k"].cpu(), vm.cpu(), d["K"].cpu(), (d["H"], d["W"]),
+                                                  history=hist)
+    its, conv, fail, _ = status.tolist()
+    assert (its, conv, fail) == (its_o, int(conv_o), 0)
+    assert np.allclose(_np(cost)[:its], [h[0] for h in hist], rtol=1e-3)
+    assert np.abs(_np(T) - _np(T_o.data[0])).max() < 2e-5
+    assert np.abs(_np(T) - _np(d["T_gt"])).max() < 1e-3
+    trk = FrameTracker(None, None, DEV)
+    q = torch.tensor([0.05, 0.02, -0.03, 1.0]); q = q / q.norm()
+    T_WCk = Sim3(torch.cat([torch.tensor([0.3, -0.1, 0.2]), q, torch.tensor([1.1])])[None].to(DEV))
+    T_WCf, T_CkCf = trk.opt_pose_calib_sim3(Xf, d["Xk"], Sim3(T_WCk.data.clone()), T_WCk, d["Qk"], d["valid"],
+                                            d["meas_k"], vm, d["K"], (d["H"], d["W"]))
+    assert np.abs(_np(T_CkCf.data[0]) - _np(T)).max() < 1e-5
+    assert np.abs(_np(T_WCf.data) - _np((T_WCk * T_CkCf).data)).max() == 0.0
+
+
 def test_tracker_cholesky_failure_flag(backends):
     """No valid points => H = 0 => not SPD: status.failed, pose untouched (the reference raises
     from torch.linalg.cholesky and the caller treats it as a tracking failure, tracker.py:72-93)."""
