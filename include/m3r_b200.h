@@ -240,6 +240,26 @@ int m3r_track_calib(const float* Xf, const float* meas_k, const float* Qk,
                     int* status, float* cost, void* workspace, size_t workspace_bytes,
                     m3r_stream_t stream);
 
+/* ------------------------------------------------------------------------- *
+ * Streaming steps either side of the solvers
+ * ------------------------------------------------------------------------- */
+
+/* Edge-tensor construction of FactorGraph.add_factors for ONE direction (global_opt.py:55-67):
+ *   Q_out[e][k] = sqrt(Q_src[e][idx_src2dst[e][k]] * Q_dst[e][k])
+ *   valid_count[e] = #{k : valid_match[e][k] && Q_out[e][k] > Q_conf}   (match_frac = count / n)
+ * idx (E,n) i64 ; valid_match (E,n,1) u8 ; Q_src, Q_dst, Q_out (E,n,1) f32 ; valid_count (E) i32.
+ * The reference's call for direction j is (idx_i2j, valid_match_j, Qii, Qji). */
+int m3r_edge_build(const int64_t* idx_src2dst, const uint8_t* valid_match, const float* Q_src,
+                   const float* Q_dst, int num_edges, int n, float Q_conf, float* Q_out,
+                   int* valid_count, m3r_stream_t stream);
+
+/* Frame.update_pointmap for the per-point filtering modes (frame.py:41-105), in place on
+ * X_canon (n,3) / C (n,1), optionally applying a Sim3 to the new points first
+ * (tracker.py:97-98).  mode: 0 weighted_pointmap (bit-identical to the reference's expression),
+ * 1 weighted_spherical, 2 indep_conf.  T_act: (8) f32 [t, q(xyzw), s] device pointer or NULL. */
+int m3r_pointmap_update(float* X_canon, float* C, const float* X_new, const float* C_new,
+                        const float* T_act, int n, int mode, m3r_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,168 @@
+// m3r_frontend.cu — the two streaming steps either side of the solvers, sm_100a.
+//
+//  * m3r_edge_build: the per-edge tensor construction of FactorGraph.add_factors (reference
+//    global_opt.py:55-67): Qj = sqrt(Qii[idx_i2j] * Qji), valid_j = valid_match_j & (Qj > Q_conf),
+//    and the per-edge count of valid_j that match_frac is made of.  The reference runs 6 PyTorch
+//    kernels (arange/repeat index tensor, advanced-index gather, mul, sqrt, compare, and, sum)
+//    and materialises a (B,n) int64 batch-index tensor; here it is one pass, 21 B per point.
+//  * m3r_pointmap_update: Frame.update_pointmap (frame.py:41-105) for the per-point filtering
+//    modes, optionally preceded by T.act(X) (tracker.py:97-98: `Xkk = T_CkCf.act(Xkf)` then
+//    `keyframe.update_pointmap(Xkk, Ckf)`), in place: 48 B per point instead of ~8 elementwise
+//    kernels with their temporaries.
+//    The weighted mean is evaluated with the reference's operation order and without FMA
+//    contraction, so the weighted_pointmap / indep_conf modes are bit-identical to torch.
+#include "m3r_common.cuh"
+#include "m3r_sim3.cuh"
+
+namespace m3r {
+
+constexpr int kFeThreads = 256;
+constexpr int kFeUnroll = 4;
+
+__global__ void __launch_bounds__(kFeThreads)
+edge_build_kernel(const int64_t* __restrict__ idx, const uint8_t* __restrict__ vmatch,
+                  const float* __restrict__ Qsrc, const float* __restrict__ Qdst, int n,
+                  float Q_conf, float* __restrict__ Qout, int* __restrict__ count) {
+  const int b = blockIdx.y;
+  const size_t row = (size_t)b * n;
+  int local = 0;
+  const int base = blockIdx.x * (kFeThreads * kFeUnroll) + threadIdx.x;
+  int64_t id[kFeUnroll];
+  float qd[kFeUnroll];
+  bool vm[kFeUnroll];
+#pragma unroll
+  for (int u = 0; u < kFeUnroll; u++) {
+    const int k = base + u * kFeThreads;
+    const bool in = k < n;
+    id[u] = in ? idx[row + k] : 0;
+    qd[u] = in ? ld_stream_f(Qdst + row + k) : 0.f;
+    vm[u] = in && vmatch[row + k] != 0;
+  }
+#pragma unroll
+  for (int u = 0; u < kFeUnroll; u++) {
+    const int k = base + u * kFeThreads;
+    if (k < n) {
+      const float q = sqrtf(__fmul_rn(__ldg(Qsrc + row + id[u]), qd[u]));  // torch.sqrt(Qii[.., idx] * Qji)
+      Qout[row + k] = q;
+      local += (vm[u] && q > Q_conf) ? 1 : 0;
+    }
+  }
+  // block count -> one integer atomic per CTA (order-independent, hence deterministic)
+  __shared__ int wsum[kFeThreads / 32];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = local;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int s = 0;
+#pragma unroll
+    for (int w = 0; w < kFeThreads / 32; w++) s += wsum[w];
+    if (s) atomicAdd(count + b, s);
+  }
+}
+
+enum { kPmWeighted = 0, kPmSpherical = 1, kPmIndepConf = 2 };
+
+__device__ __forceinline__ void to_spherical(float x, float y, float z, float& r, float& phi, float& th) {
+  r = sqrtf(x * x + y * y + z * z);  // torch.linalg.norm
+  phi = atan2f(y, x);
+  th = acosf(z / r);
+}
+
+template <int MODE, bool ACT>
+__global__ void __launch_bounds__(kFeThreads)
+pointmap_update_kernel(float* __restrict__ Xc, float* __restrict__ Cc, const float* __restrict__ Xn,
+                       const float* __restrict__ Cn, const float* __restrict__ T, int n) {
+  float R[9], t[3];
+  if (ACT) {  // s R X + t  (Sim3.act; actSim3 gn_kernels.cu:207-219)
+    float q[4] = {__ldg(T + 3), __ldg(T + 4), __ldg(T + 5), __ldg(T + 6)};
+    const float s = __ldg(T + 7);
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      float ev[3] = {0.f, 0.f, 0.f}, col[3];
+      ev[c] = 1.f;
+      act_so3<float>(q, ev, col);
+      R[0 + c] = s * col[0]; R[3 + c] = s * col[1]; R[6 + c] = s * col[2];
+    }
+    t[0] = __ldg(T); t[1] = __ldg(T + 1); t[2] = __ldg(T + 2);
+  }
+  const int stride = gridDim.x * kFeThreads;
+  for (int p = blockIdx.x * kFeThreads + threadIdx.x; p < n; p += stride) {
+    float x = ld_stream_f(Xn + 3 * (size_t)p), y = ld_stream_f(Xn + 3 * (size_t)p + 1),
+          z = ld_stream_f(Xn + 3 * (size_t)p + 2);
+    const float cn = ld_stream_f(Cn + p);
+    if (ACT) {
+      const float px = fmaf(R[0], x, fmaf(R[1], y, fmaf(R[2], z, t[0])));
+      const float py = fmaf(R[3], x, fmaf(R[4], y, fmaf(R[5], z, t[1])));
+      const float pz = fmaf(R[6], x, fmaf(R[7], y, fmaf(R[8], z, t[2])));
+      x = px; y = py; z = pz;
+    }
+    float* xo = Xc + 3 * (size_t)p;
+    const float c0 = Cc[p];
+    const float ox = xo[0], oy = xo[1], oz = xo[2];
+    if (MODE == kPmWeighted) {  // ((C * X_canon) + (C_new * X)) / (C + C_new), frame.py:74-77
+      const float den = __fadd_rn(c0, cn);
+      xo[0] = __fdiv_rn(__fadd_rn(__fmul_rn(c0, ox), __fmul_rn(cn, x)), den);
+      xo[1] = __fdiv_rn(__fadd_rn(__fmul_rn(c0, oy), __fmul_rn(cn, y)), den);
+      xo[2] = __fdiv_rn(__fadd_rn(__fmul_rn(c0, oz), __fmul_rn(cn, z)), den);
+      Cc[p] = den;
+    } else if (MODE == kPmSpherical) {  // frame.py:78-101
+      float r1, p1, t1, r2, p2, t2;
+      to_spherical(ox, oy, oz, r1, p1, t1);
+      to_spherical(x, y, z, r2, p2, t2);
+      const float den = c0 + cn;
+      const float r = (c0 * r1 + cn * r2) / den, ph = (c0 * p1 + cn * p2) / den, th = (c0 * t1 + cn * t2) / den;
+      float st, ct, sp, cp;
+      sincosf(th, &st, &ct);
+      sincosf(ph, &sp, &cp);
+      xo[0] = r * st * cp; xo[1] = r * st * sp; xo[2] = r * ct;
+      Cc[p] = den;
+    } else {  // indep_conf: keep the more confident observation per point, frame.py:69-72
+      if (cn > c0) { xo[0] = x; xo[1] = y; xo[2] = z; Cc[p] = cn; }
+    }
+  }
+}
+
+}  // namespace m3r
+
+using namespace m3r;
+
+extern "C" int m3r_edge_build(const int64_t* idx_src2dst, const uint8_t* valid_match,
+                              const float* Q_src, const float* Q_dst, int num_edges, int n,
+                              float Q_conf, float* Q_out, int* valid_count, m3r_stream_t stream) {
+  if (num_edges < 0 || n < 0 || num_edges > 65535) return M3R_EINVAL;
+  if (num_edges == 0) return M3R_OK;
+  if (!valid_count) return M3R_EINVAL;
+  cudaStream_t st = as_stream(stream);
+  M3R_TRY(check_cuda(cudaMemsetAsync(valid_count, 0, sizeof(int) * (size_t)num_edges, st)));
+  if (n == 0) return M3R_OK;
+  if (!idx_src2dst || !valid_match || !Q_src || !Q_dst || !Q_out) return M3R_EINVAL;
+  dim3 grid((n + kFeThreads * kFeUnroll - 1) / (kFeThreads * kFeUnroll), num_edges);
+  edge_build_kernel<<<grid, kFeThreads, 0, st>>>(idx_src2dst, valid_match, Q_src, Q_dst, n, Q_conf,
+                                                 Q_out, valid_count);
+  return after_launch();
+}
+
+extern "C" int m3r_pointmap_update(float* X_canon, float* C, const float* X_new, const float* C_new,
+                                   const float* T_act, int n, int mode, m3r_stream_t stream) {
+  if (n < 0 || mode < 0 || mode > 2) return M3R_EINVAL;
+  if (n == 0) return M3R_OK;
+  if (!X_canon || !C || !X_new || !C_new) return M3R_EINVAL;
+  cudaStream_t st = as_stream(stream);
+  int grid = (n + kFeThreads - 1) / kFeThreads;
+  if (grid > kNumSMs * 8) grid = kNumSMs * 8;
+#define M3R_PM(MODE)                                                                              \
+  do {                                                                                            \
+    if (T_act) pointmap_update_kernel<MODE, true><<<grid, kFeThreads, 0, st>>>(X_canon, C, X_new, \
+                                                                               C_new, T_act, n);  \
+    else pointmap_update_kernel<MODE, false><<<grid, kFeThreads, 0, st>>>(X_canon, C, X_new,      \
+                                                                          C_new, T_act, n);       \
+  } while (0)
+  switch (mode) {
+    case kPmWeighted: M3R_PM(kPmWeighted); break;
+    case kPmSpherical: M3R_PM(kPmSpherical); break;
+    default: M3R_PM(kPmIndepConf); break;
+  }
+#undef M3R_PM
+  return after_launch();
+}

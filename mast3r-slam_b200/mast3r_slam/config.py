@@ -12,7 +12,8 @@ config = {
     "tracking": {"min_match_frac": 0.05, "max_iters": 50, "C_conf": 0.0, "Q_conf": 1.5,
                  "rel_error": 1e-3, "delta_norm": 1e-3, "huber": 1.345, "match_frac_thresh": 0.333,
                  "sigma_ray": 0.003, "sigma_dist": 10.0, "sigma_pixel": 1.0, "sigma_depth": 10.0,
-                 "sigma_point": 0.05, "pixel_border": -10, "depth_eps": 1e-6},
+                 "sigma_point": 0.05, "pixel_border": -10, "depth_eps": 1e-6,
+                 "filtering_mode": "weighted_pointmap", "filtering_score": "median"},
     "local_opt": {"pin": 1, "window_size": 1e6, "C_conf": 0.0, "Q_conf": 1.5, "min_match_frac": 0.1,
                   "pixel_border": -10, "depth_eps": 1e-6, "max_iters": 10, "sigma_ray": 0.003,
                   "sigma_dist": 10.0, "sigma_pixel": 1.0, "sigma_depth": 10.0, "sigma_point": 0.05,

@@ -1,7 +1,9 @@
 """FactorGraph.solve_GN_rays / solve_GN_calib with the reference's behaviour (reference
 mast3r_slam/global_opt.py:101-213) on top of mast3r_slam_backends.gauss_newton_{rays,calib}.
-Edge construction (`add_factors`, :30-99) runs the MASt3R network and is caller-side; edges are
-handed in with `add_edges` in the tensors `add_factors` would have appended.
+Edge construction (`add_factors`, :30-99): the MASt3R network + symmetric matching is caller-side
+(`matcher`, the reference's mast3r_match_symmetric); everything after it — Q = sqrt(Q_src[idx] * Q_dst),
+the Q_conf gate, match fractions, edge acceptance and appending — is here, the per-point part as
+one CUDA launch per direction (m3r_edge_build).  `add_edges` appends already-built tensors.
 
 `frames` is any keyframe store with the reference's protocol: `frames[i]` has `.X_canon (n,3)`,
 `.T_WC` (Sim3 with data (1,8)), `.get_average_conf() (n,1)`, `.img (3,h,w)`; and
@@ -36,6 +38,33 @@ class FactorGraph:
         self.valid_match_j = cat(self.valid_match_j, valid_match_j)
         self.valid_match_i = cat(self.valid_match_i, valid_match_i)
         self.Q_ii2jj, self.Q_jj2ii = cat(self.Q_ii2jj, Q_ii2jj), cat(self.Q_jj2ii, Q_jj2ii)
+
+    def add_factors(self, ii, jj, min_match_frac, is_reloc=False, matcher=None):
+        """global_opt.py:30-99.  `matcher(model, frames, ii, jj)` must return what the reference's
+        mast3r_match_symmetric returns: (idx_i2j, idx_j2i, valid_match_j, valid_match_i, Qii, Qjj,
+        Qji, Qij) with shapes (E,n) i64 / (E,n,1) bool / (E,n,1) f32."""
+        matcher = matcher or self.model
+        (idx_i2j, idx_j2i, valid_match_j, valid_match_i, Qii, Qjj, Qji, Qij) = matcher(self.model, self.frames, ii, jj)
+        Q_conf = self.cfg["Q_conf"]
+        Qj, cnt_j = _be.edge_build(idx_i2j.contiguous(), valid_match_j.contiguous(), Qii.contiguous(),
+                                   Qji.contiguous(), Q_conf)
+        Qi, cnt_i = _be.edge_build(idx_j2i.contiguous(), valid_match_i.contiguous(), Qjj.contiguous(),
+                                   Qij.contiguous(), Q_conf)
+        n = idx_i2j.shape[1]
+        match_frac_j = cnt_j / n  # valid_j.sum(dim=(1,2)) / nj
+        match_frac_i = cnt_i / n
+        ii_tensor = torch.as_tensor(ii, device=self.device)
+        jj_tensor = torch.as_tensor(jj, device=self.device)
+        # both directions must clear the threshold; consecutive keyframes are always kept (:74-77)
+        invalid_edges = torch.minimum(match_frac_j, match_frac_i) < min_match_frac
+        invalid_edges = (~(ii_tensor == (jj_tensor - 1))) & invalid_edges
+        if invalid_edges.any() and is_reloc:
+            return False
+        valid_edges = ~invalid_edges
+        self.add_edges(ii_tensor[valid_edges], jj_tensor[valid_edges], idx_i2j[valid_edges],
+                       idx_j2i[valid_edges], valid_match_j[valid_edges], valid_match_i[valid_edges],
+                       Qj[valid_edges], Qi[valid_edges])
+        return valid_edges.sum() > 0
 
     def get_unique_kf_idx(self):
         return torch.unique(torch.cat((self.ii, self.jj)), sorted=True)

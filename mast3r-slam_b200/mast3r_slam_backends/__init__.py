@@ -40,7 +40,7 @@ EXPORTS = [
     "m3r_match_iter_proj_fused", "m3r_match_refine_fused", "m3r_pose_retr",
     "m3r_gn_workspace_bytes", "m3r_gauss_newton", "m3r_gn_prepare", "m3r_gn_accumulate",
     "m3r_gn_solve_step", "m3r_gn_done_flag", "m3r_gn_blocks", "m3r_track_workspace_bytes",
-    "m3r_track_ray_dist", "m3r_track_calib", "m3r_debug_chol_trace",
+    "m3r_track_ray_dist", "m3r_track_calib", "m3r_debug_chol_trace", "m3r_edge_build", "m3r_pointmap_update",
 ]
 
 
@@ -83,6 +83,8 @@ def _load():
                                        vp, vp, sz, vp]
     lib.m3r_track_calib.argtypes = [vp, vp, vp, vp, vp, i32, f32, f32, f32, f32, i32, i32, i32, f32,
                                     f32, f32, f32, i32, f32, f32, vp, vp, vp, vp, sz, vp]
+    lib.m3r_edge_build.argtypes = [vp, vp, vp, vp, i32, i32, f32, vp, vp, vp]
+    lib.m3r_pointmap_update.argtypes = [vp, vp, vp, vp, vp, i32, i32, vp]
     return lib
 
 
@@ -449,3 +451,41 @@ def track_calib(Xf, meas_k, Qk, valid, valid_meas_k, K, img_size, T_CkCf, sigma_
                                     float(rel_error), float(delta_norm), _ptr(T), _ptr(status), _ptr(cost),
                                     _ptr(ws), nbytes, _stream(Xf)), "track_calib")
     return (status, cost) if want_cost else status
+
+
+# --------------------------------------------------------------------------- front-end steps
+
+def edge_build(idx_src2dst, valid_match, Q_src, Q_dst, Q_conf):
+    """One direction of add_factors' edge tensors (global_opt.py:55-67).
+    -> (Q (E,n,1) f32 = sqrt(Q_src[idx] * Q_dst), valid_count (E,) i32 of valid_match & (Q > Q_conf))."""
+    idx = _req(idx_src2dst, "idx", torch.int64, 2)
+    vm = _req(valid_match, "valid_match", torch.bool)
+    Qs = _req(Q_src, "Q_src", torch.float32)
+    Qd = _req(Q_dst, "Q_dst", torch.float32)
+    E, n = idx.shape
+    with torch.cuda.device(idx.device):
+        Q = torch.empty((E, n, 1), dtype=torch.float32, device=idx.device)
+        cnt = torch.empty((E,), dtype=torch.int32, device=idx.device)
+        _check(_lib.m3r_edge_build(_ptr(idx), _ptr(vm), _ptr(Qs), _ptr(Qd), E, n, float(Q_conf), _ptr(Q),
+                                   _ptr(cnt), _stream(idx)), "edge_build")
+    return Q, cnt
+
+
+POINTMAP_MODES = {"weighted_pointmap": 0, "weighted_spherical": 1, "indep_conf": 2}
+
+
+def pointmap_update(X_canon, C, X_new, C_new, mode="weighted_pointmap", T_act=None):
+    """In place: Frame.update_pointmap's per-point modes (frame.py:69-101); T_act (8,) f32 applies
+    Sim3.act to X_new first (tracker.py:97-98)."""
+    Xc = _req(X_canon, "X_canon", torch.float32, 2)
+    Cc = _req(C, "C", torch.float32)
+    Xn = _req(X_new, "X_new", torch.float32, 2)
+    Cn = _req(C_new, "C_new", torch.float32)
+    if T_act is not None:
+        T_act = _req(T_act, "T_act", torch.float32)
+    if Xn.shape != Xc.shape or Cn.numel() != Cc.numel() or Cc.numel() != Xc.shape[0]:
+        raise RuntimeError("pointmap_update: shape mismatch")
+    with torch.cuda.device(Xc.device):
+        _check(_lib.m3r_pointmap_update(_ptr(Xc), _ptr(Cc), _ptr(Xn), _ptr(Cn), _ptr(T_act), Xc.shape[0],
+                                        POINTMAP_MODES[mode], _stream(Xc)), "pointmap_update")
+    return Xc, Cc

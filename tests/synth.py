@@ -281,3 +281,27 @@ def make_tracker_calib_inputs(H=H0, W=W0, seed=1234, device="cpu", noise=1e-3):
     meas = torch.where(valid_meas.expand(-1, 3), meas, torch.zeros_like(meas)).contiguous()
     return dict(Xf=Xf, Xk=Xk, Qk=d["Qk"], valid=d["valid"], meas_k=meas, valid_meas_k=valid_meas, K=K,
                 T_gt=d["T_gt"], H=H, W=W)
+
+
+def make_symmetric_match_outputs(E, H=H0, W=W0, seed=77, device="cpu", weak=()):
+    """What mast3r_match_symmetric returns for E keyframe pairs (global_opt.py:41-53): smooth
+    correspondences with seeded dropouts, descriptor confidences 1+exp(.); edges listed in `weak`
+    get mostly-invalid matches so that the match-fraction gate rejects them."""
+    gen = _gen(seed, device)
+    n = H * W
+    out = {}
+    for tag in ("i2j", "j2i"):
+        u, v = pixel_grid(H, W, device)
+        du = 6.0 * smooth_noise((E, 1, H, W), 16.0 * W / W0, gen, device)[:, 0]
+        dv = 6.0 * smooth_noise((E, 1, H, W), 16.0 * W / W0, gen, device)[:, 0]
+        uu = (u[None] + du).round().clamp(0, W - 1)
+        vv = (v[None] + dv).round().clamp(0, H - 1)
+        out["idx_" + tag] = (vv * W + uu).long().view(E, n).contiguous()
+        keep = torch.rand((E, n, 1), generator=gen, device=device) > 0.2
+        for e in weak:
+            keep[e] = torch.rand((n, 1), generator=gen, device=device) > 0.97
+        out["valid_" + tag] = keep.contiguous()
+    for name in ("Qii", "Qjj", "Qji", "Qij"):
+        q = smooth_noise((E, 1, H, W), 4.0 * W / W0, gen, device).view(E, n, 1)
+        out[name] = (1.0 + torch.exp(0.7 + 0.5 * q)).contiguous()
+    return out
