@@ -290,6 +290,7 @@ def main():
             if world == 1:
                 extra.update(bench_gn_calib(be, synth, dev))
                 extra.update(bench_tracker(be, synth, dev, peak))
+                extra.update(bench_frontend(be, synth, dev, peak))
             if not args.no_large:
                 extra.update(bench_gn_large(be, synth, dev, rank, world, peak, barrier, max_over_ranks))
         except Exception as e:  # keep the headline line even if an extra fails
@@ -493,6 +494,54 @@ def bench_tracker(be, synth, dev, peak):
                         "roofline": {"bound": "hbm (L2-resident after pass 1: latency-bound)", "achieved": ach,
                                      "peak": peak, "unit": "GB/s", "frac": ach / peak,
                                      "algorithmic_bytes_per_point": B_TRACK_POINT}}}
+
+
+def bench_frontend(be, synth, dev, peak):
+    """calibrated tracker, add_factors edge tensors, pointmap fusion."""
+    import torch
+
+    def timeit(fn, reps=20):
+        for _ in range(3):
+            fn()
+        a = torch.cuda.Event(enable_timing=True); z = torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(); a.record()
+        for _ in range(reps):
+            fn()
+        z.record(); torch.cuda.synchronize()
+        return a.elapsed_time(z) / reps
+
+    out = {}
+    E = 48  # 48 edges x 196608 points x 21 B = 198 MB > L2
+    m = synth.make_symmetric_match_outputs(E, seed=5, device=dev)
+    ms = timeit(lambda: be.edge_build(m["idx_i2j"], m["valid_i2j"], m["Qii"], m["Qji"], 1.5))
+    by = 21 * E * N_PIX  # idx 8 + valid 1 + Q_dst 4 + gathered Q_src 4 + Q_out 4
+    out["edge_build"] = {"workload": f"add_factors edge tensors, {E} edges x {N_PIX} points, one direction",
+                         "ms": ms, "algorithmic_bytes_per_point": 21, "achieved": by / (ms * 1e-3) / 1e9,
+                         "peak": peak, "unit": "GB/s", "frac": by / (ms * 1e-3) / 1e9 / peak}
+    nk = 32  # 32 keyframes updated back to back: 32 x 9.4 MB = 302 MB > L2
+    X = torch.randn((nk, N_PIX, 3), device=dev); C = torch.rand((nk, N_PIX, 1), device=dev) + 1
+    Xn = torch.randn((nk, N_PIX, 3), device=dev); Cn = torch.rand((nk, N_PIX, 1), device=dev) + 1
+    T = torch.tensor([0.1, 0.2, 0.3, 0, 0, 0, 1, 1.1], device=dev)
+
+    Xf_, Cf_, Xnf, Cnf = X.view(-1, 3), C.view(-1, 1), Xn.view(-1, 3), Cn.view(-1, 1)
+    ms = timeit(lambda: be.pointmap_update(Xf_, Cf_, Xnf, Cnf, "weighted_pointmap", T), reps=10)
+    by = 48 * N_PIX * nk  # X_canon 12 + C 4 in, X 12 + C 4 in, X_canon 12 + C 4 out
+    ms1 = timeit(lambda: be.pointmap_update(X[0], C[0], Xn[0], Cn[0], "weighted_pointmap", T), reps=50)
+    out["pointmap_update"] = {"workload": f"Sim3.act + weighted_pointmap update, {nk} x 512x384 points in one launch "
+                                          "(302 MB > L2)", "ms_single_keyframe_call": ms1,
+                              "ms": ms, "algorithmic_bytes_per_point": 48, "achieved": by / (ms * 1e-3) / 1e9,
+                              "peak": peak, "unit": "GB/s", "frac": by / (ms * 1e-3) / 1e9 / peak}
+    d = synth.make_tracker_calib_inputs(seed=1234, device=dev)
+    ident = torch.tensor([0, 0, 0, 0, 0, 0, 1, 1], dtype=torch.float32, device=dev)
+
+    def trk():
+        return be.track_calib(d["Xf"], d["meas_k"], d["Qk"], d["valid"], d["valid_meas_k"], d["K"], (H, W),
+                              ident.clone(), 1.0, 10.0, -10, 1e-6, 1.345, 50, 1e-3, 1e-3)
+    its = int(trk()[0])
+    ms = timeit(trk)
+    out["tracker_calib"] = {"workload": "opt_pose_calib_sim3 512x384, known Sim3 offset", "iterations": its,
+                            "ms_per_solve": ms, "iters_per_s": its / (ms * 1e-3)}
+    return {"frontend": out}
 
 
 if __name__ == "__main__":
