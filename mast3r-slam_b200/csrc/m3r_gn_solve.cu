@@ -83,7 +83,9 @@ gn_assemble_kernel(const double* __restrict__ blocks, const int* __restrict__ ie
 // ---------------------------------------------------------------------------------
 // Tile-dataflow Cholesky (left-looking), NB = 32, one 64-thread CTA per tile task.
 // ---------------------------------------------------------------------------------
-constexpr int kCholThreads = 64;
+constexpr int kCholThreads = 128;
+constexpr int kTY = kCholThreads / 8;  // thread grid kTY x 8 over a 32x32 tile
+constexpr int kRX = NB / kTY;          // micro-tile: rows ty + kTY*x (x < kRX), cols tx + 8*y (y < 4)
 
 __device__ __forceinline__ int ld_acquire(const int* p) {
   int v;
@@ -145,76 +147,140 @@ __device__ __forceinline__ void load_tile(const double* __restrict__ A, int Dp, 
   }
 }
 
-// In-place Cholesky of the 32x32 tile in `s` by warp 0 (lane r owns row r in registers).
-// Rows whose global index is >= D (augmented rhs row, padding) take pivot 1.  The pivot is
-// formed as d * rsqrt(d) and the column is scaled by rsqrt(d) (no fp64 sqrt + divide on the
-// 32-step dependent chain: 71 vs 171 cycles, profiles/micro/fp64_lat.cu); 1/pivot is kept in
-// `dinv_g` for the TRSM and the back-substitution.  Fully unrolled (registers need static
-// indices): ~40 KB of straight-line code that every SM fetches cold (each tile task runs on
-// another SM): measured 12.6 us per POTRF in the kernel (m3r_debug_chol_trace) vs 4.7 us warm
-// (profiles/micro/potrf_lat.cu).  Tried and rejected (profiles/r1j_chol_notes.md): a compact
-// shifted-register loop (no cold fetch, but 14.8 us), pre-warming the bodies on idle CTAs
-// (27 CTAs fetching at once delayed the first column by 20 us).
-__device__ __forceinline__ void potrf_tile(double (*s)[NB + 1], double* col, int g0, int D,
+// In-place Cholesky of the 32x32 tile in `s` by the whole 64-thread CTA: thread (ty,tx) of an
+// 8x8 grid keeps the 4x4 micro-tile {rows ty+8x, cols tx+8y} in registers; per column step the
+// raw column goes through a double-buffered shared vector (ONE __syncthreads per step), every
+// thread scales the 4+4 entries it needs by rsqrt(pivot) itself, and updates its micro-tile.
+// The per-step dependent chain is sts -> bar -> lds -> rsqrt -> dmul -> dfma (~170 cycles,
+// profiles/micro/fp64_lat.cu) and the loop body is the same code for every column, so nothing
+// is fetched cold: the earlier one-warp, fully unrolled form was 40 KB of straight-line code
+// and cost 11 us per tile inside the kernel (4.7 us warm), profiles/r1j_chol_notes.md.
+// Rows whose global index is >= D (augmented rhs row, padding) take pivot 1; 1/pivot is kept in
+// `dinv_g` for the TRSM and the back-substitution.
+// One column step of potrf_tile for a column c = 8*YC + cc whose micro-tile index YC is a
+// compile-time constant: register indices are static and whole micro-tile rows/columns that lie
+// left of / above the pivot drop out at compile time.
+template <int YC>
+__device__ __forceinline__ void potrf_step(double (&a)[kRX][4], double (*s)[NB + 1], double* colbuf,
+                                           int cc, int ty, int tx, int g0, int D,
                                            double* __restrict__ dinv_g, GnHeader* hdr) {
-  const int r = threadIdx.x;
-  if (r < NB) {
-    double a[NB];
+  const int c = 8 * YC + cc;
+  double* col = colbuf + (c & 1) * NB;
+  if (tx == cc) {  // owners of column c publish its raw entries (rows < c: unused)
 #pragma unroll
-    for (int c = 0; c < NB; c++) a[c] = s[r][c];
-#pragma unroll
-    for (int c = 0; c < NB; c++) {
-      const double d = __shfl_sync(0xffffffffu, a[c], c);
-      const bool unit = (g0 + c >= D) || !(d > 0.0);
-      if (r == 0 && g0 + c < D && !(d > 0.0)) hdr->chol_fail = 1;
-      const double y = unit ? 1.0 : rsqrt(d);
-      const double l = (r == c) ? (unit ? 1.0 : d * y) : a[c] * y;
-      a[c] = l;
-      col[r] = l;
-      if (r == c) dinv_g[g0 + c] = y;
-      __syncwarp();
-#pragma unroll
-      for (int c2 = c + 1; c2 < NB; c2++)
-        if (r >= c2) a[c2] = fma(-l, col[c2], a[c2]);
-      __syncwarp();
-    }
-#pragma unroll
-    for (int c = 0; c < NB; c++) s[r][c] = (c <= r) ? a[c] : 0.0;
+    for (int x = 0; x < kRX; x++) col[ty + kTY * x] = a[x][YC];
   }
+  __syncthreads();
+  const double d = col[c];
+  const bool bad = !(d > 0.0);
+  const bool unit = (g0 + c >= D) || bad;
+  if (threadIdx.x == 0) {
+    if (bad && g0 + c < D) hdr->chol_fail = 1;
+  }
+  const double yv = unit ? 1.0 : rsqrt(d);
+  if (threadIdx.x == 0) dinv_g[g0 + c] = yv;
+  double lr[kRX], lc[4];
+#pragma unroll
+  for (int x = 0; x < kRX; x++) lr[x] = (ty + kTY * x > c) ? col[ty + kTY * x] * yv : 0.0;
+#pragma unroll
+  for (int y = YC; y < 4; y++) lc[y] = col[tx + 8 * y] * yv;
+  lc[YC] = (tx > cc) ? lc[YC] : 0.0;  // columns <= c of the pivot's micro-column are final
+  if (tx == cc) {  // column c of L: 0 above the diagonal, the pivot, then the scaled entries
+#pragma unroll
+    for (int x = 0; x < kRX; x++) {
+      const int r = ty + kTY * x;
+      s[r][c] = (r == c) ? (unit ? 1.0 : d * yv) : lr[x];
+    }
+  }
+#pragma unroll
+  for (int x = 0; x < kRX; x++)
+#pragma unroll
+    for (int y = YC; y < 4; y++) a[x][y] = fma(-lr[x], lc[y], a[x][y]);
 }
 
-// X <- X * Ljj^-T for the 32x32 tile X in `sx` (lane r owns row r), Ljj in `sl`.
-__device__ __forceinline__ void trsm_tile(double (*sx)[NB + 1], const double (*sl)[NB + 1],
-                                          double* dinv, const double* __restrict__ dinv_g) {
-  const int r = threadIdx.x;
-  if (r < NB) {
-    dinv[r] = __ldcg(dinv_g + r);
-    __syncwarp();
-    double a[NB];
+// In-place Cholesky of the 32x32 tile in `s` by the whole CTA (see above).  The factor is
+// written to `s` column by column; the registers only carry the trailing matrix.
+__device__ __forceinline__ void potrf_tile(double (*s)[NB + 1], double* colbuf, int g0, int D,
+                                           double* __restrict__ dinv_g, GnHeader* hdr) {
+  const int tid = threadIdx.x, ty = tid >> 3, tx = tid & 7;
+  double a[kRX][4];  // the strict upper triangle is zeroed: it takes part in the (symmetric) updates
 #pragma unroll
-    for (int c = 0; c < NB; c++) a[c] = sx[r][c];
+  for (int x = 0; x < kRX; x++)
 #pragma unroll
-    for (int c = 0; c < NB; c++) {
-      const double xv = a[c] * dinv[c];
-      a[c] = xv;
+    for (int y = 0; y < 4; y++)
+      a[x][y] = (tx + 8 * y <= ty + kTY * x) ? s[ty + kTY * x][tx + 8 * y] : 0.0;
+  __syncthreads();  // everyone has its micro-tile before columns of `s` are overwritten
+#pragma unroll 1
+  for (int cc = 0; cc < 8; cc++) potrf_step<0>(a, s, colbuf, cc, ty, tx, g0, D, dinv_g, hdr);
+#pragma unroll 1
+  for (int cc = 0; cc < 8; cc++) potrf_step<1>(a, s, colbuf, cc, ty, tx, g0, D, dinv_g, hdr);
+#pragma unroll 1
+  for (int cc = 0; cc < 8; cc++) potrf_step<2>(a, s, colbuf, cc, ty, tx, g0, D, dinv_g, hdr);
+#pragma unroll 1
+  for (int cc = 0; cc < 8; cc++) potrf_step<3>(a, s, colbuf, cc, ty, tx, g0, D, dinv_g, hdr);
+}
+
+template <int YC>
+__device__ __forceinline__ void trsm_step(double (&a)[kRX][4], double (*sx)[NB + 1],
+                                          const double (*sl)[NB + 1], double* colbuf,
+                                          const double* dinv, int cc, int ty, int tx) {
+  const int c = 8 * YC + cc;
+  double* col = colbuf + (c & 1) * NB;
+  if (tx == cc) {  // column c of X is final after scaling by 1/L[c][c]
+    const double di = dinv[c];
 #pragma unroll
-      for (int c2 = c + 1; c2 < NB; c2++) a[c2] = fma(-xv, sl[c2][c], a[c2]);
+    for (int x = 0; x < kRX; x++) {
+      const double v = a[x][YC] * di;
+      col[ty + kTY * x] = v;
+      sx[ty + kTY * x][c] = v;
     }
-#pragma unroll
-    for (int c = 0; c < NB; c++) sx[r][c] = a[c];
   }
+  __syncthreads();
+  double xr[kRX], lc[4];
+#pragma unroll
+  for (int x = 0; x < kRX; x++) xr[x] = col[ty + kTY * x];
+#pragma unroll
+  for (int y = YC; y < 4; y++) lc[y] = sl[tx + 8 * y][c];
+  lc[YC] = (tx > cc) ? lc[YC] : 0.0;
+#pragma unroll
+  for (int x = 0; x < kRX; x++)
+#pragma unroll
+    for (int y = YC; y < 4; y++) a[x][y] = fma(-xr[x], lc[y], a[x][y]);
+}
+
+// X <- X * Ljj^-T for the 32x32 tile X in `sx`, Ljj in `sl`: same thread grid; per column step
+// the finished column of X is broadcast through the double-buffered shared vector.
+__device__ __forceinline__ void trsm_tile(double (*sx)[NB + 1], const double (*sl)[NB + 1],
+                                          double* colbuf, double* dinv,
+                                          const double* __restrict__ dinv_g) {
+  const int tid = threadIdx.x, ty = tid >> 3, tx = tid & 7;
+  if (tid < NB) dinv[tid] = __ldcg(dinv_g + tid);
+  double a[kRX][4];
+#pragma unroll
+  for (int x = 0; x < kRX; x++)
+#pragma unroll
+    for (int y = 0; y < 4; y++) a[x][y] = sx[ty + kTY * x][tx + 8 * y];
+  __syncthreads();
+#pragma unroll 1
+  for (int cc = 0; cc < 8; cc++) trsm_step<0>(a, sx, sl, colbuf, dinv, cc, ty, tx);
+#pragma unroll 1
+  for (int cc = 0; cc < 8; cc++) trsm_step<1>(a, sx, sl, colbuf, dinv, cc, ty, tx);
+#pragma unroll 1
+  for (int cc = 0; cc < 8; cc++) trsm_step<2>(a, sx, sl, colbuf, dinv, cc, ty, tx);
+#pragma unroll 1
+  for (int cc = 0; cc < 8; cc++) trsm_step<3>(a, sx, sl, colbuf, dinv, cc, ty, tx);
 }
 
 // Tile (i,j), i >= j:  A_ij <- (A_ij - sum_{k<j} L_ik L_jk^T) [chol | * L_jj^-T], then flag it.
 __device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, int epoch,
                                                double (*sA)[NB + 1], double (*sB)[NB + 1],
-                                               double* sv, int slot) {
+                                               double* sv, double* sred, int slot) {
   const int tid = threadIdx.x;
   const unsigned long long t_begin = a.trace ? gtimer() : 0ull;
-  const int ty = tid >> 3, tx = tid & 7;  // 4x4 micro-tile: rows ty+8x, cols tx+8y
-  double acc[4][4];
+  const int ty = tid >> 3, tx = tid & 7;  // micro-tile: rows ty+kTY*x, cols tx+8y
+  double acc[kRX][4];
 #pragma unroll
-  for (int x = 0; x < 4; x++)
+  for (int x = 0; x < kRX; x++)
 #pragma unroll
     for (int y = 0; y < 4; y++) acc[x][y] = 0.0;
   for (int k = 0; k < j; k++) {
@@ -226,11 +292,13 @@ __device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, 
     const double (*sR)[NB + 1] = (i != j) ? sB : sA;
 #pragma unroll 8
     for (int m = 0; m < NB; m++) {
-      double li[4], lj[4];
+      double li[kRX], lj[4];
 #pragma unroll
-      for (int x = 0; x < 4; x++) { li[x] = sA[ty + 8 * x][m]; lj[x] = sR[tx + 8 * x][m]; }
+      for (int x = 0; x < kRX; x++) li[x] = sA[ty + kTY * x][m];
 #pragma unroll
-      for (int x = 0; x < 4; x++)
+      for (int y = 0; y < 4; y++) lj[y] = sR[tx + 8 * y][m];
+#pragma unroll
+      for (int x = 0; x < kRX; x++)
 #pragma unroll
         for (int y = 0; y < 4; y++) acc[x][y] = fma(li[x], lj[y], acc[x][y]);
     }
@@ -239,10 +307,10 @@ __device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, 
   // own tile (assembled by the previous launch; nobody else touches it before the flag)
   double* dst = a.A + (size_t)i * NB * a.Dp + (size_t)j * NB;
 #pragma unroll
-  for (int x = 0; x < 4; x++)
+  for (int x = 0; x < kRX; x++)
 #pragma unroll
     for (int y = 0; y < 4; y++) {
-      const int r = ty + 8 * x, c = tx + 8 * y;
+      const int r = ty + kTY * x, c = tx + 8 * y;
       sA[r][c] = __ldcg(dst + (size_t)r * a.Dp + c) - acc[x][y];
     }
   __syncthreads();
@@ -254,7 +322,7 @@ __device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, 
     if (a.trace) t_ready = gtimer();
     load_tile(a.A, a.Dp, j, j, sB);
     __syncthreads();
-    trsm_tile(sA, sB, sv, a.x + a.Dp + j * NB);
+    trsm_tile(sA, sB, sv, sred, a.x + a.Dp + j * NB);
   }
   __syncthreads();
   for (int idx = tid; idx < NB * NB; idx += kCholThreads) {
@@ -270,7 +338,8 @@ __device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, 
 __device__ __forceinline__ void chol_back_task(const CholArgs& a, int c, int epoch,
                                                double (*sA)[NB + 1], double* sx, double* sred,
                                                int slot) {
-  const int tid = threadIdx.x, t = tid & 31, half = tid >> 5;
+  constexpr int kParts = kCholThreads / 32, kRows = NB / kParts;
+  const int tid = threadIdx.x, t = tid & 31, part = tid >> 5;
   const unsigned long long t_begin = a.trace ? gtimer() : 0ull;
   int* xflags = a.flags + a.nb * a.nb;
   wait_flag(a.flags + (a.nb - 1) * a.nb + c, epoch);  // row D of L (and, transitively, column c)
@@ -281,17 +350,20 @@ __device__ __forceinline__ void chol_back_task(const CholArgs& a, int c, int epo
     __syncthreads();
     const double* Lmc = a.A + (size_t)m * NB * a.Dp + (size_t)c * NB;
 #pragma unroll 4
-    for (int r = half * 16; r < half * 16 + 16; r++)
+    for (int r = part * kRows; r < part * kRows + kRows; r++)
       s = fma(__ldcg(Lmc + (size_t)r * a.Dp + t), sx[r], s);
     __syncthreads();
   }
   const unsigned long long t_ready = a.trace ? gtimer() : 0ull;
-  if (half == 1) sred[t] = s;
+  if (part > 0) sred[(part - 1) * NB + t] = s;
   load_tile(a.A, a.Dp, c, c, sA);
   __syncthreads();
   if (tid < NB) {
     const int g = c * NB + t;
-    double rhs = (g < a.D) ? __ldcg(a.A + (size_t)a.D * a.Dp + g) - (s + sred[t]) : 0.0;
+    double tot = s;
+#pragma unroll
+    for (int pp = 1; pp < kParts; pp++) tot += sred[(pp - 1) * NB + t];
+    double rhs = (g < a.D) ? __ldcg(a.A + (size_t)a.D * a.Dp + g) - tot : 0.0;
     const double dinv = __ldcg(a.x + a.Dp + g);
     double xo = 0.0;
 #pragma unroll
@@ -346,7 +418,7 @@ chol_dataflow_kernel(const CholArgs a) {
   if (a.hdr->done) return;
   __shared__ double sA[NB][NB + 1];
   __shared__ double sB[NB][NB + 1];
-  __shared__ double sv[NB], sred[NB];
+  __shared__ double sv[2 * NB], sred[(kCholThreads / 32) * NB];
   __shared__ float red[kCholThreads / 32];
   const int epoch = a.hdr->iters + 1;
   const int G = gridDim.x, cta = blockIdx.x;
@@ -355,7 +427,7 @@ chol_dataflow_kernel(const CholArgs a) {
   int t = 0;
   for (int j = 0; j < a.nb; j++)
     for (int i = j; i < a.nb; i++, t++)
-      if (t % G == cta) chol_tile_task(a, i, j, epoch, sA, sB, sv, t);
+      if (t % G == cta) chol_tile_task(a, i, j, epoch, sA, sB, sv, sred, t);
   // block columns of the back substitution, last to first (all after every tile)
   for (int c = a.nb - 1; c >= 0; c--)
     if (c % G == cta) {
