@@ -149,19 +149,21 @@ __device__ __forceinline__ void acc_row(float* h, float* g, float w, float e, co
 // sqrt_w = sigma^-1 sqrt(q) (gn_kernels.cu:963-978); |sqrt_w err| < k  <=>  wc err^2 < k^2.
 __device__ __forceinline__ float robust_weight(float wc, float err) {
   const float s2 = wc * err * err;
-  const float hub = s2 < 1.345f * 1.345f ? 1.0f : 1.345f * rsqrtf(s2);
-  return hub * wc;
+  // huber = 1 if s2 < k^2 else k / sqrt(s2)  ==  min(1, k * rsqrt(s2))   (rsqrt(0) = +inf)
+  return wc * fminf(1.0f, 1.345f * rsqrtf(s2));
 }
 
 template <int MODE>
 __device__ __forceinline__ void point_terms(const GnDev& prm, const float* R, const float* t,
                                             const float4 xi, const float4 xj, long long ind,
-                                            float q, bool vm, float* h, float* g) {
+                                            float qm, float* h, float* g) {
+  // qm: the match confidence Q, or -3e38 when valid_match is false / the lane is past the end
   // P = s_ij R_ij Xj + t_ij  (actSim3, gn_kernels.cu:207-219)
   const float Px = fmaf(R[0], xj.x, fmaf(R[1], xj.y, fmaf(R[2], xj.z, t[0])));
   const float Py = fmaf(R[3], xj.x, fmaf(R[4], xj.y, fmaf(R[5], xj.z, t[1])));
   const float Pz = fmaf(R[6], xj.x, fmaf(R[7], xj.y, fmaf(R[8], xj.z, t[2])));
-  const bool valid = vm & (q > prm.Q_thresh) & (xi.w > prm.C_thresh) & (xj.w > prm.C_thresh);
+  const bool valid = (qm > prm.Q_thresh) && (fminf(xi.w, xj.w) > prm.C_thresh);
+  const float q = valid ? qm : 0.f;  // weight numerator; 0 switches the point off
   if (MODE == M3R_GN_RAYS) {  // gn_kernels.cu:924-1089
     const float n2i = xi.x * xi.x + xi.y * xi.y + xi.z * xi.z;
     const float ni_inv = rsqrtf(n2i);
@@ -171,8 +173,8 @@ __device__ __forceinline__ void point_terms(const GnDev& prm, const float* R, co
     const float rx = Px * nj_inv, ry = Py * nj_inv, rz = Pz * nj_inv;
     const float e0 = rx - xi.x * ni_inv, e1 = ry - xi.y * ni_inv, e2 = rz - xi.z * ni_inv;
     const float e3 = nj - n2i * ni_inv;
-    const float wc_ray = valid ? q * prm.inv_var_a : 0.f;
-    const float wc_dist = valid ? q * prm.inv_var_b : 0.f;
+    const float wc_ray = q * prm.inv_var_a;
+    const float wc_dist = q * prm.inv_var_b;
     const float w0 = robust_weight(wc_ray, e0), w1 = robust_weight(wc_ray, e1);
     const float w2 = robust_weight(wc_ray, e2), w3 = robust_weight(wc_dist, e3);
     // d r / d P = (I - r r^T) / |P|
@@ -194,7 +196,7 @@ __device__ __forceinline__ void point_terms(const GnDev& prm, const float* R, co
     const bool valid_u = (u > prm.u_lo) && (u < prm.u_hi);
     const bool valid_v = (v > prm.v_lo) && (v < prm.v_hi);
     const float e0 = u - (float)u_t, e1 = v - (float)v_t, e2 = zj_log - zi_log;
-    const bool ok = valid & valid_u & valid_v & valid_z;
+    const bool ok = valid_u & valid_v & valid_z;
     const float wc_pix = ok ? q * prm.inv_var_a : 0.f;
     const float wc_dep = ok ? q * prm.inv_var_b : 0.f;
     const float w0 = robust_weight(wc_pix, e0), w1 = robust_weight(wc_pix, e1);
@@ -208,7 +210,7 @@ __device__ __forceinline__ void point_terms(const GnDev& prm, const float* R, co
     { const float J[7] = {0.f, 0.f, zinv, yz, -xz, 0.f, 1.f}; acc_row<0x5Cu>(h, g, w2, e2, J); }
   } else {  // points, gn_kernels.cu:567-674
     const float e0 = Px - xi.x, e1 = Py - xi.y, e2 = Pz - xi.z;
-    const float wc = valid ? q * prm.inv_var_a : 0.f;
+    const float wc = q * prm.inv_var_a;
     const float w0 = robust_weight(wc, e0), w1 = robust_weight(wc, e1), w2 = robust_weight(wc, e2);
     { const float J[7] = {1.f, 0.f, 0.f, 0.f, Pz, -Py, Px}; acc_row<0x71u>(h, g, w0, e0, J); }
     { const float J[7] = {0.f, 1.f, 0.f, -Pz, 0.f, Px, Py}; acc_row<0x6Au>(h, g, w1, e1, J); }
@@ -283,24 +285,23 @@ gn_accum_kernel(const GnDev prm, const float* __restrict__ Twc, const float4* __
   for (int base = p_begin + threadIdx.x; base < p_end; base += kAccThreads * kAccUnroll) {
     long long ind[kAccUnroll];
     float qv[kAccUnroll];
-    bool vm[kAccUnroll];
     float4 xj[kAccUnroll], xi[kAccUnroll];
 #pragma unroll
     for (int u = 0; u < kAccUnroll; u++) {
       const int k = base + u * kAccThreads;
       const bool in = k < p_end;
       const int kk = in ? k : p_begin;
-      vm[u] = in && (vm_e[kk] != 0);
-      ind[u] = vm[u] ? idx_e[kk] : 0;  // invalid matches gather pixel 0 (gn_kernels.cu:913-914)
-      qv[u] = in ? ld_stream_f(q_e + kk) : 0.f;
+      const bool vm = in && (vm_e[kk] != 0);
+      ind[u] = vm ? idx_e[kk] : 0;  // invalid matches gather pixel 0 (gn_kernels.cu:913-914)
+      const float qq = ld_stream_f(q_e + kk);
+      qv[u] = vm ? qq : -3.0e38f;   // fails q > Q_thresh for any finite threshold
       xj[u] = ld_stream_f4(xj_base + kk);
-      if (!in) qv[u] = -3.0e38f;  // fails q > Q_thresh for any finite threshold
     }
 #pragma unroll
     for (int u = 0; u < kAccUnroll; u++) xi[u] = __ldg(xi_base + ind[u]);
 #pragma unroll
     for (int u = 0; u < kAccUnroll; u++)
-      point_terms<MODE>(prm, R, t, xi[u], xj[u], ind[u], qv[u], vm[u], h, g);
+      point_terms<MODE>(prm, R, t, xi[u], xj[u], ind[u], qv[u], h, g);
   }
   block_reduce_store(h, g, part + ((size_t)el * S + split) * kGnPartStride);
 }
@@ -422,9 +423,9 @@ gn_accum_stream_kernel(const GnDev prm, const float* __restrict__ Twc, const flo
       const int sl = slot_of(it, u);
       const int s0 = sl < 0 ? 0 : sl;  // past-the-end lanes re-read slot 0 with weight 0
       const bool vm = sl >= 0 && buf[kOffVm + s0] != 0;
-      const float qv = sl >= 0 ? reinterpret_cast<const float*>(buf + kOffQ)[s0] : -3.0e38f;
+      const float qv = vm ? reinterpret_cast<const float*>(buf + kOffQ)[s0] : -3.0e38f;
       const float4 xj = reinterpret_cast<const float4*>(buf)[s0];
-      point_terms<MODE>(prm, R, t, xi[u], xj, (long long)ind[u], qv, vm, h, g);
+      point_terms<MODE>(prm, R, t, xi[u], xj, (long long)ind[u], qv, h, g);
     }
     __syncthreads();  // every thread is done with stage `it`: its buffer may be refilled
     if (tid == 0 && it + kStages < T) issue(it + kStages);
