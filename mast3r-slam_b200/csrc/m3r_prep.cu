@@ -20,6 +20,9 @@ __device__ __forceinline__ int reflect(int i, int n) {  // F.pad(mode="reflect")
 __global__ void __launch_bounds__(kPrepTX * kPrepTY)
 prep_rays_kernel(const float* __restrict__ X11, int H, int W, float* __restrict__ out) {
   __shared__ float tile[kPrepTY + 2][kPrepTX + 2][3];
+  // output staging: one tile row is kPrepTX*9 contiguous floats in the (b,H,W,9) image, written
+  // back as coalesced 16-B words (9 scalar 36-B-strided stores per thread kept the LSU 69 % busy)
+  __shared__ __align__(16) float stage[kPrepTY][kPrepTX * 9];
   const int x0 = blockIdx.x * kPrepTX, y0 = blockIdx.y * kPrepTY;
   const float* Xb = X11 + (size_t)blockIdx.z * H * W * 3;
   const int tid = threadIdx.y * kPrepTX + threadIdx.x;
@@ -33,19 +36,37 @@ prep_rays_kernel(const float* __restrict__ X11, int H, int W, float* __restrict_
     tile[ty][tx][0] = a / nrm; tile[ty][tx][1] = b / nrm; tile[ty][tx][2] = c / nrm;
   }
   __syncthreads();
-  const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
-  if (x >= W || y >= H) return;
-  const int tx = threadIdx.x + 1, ty = threadIdx.y + 1;
-  float* o = out + (((size_t)blockIdx.z * H + y) * W + x) * 9;
-  const float k3 = 3.0f / 32.0f, k10 = 10.0f / 32.0f;  // (1/32)*[-3,0,3;-10,0,10;-3,0,3]
+  {
+    const int tx = threadIdx.x + 1, ty = threadIdx.y + 1;
+    float* o = &stage[threadIdx.y][threadIdx.x * 9];
+    const float k3 = 3.0f / 32.0f, k10 = 10.0f / 32.0f;  // (1/32)*[-3,0,3;-10,0,10;-3,0,3]
 #pragma unroll
-  for (int c = 0; c < 3; c++) {
-    const float tl = tile[ty - 1][tx - 1][c], tc = tile[ty - 1][tx][c], tr = tile[ty - 1][tx + 1][c];
-    const float ml = tile[ty][tx - 1][c], mr = tile[ty][tx + 1][c];
-    const float bl = tile[ty + 1][tx - 1][c], bc = tile[ty + 1][tx][c], br = tile[ty + 1][tx + 1][c];
-    o[c] = tile[ty][tx][c];
-    o[3 + c] = -k3 * tl + k3 * tr - k10 * ml + k10 * mr - k3 * bl + k3 * br;   // gx
-    o[6 + c] = -k3 * tl - k10 * tc - k3 * tr + k3 * bl + k10 * bc + k3 * br;   // gy
+    for (int c = 0; c < 3; c++) {
+      const float tl = tile[ty - 1][tx - 1][c], tc = tile[ty - 1][tx][c], tr = tile[ty - 1][tx + 1][c];
+      const float ml = tile[ty][tx - 1][c], mr = tile[ty][tx + 1][c];
+      const float bl = tile[ty + 1][tx - 1][c], bc = tile[ty + 1][tx][c], br = tile[ty + 1][tx + 1][c];
+      o[c] = tile[ty][tx][c];
+      o[3 + c] = -k3 * tl + k3 * tr - k10 * ml + k10 * mr - k3 * bl + k3 * br;   // gx
+      o[6 + c] = -k3 * tl - k10 * tc - k3 * tr + k3 * bl + k10 * bc + k3 * br;   // gy
+    }
+  }
+  __syncthreads();
+  const int cols = min(kPrepTX, W - x0);   // valid pixels of this tile row
+  const int rows = min(kPrepTY, H - y0);
+  const int nfl = cols * 9;                // valid floats per row
+  float* dst0 = out + (((size_t)blockIdx.z * H + y0) * W + x0) * 9;
+  const size_t row_stride = (size_t)W * 9;
+  if ((nfl & 3) == 0 && (row_stride & 3) == 0 && ((reinterpret_cast<uintptr_t>(dst0) & 15) == 0)) {
+    const int per_row = nfl / 4;
+    for (int i = tid; i < rows * per_row; i += kPrepTX * kPrepTY) {
+      const int r = i / per_row, k = i - r * per_row;
+      reinterpret_cast<float4*>(dst0 + r * row_stride)[k] = reinterpret_cast<const float4*>(stage[r])[k];
+    }
+  } else {
+    for (int i = tid; i < rows * nfl; i += kPrepTX * kPrepTY) {
+      const int r = i / nfl, k = i - r * nfl;
+      dst0[r * row_stride + k] = stage[r][k];
+    }
   }
 }
 
