@@ -361,10 +361,10 @@ def bench_gn(be, synth, dev, rank, world, peak, barrier, max_over_ranks):
         sl = slice(e0, e1)
         idx_l, val_l, Q_l = g["idx"][sl].contiguous(), g["valid"][sl].contiguous(), g["Q"][sl].contiguous()
 
-        def run():
+        def run(p2p=True):
             T = g["Twc"].clone()
             be.gauss_newton_sharded(prm, T, g["Xs"], g["Cs"], g["ii"], g["jj"], idx_l, val_l, Q_l, e0,
-                                    iters, 0.0, edge_counts=counts)
+                                    iters, 0.0, edge_counts=counts, p2p=p2p)
             return T
     for _ in range(3):
         run()
@@ -377,15 +377,27 @@ def bench_gn(be, synth, dev, rank, world, peak, barrier, max_over_ranks):
     barrier()
     ms = max_over_ranks(a.elapsed_time(z)) / reps
     if world > 1:  # the sharded solve must reproduce the single-GPU poses bit for bit
+        for _ in range(2):
+            run(p2p=False)
+        barrier()
+        a.record()
+        for _ in range(reps):
+            run(p2p=False)
+        z.record()
+        barrier()
+        ms_nccl = max_over_ranks(a.elapsed_time(z)) / reps
+        out["gn_rays_nccl_allgather_exchange"] = {"iters_per_s": iters / (ms_nccl * 1e-3), "ms_per_solve": ms_nccl}
+        T_nc = run(p2p=False)
         T_sh = run()
         T_one = g["Twc"].clone()
         be.gauss_newton_rays(T_one, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
                              0.003, 10.0, 0.0, 1.5, iters, 0.0)
-        same = torch.tensor([1 if torch.equal(T_sh, T_one) else 0], device=dev)
+        same = torch.tensor([1 if (torch.equal(T_sh, T_one) and torch.equal(T_nc, T_one)) else 0], device=dev)
         dist.all_reduce(same, op=dist.ReduceOp.MIN)
         out["gn_rays_sharded_equals_single_gpu"] = bool(same.item())
     out["gn_rays"] = {"workload": "gauss_newton_rays N=32, 200 directed edges, 512x384, 10 iterations "
-                                  "(BASELINE configs[2])" + (f", edge-sharded x{world}" if world > 1 else ""),
+                                  "(BASELINE configs[2])" + (f", edge-sharded x{world}, block exchange fused into the "
+                                                             "kernels over NVLink peer memory" if world > 1 else ""),
                       "iters_per_s": iters / (ms * 1e-3), "ms_per_solve": ms}
     if world == 1:
         # accumulation kernel alone (the HBM-bound part): 45 B per (directed edge, point)
@@ -466,7 +478,8 @@ def bench_gn_large(be, synth, dev, rank, world, peak, barrier, max_over_ranks):
 
     def run():
         T = T0.clone()
-        be.gauss_newton_sharded(prm, T, Xs, Cs, ii_g, jj_g, idx, valid, Q, e0, iters, 0.0, edge_counts=ecounts)
+        be.gauss_newton_sharded(prm, T, Xs, Cs, ii_g, jj_g, idx, valid, Q, e0, iters, 0.0, edge_counts=ecounts,
+                                p2p=True)
         return T
     run()
     barrier()

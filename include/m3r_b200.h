@@ -197,6 +197,30 @@ int m3r_gn_accumulate(const m3r_gn_params* prm, const float* Twc,
 int m3r_gn_solve_step(float* Twc, const double* blocks, int num_poses, int num_edges,
                       float delta_thresh, float* dx, void* workspace,
                       size_t workspace_bytes, m3r_stream_t stream);
+/* Edge-sharded solve with the block exchange FUSED into the kernels over NVLink peer memory
+ * (no collective call): every process maps every other process's `blocks` buffer and a small
+ * int32 flag array (CUDA peer / symmetric memory; torch.distributed._symmetric_memory in the
+ * Python binding).  m3r_gn_accumulate_p2p stores each finished per-edge block straight into
+ * ALL processes' buffers (plain stores to the peer pointers) and then raises flags[rank] = epoch
+ * in every process; m3r_gn_solve_step_p2p waits, on the device, until all `world` flags of its
+ * own array have reached `epoch` before it assembles.  `epoch` must increase by one per
+ * iteration across the whole life of the buffers (the caller counts).  The wait is bounded
+ * (about 10 s): on expiry the step becomes zero like a failed factorisation. */
+#define M3R_MAX_PEERS 16
+typedef struct m3r_gn_peers {
+  double* blocks[M3R_MAX_PEERS]; /* blocks[r]: rank r's (num_edges*56) buffer as mapped HERE  */
+  int* flags[M3R_MAX_PEERS];     /* flags[r]: rank r's int32[world] flag array as mapped HERE */
+  int world, rank;
+  int epoch;
+} m3r_gn_peers;
+int m3r_gn_accumulate_p2p(const m3r_gn_params* prm, const float* Twc,
+                          const int64_t* idx_ii2jj, const uint8_t* valid_match, const float* Q,
+                          int num_poses, int n, int num_edges, int edge_begin, int edge_count,
+                          const m3r_gn_peers* peers, void* workspace, size_t workspace_bytes,
+                          m3r_stream_t stream);
+int m3r_gn_solve_step_p2p(float* Twc, const m3r_gn_peers* peers, int num_poses, int num_edges,
+                          float delta_thresh, float* dx, void* workspace,
+                          size_t workspace_bytes, m3r_stream_t stream);
 /* Device pointer (inside workspace) of the int32 convergence flag: 0 running, 1 done. */
 int* m3r_gn_done_flag(void* workspace);
 /* Device pointer (inside workspace) of the per-edge block buffer (num_edges*56 doubles). */

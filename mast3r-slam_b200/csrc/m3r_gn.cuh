@@ -26,7 +26,7 @@ struct GnHeader {
   int done;        // 1 once |dx| < delta_thresh (the reference's `break`)
   int chol_fail;   // set by the factorisation of the current iteration
   int iters;       // iterations actually executed
-  int pad;
+  int peer_timeout;  // a peer's blocks did not arrive in time (m3r_gn_solve_step_p2p): zero steps
 };
 
 struct GnLayout {
@@ -88,8 +88,10 @@ inline GnLayout gn_layout(int N, int M, int Ml, int n) {
 template <typename T>
 inline T* ws_ptr(void* ws, size_t off) { return reinterpret_cast<T*>(static_cast<char*>(ws) + off); }
 
-// m3r_gn_solve.cu
+// m3r_gn_solve.cu.  wait_flags != nullptr: before assembling, wait on the device until all
+// `wait_world` entries of wait_flags have reached `wait_epoch` (peer-memory block exchange).
 int gn_solve_launch(float* Twc, const double* blocks, int N, int M, float delta_thresh, float* dx,
-                    void* ws, const GnLayout& L, cudaStream_t st);
+                    void* ws, const GnLayout& L, cudaStream_t st, const int* wait_flags = nullptr,
+                    int wait_world = 0, int wait_epoch = 0);
 
 }  // namespace m3r

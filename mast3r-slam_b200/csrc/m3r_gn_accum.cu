@@ -57,7 +57,7 @@ gn_index_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, 
   __shared__ int64_t skeys[kIdxSmemKeys];
   __shared__ int scan[kIdxThreads];
   const int tid = threadIdx.x;
-  if (tid == 0) { hdr->done = 0; hdr->chol_fail = 0; hdr->iters = 0; hdr->pad = 0; }
+  if (tid == 0) { hdr->done = 0; hdr->chol_fail = 0; hdr->iters = 0; hdr->peer_timeout = 0; }
   for (int t = tid; t < nflags; t += kIdxThreads) flags[t] = 0;
   int64_t* buf = (P <= kIdxSmemKeys) ? skeys : keys;
   const int64_t kMax = 0x7fffffffffffffffLL;
@@ -436,10 +436,15 @@ gn_accum_stream_kernel(const GnDev prm, const float* __restrict__ Twc, const flo
 // Per edge: sum the S partials (fp64, fixed order), apply the adjoint of T_i once:
 //   Jj = J_local * A with A[k][:] = apply_Sim3_adj_inv(T_i, e_k)   (gn_kernels.cu:277-297)
 //   S = A^T H_local A,  v = A^T g_local.
+// With peers.world > 1 the block is stored into EVERY process's buffer through the NVLink peer
+// mappings (the exchange step of the sharded solve, fused into the producer).
+struct GnPeerDst { double* blocks[M3R_MAX_PEERS]; int world; };
+
 __global__ void __launch_bounds__(64)
 gn_edge_finish_kernel(const float* __restrict__ Twc, const int* __restrict__ ie,
                       const float* __restrict__ part, int edge_begin, int S,
-                      double* __restrict__ blocks, const GnHeader* __restrict__ hdr) {
+                      double* __restrict__ blocks, const GnPeerDst dst,
+                      const GnHeader* __restrict__ hdr) {
   if (hdr->done) return;
   __shared__ double Hl[7][7], gl[7], A[7][7], HA[7][7];
   const int el = blockIdx.x, e = edge_begin + el, t = threadIdx.x;
@@ -475,13 +480,26 @@ gn_edge_finish_kernel(const float* __restrict__ Twc, const int* __restrict__ ie,
     const int a = t / 7, b = t % 7;
     double s = 0.0;
     for (int k = 0; k < 7; k++) s += A[k][a] * HA[k][b];
-    blocks[(size_t)e * kGnBlock + t] = s;
+    if (dst.world <= 1) blocks[(size_t)e * kGnBlock + t] = s;
+    else for (int r = 0; r < dst.world; r++) dst.blocks[r][(size_t)e * kGnBlock + t] = s;
   } else if (t < 56) {
     const int m = t - 49;
     double s = 0.0;
     for (int k = 0; k < 7; k++) s += gl[k] * A[k][m];
-    blocks[(size_t)e * kGnBlock + t] = s;
+    if (dst.world <= 1) blocks[(size_t)e * kGnBlock + t] = s;
+    else for (int r = 0; r < dst.world; r++) dst.blocks[r][(size_t)e * kGnBlock + t] = s;
   }
+  if (dst.world > 1) __threadfence_system();  // peer stores ordered before the flag that follows
+}
+
+// Raises flags[rank] = epoch in every process (one warp; launched behind the finish kernel).
+struct GnPeerFlags { int* flags[M3R_MAX_PEERS]; int world, rank, epoch; };
+__global__ void gn_peer_signal_kernel(const GnPeerFlags f, const GnHeader* __restrict__ hdr) {
+  if (hdr->done) return;
+  __threadfence_system();
+  const int r = threadIdx.x;
+  if (r < f.world)
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(f.flags[r] + f.rank), "r"(f.epoch) : "memory");
 }
 
 static GnDev make_dev_params(const m3r_gn_params* p) {
@@ -539,15 +557,38 @@ extern "C" int m3r_gn_prepare(const float* Xs, const float* Cs, const int64_t* i
   return after_launch();
 }
 
-extern "C" int m3r_gn_accumulate(const m3r_gn_params* prm, const float* Twc,
-                                 const int64_t* idx_ii2jj, const uint8_t* valid_match,
-                                 const float* Q, int num_poses, int n, int num_edges,
-                                 int edge_begin, int edge_count, double* blocks, void* workspace,
-                                 size_t workspace_bytes, m3r_stream_t stream) {
+static int gn_accumulate_impl(const m3r_gn_params* prm, const float* Twc,
+                              const int64_t* idx_ii2jj, const uint8_t* valid_match,
+                              const float* Q, int num_poses, int n, int num_edges,
+                              int edge_begin, int edge_count, double* blocks,
+                              const m3r_gn_peers* peers, void* workspace,
+                              size_t workspace_bytes, m3r_stream_t stream) {
   if (!prm || num_poses < 1 || n <= 0 || num_edges <= 0 || edge_begin < 0 || edge_count < 0 ||
       edge_begin + edge_count > num_edges || edge_count > 65535)
     return M3R_EINVAL;
-  if (edge_count == 0) return M3R_OK;
+  GnPeerDst dst;
+  dst.world = 0;
+  if (peers) {
+    if (peers->world < 1 || peers->world > M3R_MAX_PEERS || peers->rank < 0 || peers->rank >= peers->world)
+      return M3R_EINVAL;
+    dst.world = peers->world;
+    for (int r = 0; r < peers->world; r++) {
+      if (!peers->blocks[r] || !peers->flags[r]) return M3R_EINVAL;
+      dst.blocks[r] = peers->blocks[r];
+    }
+    blocks = peers->blocks[peers->rank];
+  }
+  if (edge_count == 0) {
+    if (peers && peers->world > 1 && workspace) {  // nothing to add, but the peers still wait for this rank
+      GnPeerFlags f;
+      f.world = peers->world; f.rank = peers->rank; f.epoch = peers->epoch;
+      for (int r = 0; r < peers->world; r++) f.flags[r] = peers->flags[r];
+      const GnLayout L0 = gn_layout(num_poses, num_edges, 0, n);
+      gn_peer_signal_kernel<<<1, 32, 0, as_stream(stream)>>>(f, ws_ptr<GnHeader>(workspace, L0.hdr));
+      return after_launch();
+    }
+    return M3R_OK;
+  }
   if (!Twc || !idx_ii2jj || !valid_match || !Q || !blocks || !workspace) return M3R_EINVAL;
   if (prm->sigma_a == 0.f) return M3R_EINVAL;
   // the partial buffer is sized for `local_edges`; accept any slice up to that size
@@ -591,8 +632,49 @@ extern "C" int m3r_gn_accumulate(const m3r_gn_params* prm, const float* Twc,
   M3R_TRY(after_launch());
   gn_edge_finish_kernel<<<edge_count, 64, 0, st>>>(Twc, ws_ptr<int>(workspace, L.ie),
                                                    ws_ptr<float>(workspace, L.part), edge_begin,
-                                                   L.S, blocks, hdr);
-  return after_launch();
+                                                   L.S, blocks, dst, hdr);
+  M3R_TRY(after_launch());
+  if (peers && peers->world > 1) {
+    GnPeerFlags f;
+    f.world = peers->world; f.rank = peers->rank; f.epoch = peers->epoch;
+    for (int r = 0; r < peers->world; r++) f.flags[r] = peers->flags[r];
+    gn_peer_signal_kernel<<<1, 32, 0, st>>>(f, hdr);
+    M3R_TRY(after_launch());
+  }
+  return M3R_OK;
+}
+
+extern "C" int m3r_gn_accumulate(const m3r_gn_params* prm, const float* Twc,
+                                 const int64_t* idx_ii2jj, const uint8_t* valid_match,
+                                 const float* Q, int num_poses, int n, int num_edges,
+                                 int edge_begin, int edge_count, double* blocks, void* workspace,
+                                 size_t workspace_bytes, m3r_stream_t stream) {
+  return gn_accumulate_impl(prm, Twc, idx_ii2jj, valid_match, Q, num_poses, n, num_edges, edge_begin,
+                            edge_count, blocks, nullptr, workspace, workspace_bytes, stream);
+}
+
+extern "C" int m3r_gn_accumulate_p2p(const m3r_gn_params* prm, const float* Twc,
+                                     const int64_t* idx_ii2jj, const uint8_t* valid_match,
+                                     const float* Q, int num_poses, int n, int num_edges,
+                                     int edge_begin, int edge_count, const m3r_gn_peers* peers,
+                                     void* workspace, size_t workspace_bytes, m3r_stream_t stream) {
+  if (!peers) return M3R_EINVAL;
+  return gn_accumulate_impl(prm, Twc, idx_ii2jj, valid_match, Q, num_poses, n, num_edges, edge_begin,
+                            edge_count, nullptr, peers, workspace, workspace_bytes, stream);
+}
+
+extern "C" int m3r_gn_solve_step_p2p(float* Twc, const m3r_gn_peers* peers, int num_poses,
+                                     int num_edges, float delta_thresh, float* dx, void* workspace,
+                                     size_t workspace_bytes, m3r_stream_t stream) {
+  if (!peers || peers->world < 1 || peers->world > M3R_MAX_PEERS || peers->rank < 0 ||
+      peers->rank >= peers->world)
+    return M3R_EINVAL;
+  if (num_poses < 2 || num_edges <= 0 || !Twc || !dx || !workspace) return M3R_EINVAL;
+  const GnLayout L = gn_layout(num_poses, num_edges, 0, 0);
+  if (workspace_bytes < L.xc) return M3R_EWORKSPACE;
+  return gn_solve_launch(Twc, peers->blocks[peers->rank], num_poses, num_edges, delta_thresh, dx,
+                         workspace, L, as_stream(stream), peers->flags[peers->rank], peers->world,
+                         peers->epoch);
 }
 
 extern "C" int m3r_gn_solve_step(float* Twc, const double* blocks, int num_poses, int num_edges,

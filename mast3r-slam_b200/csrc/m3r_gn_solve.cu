@@ -36,8 +36,26 @@ __global__ void __launch_bounds__(64)
 gn_assemble_kernel(const double* __restrict__ blocks, const int* __restrict__ ie,
                    const int* __restrict__ je, const int* __restrict__ row_ptr,
                    const int* __restrict__ adj, int M, int N, int D, int Dp, double* __restrict__ A,
-                   GnHeader* hdr) {
+                   GnHeader* hdr, const int* wait_flags, int wait_world, int wait_epoch) {
   if (hdr->done) return;
+  if (wait_flags) {  // peer-memory exchange: all ranks' blocks of this iteration must have landed
+    if (threadIdx.x == 0) {
+      unsigned long long t0;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+      for (int r = 0; r < wait_world; r++) {
+        for (;;) {
+          int v;
+          asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(wait_flags + r) : "memory");
+          if (v - wait_epoch >= 0) break;
+          unsigned long long t1;
+          asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+          if (t1 - t0 > 10000000000ull) { hdr->peer_timeout = 1; break; }  // 10 s: give up, zero step
+          __nanosleep(64);
+        }
+      }
+    }
+    __syncthreads();
+  }
   const int t = threadIdx.x;
   const int r = blockIdx.x;  // free index; pose row r+1
   if (r == N - 1) {          // augmented row diagonal + identity padding
@@ -63,12 +81,12 @@ gn_assemble_kernel(const double* __restrict__ blocks, const int* __restrict__ ie
     const int e = role_i ? slot : slot - M;
     const int other = (role_i ? je[e] : ie[e]) - 1;  // free index of the other end (-1: fixed)
     if (t < 49) {
-      const double v = blocks[(size_t)e * kGnBlock + t];
+      const double v = __ldcg(blocks + (size_t)e * kGnBlock + t);
       acc += v;
       if (other == r) acc -= v;  // self edge
       else if (other >= 0 && other < r) A[(size_t)(7 * r + k) * Dp + 7 * other + l] -= v;
     } else if (t < 56) {
-      const double v = blocks[(size_t)e * kGnBlock + t];
+      const double v = __ldcg(blocks + (size_t)e * kGnBlock + t);
       acc += role_i ? -v : v;
     }
   }
@@ -384,7 +402,8 @@ __device__ __forceinline__ void gn_update_block(float* __restrict__ Twc, const d
                                                 int N, int D, float delta_thresh,
                                                 float* __restrict__ dx, GnHeader* hdr, float* red) {
   const int nthr = blockDim.x, tid = threadIdx.x;
-  const bool fail = *reinterpret_cast<volatile int*>(&hdr->chol_fail) != 0;
+  const bool fail = *reinterpret_cast<volatile int*>(&hdr->chol_fail) != 0 ||
+                    *reinterpret_cast<volatile int*>(&hdr->peer_timeout) != 0;
   float ss = 0.f;
   for (int i = tid; i < D; i += nthr) {
     const float v = fail ? 0.f : (float)(-__ldcg(x + i));
@@ -470,13 +489,14 @@ static int chol_max_ctas() {
 }
 
 int gn_solve_launch(float* Twc, const double* blocks, int N, int M, float delta_thresh, float* dx,
-                    void* ws, const GnLayout& L, cudaStream_t st) {
+                    void* ws, const GnLayout& L, cudaStream_t st, const int* wait_flags,
+                    int wait_world, int wait_epoch) {
   GnHeader* hdr = ws_ptr<GnHeader>(ws, L.hdr);
   double* A = ws_ptr<double>(ws, L.A);
   const int D = L.D, Dp = L.Dp, nb = Dp / NB;
   gn_assemble_kernel<<<N, 64, 0, st>>>(blocks, ws_ptr<int>(ws, L.ie), ws_ptr<int>(ws, L.je),
                                        ws_ptr<int>(ws, L.row_ptr), ws_ptr<int>(ws, L.adj), M, N, D,
-                                       Dp, A, hdr);
+                                       Dp, A, hdr, wait_flags, wait_world, wait_epoch);
   M3R_TRY(after_launch());
   CholArgs a;
   a.A = A; a.Dp = Dp; a.D = D; a.nb = nb;

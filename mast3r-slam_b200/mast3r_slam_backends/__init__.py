@@ -32,6 +32,14 @@ class _GNParams(C.Structure):
                 ("z_eps", C.c_float)]
 
 
+MAX_PEERS = 16
+
+
+class _GNPeers(C.Structure):
+    _fields_ = [("blocks", C.c_void_p * MAX_PEERS), ("flags", C.c_void_p * MAX_PEERS),
+                ("world", C.c_int), ("rank", C.c_int), ("epoch", C.c_int)]
+
+
 GN_RAYS, GN_CALIB, GN_POINTS = 0, 1, 2
 
 EXPORTS = [
@@ -40,7 +48,7 @@ EXPORTS = [
     "m3r_match_iter_proj_fused", "m3r_match_refine_fused", "m3r_pose_retr",
     "m3r_gn_workspace_bytes", "m3r_gauss_newton", "m3r_gn_prepare", "m3r_gn_accumulate",
     "m3r_gn_solve_step", "m3r_gn_done_flag", "m3r_gn_blocks", "m3r_track_workspace_bytes",
-    "m3r_track_ray_dist", "m3r_track_calib", "m3r_debug_chol_trace", "m3r_edge_build", "m3r_pointmap_update",
+    "m3r_track_ray_dist", "m3r_track_calib", "m3r_debug_chol_trace", "m3r_edge_build", "m3r_pointmap_update", "m3r_gn_accumulate_p2p", "m3r_gn_solve_step_p2p",
 ]
 
 
@@ -83,6 +91,9 @@ def _load():
                                        vp, vp, sz, vp]
     lib.m3r_track_calib.argtypes = [vp, vp, vp, vp, vp, i32, f32, f32, f32, f32, i32, i32, i32, f32,
                                     f32, f32, f32, i32, f32, f32, vp, vp, vp, vp, sz, vp]
+    pp = C.POINTER(_GNPeers)
+    lib.m3r_gn_accumulate_p2p.argtypes = [gp, vp, vp, vp, vp, i32, i32, i32, i32, i32, pp, vp, sz, vp]
+    lib.m3r_gn_solve_step_p2p.argtypes = [vp, pp, i32, i32, f32, vp, vp, sz, vp]
     lib.m3r_edge_build.argtypes = [vp, vp, vp, vp, i32, i32, f32, vp, vp, vp]
     lib.m3r_pointmap_update.argtypes = [vp, vp, vp, vp, vp, i32, i32, vp]
     return lib
@@ -300,7 +311,8 @@ class GNSolver:
     list: prepare once, then per iteration accumulate() -> (exchange blocks) -> solve_step().
     `ii`/`jj` are the FULL edge lists; idx/valid/Q are the LOCAL slice."""
 
-    def __init__(self, prm, Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_local, edge_begin=0):
+    def __init__(self, prm, Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_local, edge_begin=0,
+                 peers=None):
         (self.Twc, self.Xs, self.Cs, self.ii, self.jj, self.idx, self.vm, self.Q, self.N,
          self.n) = _gn_inputs(Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_local)
         self.prm = prm
@@ -311,13 +323,24 @@ class GNSolver:
         with torch.cuda.device(dev):
             self.nbytes = _lib.m3r_gn_workspace_bytes(self.N, self.M, self.Ml, self.n)
             self.ws = torch.empty((self.nbytes,), dtype=torch.uint8, device=dev)
-            self.blocks = torch.zeros((self.M, 56), dtype=torch.float64, device=dev)
+            self.peers = peers  # PeerBlocks: exchange fused into the kernels over NVLink peer memory
+            self.blocks = peers.blocks if peers is not None else torch.zeros((self.M, 56), dtype=torch.float64,
+                                                                              device=dev)
             self.dx = torch.zeros((self.N - 1, 7), dtype=torch.float32, device=dev)
             _check(_lib.m3r_gn_prepare(_ptr(self.Xs), _ptr(self.Cs), _ptr(self.ii), _ptr(self.jj),
                                        self.N, self.n, self.M, self.Ml, _ptr(self.ws), self.nbytes,
                                        _stream(Twc)), "gn_prepare")
 
     def accumulate(self):
+        if self.peers is not None:
+            with torch.cuda.device(self.Twc.device):
+                _check(_lib.m3r_gn_accumulate_p2p(C.byref(self.prm), _ptr(self.Twc), _ptr(self.idx),
+                                                  _ptr(self.vm), _ptr(self.Q), self.N, self.n, self.M,
+                                                  self.edge_begin, self.Ml, C.byref(self.peers.next_epoch()),
+                                                  _ptr(self.ws), self.nbytes, _stream(self.Twc)),
+                       "gn_accumulate_p2p")
+            self.blocks = self.peers.blocks
+            return self.blocks
         with torch.cuda.device(self.Twc.device):
             _check(_lib.m3r_gn_accumulate(C.byref(self.prm), _ptr(self.Twc), _ptr(self.idx),
                                           _ptr(self.vm), _ptr(self.Q), self.N, self.n, self.M,
@@ -326,6 +349,12 @@ class GNSolver:
         return self.blocks
 
     def solve_step(self, delta_thresh):
+        if self.peers is not None:
+            with torch.cuda.device(self.Twc.device):
+                _check(_lib.m3r_gn_solve_step_p2p(_ptr(self.Twc), C.byref(self.peers.struct), self.N, self.M,
+                                                  float(delta_thresh), _ptr(self.dx), _ptr(self.ws),
+                                                  self.nbytes, _stream(self.Twc)), "gn_solve_step_p2p")
+            return self.dx
         with torch.cuda.device(self.Twc.device):
             _check(_lib.m3r_gn_solve_step(_ptr(self.Twc), _ptr(self.blocks), self.N, self.M,
                                           float(delta_thresh), _ptr(self.dx), _ptr(self.ws),
@@ -381,8 +410,61 @@ def exchange_blocks(blocks, begin, count, counts, group=None):
     return blocks
 
 
+class PeerBlocks:
+    """Per-edge block buffer + arrival flags of every rank, mapped into every process (NVLink peer
+    memory via torch.distributed._symmetric_memory).  With it the block exchange of the sharded solve
+    needs no collective call: the producing kernel stores into all ranks' buffers and raises a flag,
+    the consuming kernel waits for the flags on the device (include/m3r_b200.h, m3r_gn_peers).
+    Construction is collective (every rank of `group`, same num_edges); reuse the object across solves."""
+
+    _cache = {}
+
+    def __init__(self, num_edges, device, group=None):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+
+        group = group or dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if self.world > MAX_PEERS:
+            raise RuntimeError(f"PeerBlocks supports at most {MAX_PEERS} ranks")
+        with torch.cuda.device(device):
+            # two buffers, used alternately by epoch parity: a fast rank may already push iteration
+            # k+1 while a slow one still assembles iteration k; iteration k+2 cannot start anywhere
+            # before every rank has raised its flag for k+1, i.e. has finished reading k
+            self.buffers = symm.empty((2, int(num_edges), 56), dtype=torch.float64, device=device)
+            self.blocks = self.buffers[0]
+            self.flags = symm.empty((64,), dtype=torch.int32, device=device)
+            self.buffers.zero_(); self.flags.zero_()
+            torch.cuda.synchronize(device)
+            hb, hf = symm.rendezvous(self.buffers, group), symm.rendezvous(self.flags, group)
+            hf.barrier()
+        self._handles = (hb, hf)
+        self.struct = _GNPeers()
+        self._base = [int(hb.buffer_ptrs[r]) for r in range(self.world)]
+        self._stride = int(num_edges) * 56 * 8
+        for r in range(self.world):
+            self.struct.blocks[r] = self._base[r]
+            self.struct.flags[r] = hf.buffer_ptrs[r]
+        self.struct.world, self.struct.rank, self.struct.epoch = self.world, self.rank, 0
+
+    def next_epoch(self):
+        self.struct.epoch += 1
+        par = self.struct.epoch & 1
+        for r in range(self.world):
+            self.struct.blocks[r] = self._base[r] + par * self._stride
+        self.blocks = self.buffers[par]
+        return self.struct
+
+    @classmethod
+    def get(cls, num_edges, device, group=None):
+        key = (int(num_edges), str(device), id(group))
+        if key not in cls._cache:
+            cls._cache[key] = cls(num_edges, device, group)
+        return cls._cache[key]
+
+
 def gauss_newton_sharded(prm, Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_local, edge_begin,
-                         max_iter, delta_thresh, group=None, edge_counts=None):
+                         max_iter, delta_thresh, group=None, edge_counts=None, p2p=False):
     """Edge-sharded solve: each rank accumulates its contiguous slice of the directed edges
     (`shard_edges`), the 56-double per-edge blocks are exchanged with ONE all-gather per iteration
     (`exchange_blocks`), then every rank runs the identical replicated assembly + Cholesky +
@@ -390,13 +472,14 @@ def gauss_newton_sharded(prm, Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_loc
     because an edge's block does not depend on which rank computed it."""
     import torch.distributed as dist
 
-    solver = GNSolver(prm, Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_local, edge_begin)
     world = dist.get_world_size(group) if dist.is_initialized() else 1
-    if world > 1 and edge_counts is None:
+    peers = PeerBlocks.get(ii.shape[0], Twc.device, group) if (p2p and world > 1) else None
+    solver = GNSolver(prm, Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_local, edge_begin, peers=peers)
+    if world > 1 and edge_counts is None and peers is None:
         raise RuntimeError("gauss_newton_sharded: edge_counts (from shard_edges) is required")
     for _ in range(int(max_iter)):
         solver.accumulate()
-        if world > 1:
+        if world > 1 and peers is None:
             exchange_blocks(solver.blocks, solver.edge_begin, solver.Ml, list(edge_counts), group)
         solver.solve_step(delta_thresh)
     return [solver.dx]
