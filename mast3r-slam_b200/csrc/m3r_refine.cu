@@ -11,30 +11,41 @@
 // therefore scored at once in the two lanes of half2 registers (mul.rn/add.rn, which
 // ptxas may not fuse into an fma).
 //
-// What bounds this kernel (ncu, profiles/): not HBM.  Per (query, candidate) pair the exact
+// What bounds this kernel (ncu, profiles/r1q_*): not HBM.  Per (query, candidate) pair the exact
 // rounding chain needs F HMUL2-lanes + F HADD2-lanes; fp16x2 instructions issue on the
 // fma-heavy pipe only (one warp instruction per 2 cycles per SM sub-partition), and every
-// candidate is a 2F-byte gather through L1 (128 B/clk/SM).  At F = 24, 245 candidates per
-// query both floors are ~12 cycles per (warp, candidate) per SM — the kernel is balanced
-// between the fp16 pipe and the L1 data pipe; everything else (index arithmetic, bounds
-// tests, tie-breaking) is kept off the fma pipe:
+// candidate is a 2F-byte gather through the L1 data pipe (128 B/clk/SM when the lanes' 16-B
+// words fall in distinct banks: profiles/micro/l1_align.cu; ~4.9 wavefronts per LDG.128 on real
+// match fields, whose lanes are not perfectly consecutive).  At F = 24, 241 candidates per
+// query the two floors are 0.49 ms (fp16 pipe) and 0.67 ms (L1) for 8 x 512x384 queries;
+// everything else (index arithmetic, bounds tests, tie-breaking) is kept off both pipes:
 //   * the argmax keeps ONE signed 32-bit key per query, (score_fp16_bits << 16) |
 //     (0xFFFE - scan_index): a signed integer max then realises "strict > in (u outer,
 //     v inner) scan order"  in any evaluation order — negative scores have the
 //     sign bit set and lose against the initial +0, equal scores lose against an
 //     earlier scan index, and a maximum carried over from a previous dilation carries the
 //     tie field 0xFFFF so that no later tie can displace it;
-//   * candidates are therefore visited row-major (v outer) for L1 locality, by 2-D CTA tiles
-//     of 32x8 queries whose windows overlap;
-//   * interior windows (all (2r+1)^2 candidates inside the image) skip every bounds test.
+//   * the evaluation order is therefore free: interior windows at dilation 1..5 take their
+//     candidates in point-symmetric pairs with compile-time column offsets (no per-candidate
+//     address arithmetic) and skip the centre after the first dilation (it is the previous
+//     winner or an earlier loser: re-scoring it cannot change a strict-> argmax);
+//   * a CTA is a 32x24 tile of queries, one CTA per SM, so that the union of its windows
+//     (<= 62x54 pixels x 48 B at dilation 5) stays resident in that SM's L1 (hit rate 97.8 %);
+//   * windows that touch the image border take the bounds-tested row-major form.
 // Scores must not be NaN (a NaN never wins in the reference; its bit pattern would here).
 #include "m3r_common.cuh"
 
 namespace m3r {
 
-constexpr int kRefTX = 32, kRefTY = 8;
+#ifndef M3R_REFINE_TY
+#define M3R_REFINE_TY 24  // one 32x24-query CTA per SM: its windows (<= 62x54 pixels) stay L1-resident
+#endif
+constexpr int kRefTX = 32, kRefTY = M3R_REFINE_TY;
 constexpr int kRefineThreads = kRefTX * kRefTY;
 constexpr int kKeyInvalid = (int)0x80000000;
+// 0xFFFE - 7*i: tie field of window column i (row part subtracted per row).  Read from constant
+// memory so that ptxas keeps the values in registers and PRMT's immediate is its selector.
+__constant__ uint32_t kColumnTie[7] = {0xFFFE, 0xFFF7, 0xFFF0, 0xFFE9, 0xFFE2, 0xFFDB, 0xFFD4};
 
 // Scores of two candidates (A -> low lane, B -> high lane) against the packed query
 // q[t] = (q_2t, q_2t+1).  F8 = F/8 uint4 words per descriptor.
@@ -122,6 +133,80 @@ __device__ __forceinline__ void dilation_rows(const uint16_t* __restrict__ D11b,
   for (int i = 0; i < S; i += 2) eval2(S - 1, i, S - 1, (i + 1 < S) ? i + 1 : i, i + 1 < S);
 }
 
+// Interior window of side 7 at a compile-time dilation D (the hot case).  Candidates are taken in
+// point-symmetric pairs about the centre: A = (row j, col i), B = (row 6-j, col 6-i), j = 0..2,
+// then the three pairs of the centre row; the centre itself is the previous winner (or a
+// candidate that already lost), so it is only scored at the first dilation.  Column offsets
+// i*D*FB are instruction immediates; the two row pointers move by one 64-bit add per row.
+// Keys are formed with column-only ties CT[i] = 0xFFFE - 7i held in registers; the row part of
+// the scan index (i*7 + j) is subtracted once per row from the row maximum.
+__device__ __forceinline__ uint4 ld_cand(const char* p) {
+  return __ldg(reinterpret_cast<const uint4*>(p));
+}
+
+template <int F8>
+__device__ __forceinline__ uint32_t score_pair_at(const char* pa, const char* pb, int offa, int offb,
+                                                  const uint32_t* q) {
+  uint4 a[F8], b[F8];
+#pragma unroll
+  for (int w = 0; w < F8; w++) {
+    a[w] = ld_cand(pa + offa + 16 * w);
+    b[w] = ld_cand(pb + offb + 16 * w);
+  }
+  __half2 acc;
+#pragma unroll
+  for (int w = 0; w < F8; w++) {
+    const uint32_t aw[4] = {a[w].x, a[w].y, a[w].z, a[w].w};
+    const uint32_t bw[4] = {b[w].x, b[w].y, b[w].z, b[w].w};
+#pragma unroll
+    for (int t = 0; t < 4; t++) {
+      const uint32_t lo = __byte_perm(aw[t], bw[t], 0x5410);
+      const uint32_t hi = __byte_perm(aw[t], bw[t], 0x7632);
+      const __half2 qq = *reinterpret_cast<const __half2*>(&q[w * 4 + t]);
+      const __half2 plo = __hmul2_rn(*reinterpret_cast<const __half2*>(&lo), __low2half2(qq));
+      // 0 + p == p up to the sign of a zero, which cannot change a non-zero sum or any comparison
+      acc = (w == 0 && t == 0) ? plo : __hadd2_rn(acc, plo);
+      acc = __hadd2_rn(acc, __hmul2_rn(*reinterpret_cast<const __half2*>(&hi), __high2half2(qq)));
+    }
+  }
+  return *reinterpret_cast<uint32_t*>(&acc);
+}
+
+template <int F8, int D>
+__device__ __forceinline__ void dilation_sym(const char* centre, const uint32_t* q, int W, bool first,
+                                             const uint32_t (&CT)[7], int& best) {
+  constexpr int FB = F8 * 16, CS = D * FB;
+  const long long rs = (long long)D * W * FB;
+  const char* pa = centre - 3 * rs - 3 * CS;  // (row j, col 0)
+  const char* pb = centre + 3 * rs + 3 * CS;  // (row 6-j, col 6)
+#pragma unroll 1
+  for (int j = 0; j < 3; j++) {
+    int ra = kKeyInvalid + 64, rb = kKeyInvalid + 64;
+#pragma unroll
+    for (int i = 0; i < 7; i++) {
+      const uint32_t s2 = score_pair_at<F8>(pa, pb, i * CS, -i * CS, q);
+      ra = max(ra, key_lo(s2, CT[i]));
+      rb = max(rb, key_hi(s2, CT[6 - i]));
+    }
+    best = max(best, max(ra - j, rb - 6 + j));  // scan index = 7*col + row
+    pa += rs;
+    pb -= rs;
+  }
+  {  // centre row: pa is (row 3, col 0)
+    int rc = kKeyInvalid + 64;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      const uint32_t s2 = score_pair_at<F8>(pa, pa, i * CS, (6 - i) * CS, q);
+      rc = max(rc, max(key_lo(s2, CT[i]), key_hi(s2, CT[6 - i])));
+    }
+    best = max(best, rc - 3);
+  }
+  if (first) {
+    const uint32_t s2 = score_pair_at<F8>(pa, pa, 3 * CS, 3 * CS, q);
+    best = max(best, key_lo(s2, CT[3]) - 3);
+  }
+}
+
 // Generic window side (radius != 3): same key logic, runtime loops, scan order.
 template <int F8>
 __device__ __forceinline__ void dilation_generic(const uint16_t* __restrict__ D11b, const uint32_t* q,
@@ -159,13 +244,34 @@ __device__ __forceinline__ void refine_query(const uint16_t* __restrict__ D11b, 
                                              int& v0) {
   int best = 0x0000FFFF;  // score +0 (c10::Half() == 0), carried
   const int side = 2 * radius + 1;
+  uint32_t CT[7];
+#pragma unroll
+  for (int i = 0; i < 7; i++) CT[i] = kColumnTie[i];  // from constant memory: stays in registers
   for (int d = dilation_max; d > 0; d--) {
     const int us = u0 - radius * d, vs = v0 - radius * d;
     best |= 0xFFFF;  // the running maximum now predates every candidate of this dilation
     if (radius == 3) {
       const bool interior = us >= 0 && us + 6 * d < W && vs >= 0 && vs + 6 * d < H;
-      if (interior) dilation_rows<F8, 3, false>(D11b, q, H, W, d, us, vs, best);
-      else dilation_rows<F8, 3, true>(D11b, q, H, W, d, us, vs, best);
+#ifdef M3R_REFINE_OLD
+      if (false) {
+#else
+      if (interior && d <= 5) {
+#endif
+        const char* centre = reinterpret_cast<const char*>(D11b) +
+                             (size_t)((unsigned)v0 * (unsigned)W + (unsigned)u0) * (F8 * 16);
+        const bool first = d == dilation_max;
+        switch (d) {
+          case 5: dilation_sym<F8, 5>(centre, q, W, first, CT, best); break;
+          case 4: dilation_sym<F8, 4>(centre, q, W, first, CT, best); break;
+          case 3: dilation_sym<F8, 3>(centre, q, W, first, CT, best); break;
+          case 2: dilation_sym<F8, 2>(centre, q, W, first, CT, best); break;
+          default: dilation_sym<F8, 1>(centre, q, W, first, CT, best); break;
+        }
+      } else if (interior) {
+        dilation_rows<F8, 3, false>(D11b, q, H, W, d, us, vs, best);
+      } else {
+        dilation_rows<F8, 3, true>(D11b, q, H, W, d, us, vs, best);
+      }
     } else {
       dilation_generic<F8>(D11b, q, H, W, radius, d, us, vs, best);
     }
@@ -199,7 +305,7 @@ __device__ __forceinline__ int clamp_coord(long long c) {
 
 // Plain form: D21 already fp16, output (u,v) pairs.
 template <int F8>
-__global__ void __launch_bounds__(kRefineThreads)
+__global__ void __launch_bounds__(kRefineThreads, 1)
 refine_f16_kernel(const uint16_t* __restrict__ D11, const uint16_t* __restrict__ D21,
                   const int64_t* __restrict__ p1, int H, int W, int n, int radius,
                   int dilation_max, int tiles_x, int tiled, int64_t* __restrict__ p1_new) {
@@ -226,7 +332,7 @@ refine_f16_kernel(const uint16_t* __restrict__ D11, const uint16_t* __restrict__
 
 // Fused form: D21 fp32 rounded to fp16 on the fly (== .half()), output linear index.
 template <int F8>
-__global__ void __launch_bounds__(kRefineThreads)
+__global__ void __launch_bounds__(kRefineThreads, 1)
 refine_fused_kernel(const uint16_t* __restrict__ D11h, const float* __restrict__ D21,
                     const int64_t* __restrict__ p1, int H, int W, int radius,
                     int dilation_max, int tiles_x, int64_t* __restrict__ idx_out) {
