@@ -165,128 +165,168 @@ __device__ __forceinline__ void load_tile(const double* __restrict__ A, int Dp, 
   }
 }
 
-// In-place Cholesky of the 32x32 tile in `s` by the whole 64-thread CTA: thread (ty,tx) of an
-// 8x8 grid keeps the 4x4 micro-tile {rows ty+8x, cols tx+8y} in registers; per column step the
-// raw column goes through a double-buffered shared vector (ONE __syncthreads per step), every
-// thread scales the 4+4 entries it needs by rsqrt(pivot) itself, and updates its micro-tile.
-// The per-step dependent chain is sts -> bar -> lds -> rsqrt -> dmul -> dfma (~170 cycles,
-// profiles/micro/fp64_lat.cu) and the loop body is the same code for every column, so nothing
-// is fetched cold: the earlier one-warp, fully unrolled form was 40 KB of straight-line code
-// and cost 11 us per tile inside the kernel (4.7 us warm), profiles/r1j_chol_notes.md.
-// Rows whose global index is >= D (augmented rhs row, padding) take pivot 1; 1/pivot is kept in
-// `dinv_g` for the TRSM and the back-substitution.
-// One column step of potrf_tile for a column c = 8*YC + cc whose micro-tile index YC is a
-// compile-time constant: register indices are static and whole micro-tile rows/columns that lie
-// left of / above the pivot drop out at compile time.
-template <int YC>
-__device__ __forceinline__ void potrf_step(double (&a)[kRX][4], double (*s)[NB + 1], double* colbuf,
-                                           int cc, int ty, int tx, int g0, int D,
-                                           double* __restrict__ dinv_g, GnHeader* hdr) {
-  const int c = 8 * YC + cc;
-  double* col = colbuf + (c & 1) * NB;
-  if (tx == cc) {  // owners of column c publish its raw entries (rows < c: unused)
-#pragma unroll
-    for (int x = 0; x < kRX; x++) col[ty + kTY * x] = a[x][YC];
+// Tile accessors.  `TilePad` is the [32][33] staging layout of the multi-CTA kernel; `TileSw` is
+// the unpadded 8 KB tile of the single-CTA kernel with its 16-byte units XOR-swizzled by the row,
+// so that a warp reading one column (lane = row) or one row pair per lane hits distinct banks.
+struct TilePad {
+  double* p;
+  __device__ __forceinline__ double& operator()(int r, int c) const { return p[r * (NB + 1) + c]; }
+};
+struct TileSw {
+  double* p;
+  __device__ __forceinline__ double& operator()(int r, int c) const {
+    return p[r * NB + ((((c >> 1) ^ (r & 15)) << 1) | (c & 1))];
   }
-  __syncthreads();
-  const double d = col[c];
-  const bool bad = !(d > 0.0);
-  const bool unit = (g0 + c >= D) || bad;
-  if (threadIdx.x == 0) {
-    if (bad && g0 + c < D) hdr->chol_fail = 1;
+  // columns 2u, 2u+1 of row r as one 16-byte word
+  __device__ __forceinline__ double2 pair(int r, int u) const {
+    return *reinterpret_cast<const double2*>(p + r * NB + ((u ^ (r & 15)) << 1));
   }
-  const double yv = unit ? 1.0 : rsqrt(d);
-  if (threadIdx.x == 0) dinv_g[g0 + c] = yv;
-  double lr[kRX], lc[4];
+};
+
+// 4x4 Cholesky of a diagonal block held (lower) in b, redundantly by every lane: the only
+// rsqrt chain of the factorisation.  Rows whose global index is >= D (augmented rhs row,
+// padding) and non-positive pivots take pivot 1.
+__device__ __forceinline__ bool factor4(double (&b)[4][4], double (&rr)[4], int g, int D) {
+  bool fail = false;
 #pragma unroll
-  for (int x = 0; x < kRX; x++) lr[x] = (ty + kTY * x > c) ? col[ty + kTY * x] * yv : 0.0;
+  for (int j = 0; j < 4; j++) {
+    double d = b[j][j];
 #pragma unroll
-  for (int y = YC; y < 4; y++) lc[y] = col[tx + 8 * y] * yv;
-  lc[YC] = (tx > cc) ? lc[YC] : 0.0;  // columns <= c of the pivot's micro-column are final
-  if (tx == cc) {  // column c of L: 0 above the diagonal, the pivot, then the scaled entries
+    for (int k = 0; k < j; k++) d = fma(-b[j][k], b[j][k], d);
+    const bool real = g + j < D;
+    const bool bad = !(d > 0.0);
+    fail |= real && bad;
+    const bool unit = !real || bad;
+    rr[j] = unit ? 1.0 : rsqrt(d);
+    b[j][j] = unit ? 1.0 : d * rr[j];
 #pragma unroll
-    for (int x = 0; x < kRX; x++) {
-      const int r = ty + kTY * x;
-      s[r][c] = (r == c) ? (unit ? 1.0 : d * yv) : lr[x];
+    for (int i = j + 1; i < 4; i++) {
+      double v = b[i][j];
+#pragma unroll
+      for (int k = 0; k < j; k++) v = fma(-b[i][k], b[j][k], v);
+      b[i][j] = v * rr[j];
     }
   }
-#pragma unroll
-  for (int x = 0; x < kRX; x++)
-#pragma unroll
-    for (int y = YC; y < 4; y++) a[x][y] = fma(-lr[x], lc[y], a[x][y]);
+  return fail;
 }
 
-// In-place Cholesky of the 32x32 tile in `s` by the whole CTA (see above).  The factor is
-// written to `s` column by column; the registers only carry the trailing matrix.
-__device__ __forceinline__ void potrf_tile(double (*s)[NB + 1], double* colbuf, int g0, int D,
-                                           double* __restrict__ dinv_g, GnHeader* hdr) {
-  const int tid = threadIdx.x, ty = tid >> 3, tx = tid & 7;
-  double a[kRX][4];  // the strict upper triangle is zeroed: it takes part in the (symmetric) updates
+// Rank-4 update of the own-row entries at columns jj0..jj0+3 with the finished panel at column
+// p0 (x = own row of that panel).  All loads first, then the arithmetic, then the stores: the
+// shared-memory stores of one entry must not serialise the loads of the next (may-alias).
+template <class Tile>
+__device__ __forceinline__ void rank4_rows(const Tile s, int r, int p0, int jj0, const double (&x)[4],
+                                           double (&t)[4]) {
+  double v[4][4];
 #pragma unroll
-  for (int x = 0; x < kRX; x++)
+  for (int u = 0; u < 4; u++) {
 #pragma unroll
-    for (int y = 0; y < 4; y++)
-      a[x][y] = (tx + 8 * y <= ty + kTY * x) ? s[ty + kTY * x][tx + 8 * y] : 0.0;
-  __syncthreads();  // everyone has its micro-tile before columns of `s` are overwritten
-#pragma unroll 1
-  for (int cc = 0; cc < 8; cc++) potrf_step<0>(a, s, colbuf, cc, ty, tx, g0, D, dinv_g, hdr);
-#pragma unroll 1
-  for (int cc = 0; cc < 8; cc++) potrf_step<1>(a, s, colbuf, cc, ty, tx, g0, D, dinv_g, hdr);
-#pragma unroll 1
-  for (int cc = 0; cc < 8; cc++) potrf_step<2>(a, s, colbuf, cc, ty, tx, g0, D, dinv_g, hdr);
-#pragma unroll 1
-  for (int cc = 0; cc < 8; cc++) potrf_step<3>(a, s, colbuf, cc, ty, tx, g0, D, dinv_g, hdr);
+    for (int k = 0; k < 4; k++) v[u][k] = s(jj0 + u, p0 + k);
+    t[u] = s(r, jj0 + u);
+  }
+#pragma unroll
+  for (int u = 0; u < 4; u++) {
+#pragma unroll
+    for (int k = 0; k < 4; k++) t[u] = fma(-x[k], v[u][k], t[u]);
+  }
+#pragma unroll
+  for (int u = 0; u < 4; u++)
+    if (jj0 + u <= r) s(r, jj0 + u) = t[u];
 }
 
-template <int YC>
-__device__ __forceinline__ void trsm_step(double (&a)[kRX][4], double (*sx)[NB + 1],
-                                          const double (*sl)[NB + 1], double* colbuf,
-                                          const double* dinv, int cc, int ty, int tx) {
-  const int c = 8 * YC + cc;
-  double* col = colbuf + (c & 1) * NB;
-  if (tx == cc) {  // column c of X is final after scaling by 1/L[c][c]
-    const double di = dinv[c];
+// In-place Cholesky of one 32x32 tile by a team of 4 warps (`sync` = barrier over exactly these
+// 128 threads; w = warp within the team).  Lane r owns row r, which stays in shared memory.
+// Columns are taken four at a time.  Warp 0 is the critical path: it factors the 4x4 diagonal
+// block (every lane redundantly, in registers), solves its own row against it, and after the
+// barrier applies the rank-4 update to the NEXT panel's four columns only (look-ahead).  Warps
+// 1-3 apply the same update to all columns further right while warp 0 is already factoring the
+// next block.  Compact loops on purpose: a fully unrolled register-resident form (40 KB of
+// code) spent more time in cold instruction fetch than in arithmetic, and the earlier 128-thread
+// 2-D form needed a barrier per column (8.0 us per tile; this one 3.7 us,
+// profiles/micro/warp_tile.cu).  1/pivot goes to `dinv` for the TRSM and back-substitution.
+template <class Tile, class Sync>
+__device__ __forceinline__ void potrf_team(const Tile s, int w, int g0, int D, double* __restrict__ dinv,
+                                           GnHeader* hdr, Sync sync) {
+  const int r = threadIdx.x & 31;
+  double x[4] = {0.0, 0.0, 0.0, 0.0};  // warp 0: own row of the current panel
+  double cur[4] = {0.0, 0.0, 0.0, 0.0};  // warp 0: own row at the current panel's columns, up to date
+  if (w == 0) {
 #pragma unroll
-    for (int x = 0; x < kRX; x++) {
-      const double v = a[x][YC] * di;
-      col[ty + kTY * x] = v;
-      sx[ty + kTY * x][c] = v;
+    for (int j = 0; j < 4; j++) cur[j] = s(r, j);
+  }
+#pragma unroll 1
+  for (int c0 = 0; c0 < NB; c0 += 4) {
+    if (w == 0) {
+      double b[4][4], rr[4];
+#pragma unroll
+      for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j <= i; j++) b[i][j] = s(c0 + i, c0 + j);
+      const bool fail = factor4(b, rr, g0 + c0, D);
+      if (r == 0) {
+        if (fail) hdr->chol_fail = 1;
+#pragma unroll
+        for (int j = 0; j < 4; j++) dinv[c0 + j] = rr[j];
+      }
+      const int i = r - c0;  // own row against the block: same operation order as the block itself
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        double v = cur[j];
+#pragma unroll
+        for (int k = 0; k < j; k++) v = fma(-x[k], b[j][k], v);
+        x[j] = v * rr[j];
+        if (i == j) x[j] = b[j][j];  // the pivot itself (1 for unit rows)
+        if (i < j) x[j] = 0.0;       // above the diagonal (rows above the panel: unused)
+      }
+      if (i >= 0) {
+#pragma unroll
+        for (int j = 0; j < 4; j++) s(r, c0 + j) = x[j];
+      }
+    }
+    sync();  // panel c0 is final; warps 1-3 have finished the previous panel's updates
+    if (w == 0) {
+      if (c0 + 4 < NB) rank4_rows(s, r, c0, c0 + 4, x, cur);
+      __syncwarp();
+    } else {
+      double xw[4], t[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) xw[k] = s(r, c0 + k);
+#pragma unroll 1
+      for (int jj = c0 + 8 + 4 * (w - 1); jj < NB; jj += 12) rank4_rows(s, r, c0, jj, xw, t);
     }
   }
-  __syncthreads();
-  double xr[kRX], lc[4];
-#pragma unroll
-  for (int x = 0; x < kRX; x++) xr[x] = col[ty + kTY * x];
-#pragma unroll
-  for (int y = YC; y < 4; y++) lc[y] = sl[tx + 8 * y][c];
-  lc[YC] = (tx > cc) ? lc[YC] : 0.0;
-#pragma unroll
-  for (int x = 0; x < kRX; x++)
-#pragma unroll
-    for (int y = YC; y < 4; y++) a[x][y] = fma(-xr[x], lc[y], a[x][y]);
 }
 
-// X <- X * Ljj^-T for the 32x32 tile X in `sx`, Ljj in `sl`: same thread grid; per column step
-// the finished column of X is broadcast through the double-buffered shared vector.
-__device__ __forceinline__ void trsm_tile(double (*sx)[NB + 1], const double (*sl)[NB + 1],
-                                          double* colbuf, double* dinv,
-                                          const double* __restrict__ dinv_g) {
-  const int tid = threadIdx.x, ty = tid >> 3, tx = tid & 7;
-  if (tid < NB) dinv[tid] = __ldcg(dinv_g + tid);
-  double a[kRX][4];
+// X <- X * Ljj^-T for the 32x32 tile X by ONE warp: lane r solves row r (rows are independent:
+// no barrier at all); Ljj and 1/diag are broadcast reads.  Four columns per trip: the part
+// against finished columns is a load-only loop, the 4x4 triangle is solved in registers.
+template <class Tile>
+__device__ __forceinline__ void trsm_warp(const Tile sx, const Tile sl, const double* __restrict__ dinv) {
+  const int r = threadIdx.x & 31;
+#pragma unroll 1
+  for (int c0 = 0; c0 < NB; c0 += 4) {
+    double a[4];
 #pragma unroll
-  for (int x = 0; x < kRX; x++)
+    for (int j = 0; j < 4; j++) a[j] = sx(r, c0 + j);
+#pragma unroll 4
+    for (int m = 0; m < c0; m++) {
+      const double xm = sx(r, m);
 #pragma unroll
-    for (int y = 0; y < 4; y++) a[x][y] = sx[ty + kTY * x][tx + 8 * y];
-  __syncthreads();
-#pragma unroll 1
-  for (int cc = 0; cc < 8; cc++) trsm_step<0>(a, sx, sl, colbuf, dinv, cc, ty, tx);
-#pragma unroll 1
-  for (int cc = 0; cc < 8; cc++) trsm_step<1>(a, sx, sl, colbuf, dinv, cc, ty, tx);
-#pragma unroll 1
-  for (int cc = 0; cc < 8; cc++) trsm_step<2>(a, sx, sl, colbuf, dinv, cc, ty, tx);
-#pragma unroll 1
-  for (int cc = 0; cc < 8; cc++) trsm_step<3>(a, sx, sl, colbuf, dinv, cc, ty, tx);
+      for (int j = 0; j < 4; j++) a[j] = fma(-xm, sl(c0 + j, m), a[j]);
+    }
+    double l[4][4];
+#pragma unroll
+    for (int j = 1; j < 4; j++)
+#pragma unroll
+      for (int k = 0; k < j; k++) l[j][k] = sl(c0 + j, c0 + k);
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+#pragma unroll
+      for (int k = 0; k < j; k++) a[j] = fma(-a[k], l[j][k], a[j]);
+      a[j] *= dinv[c0 + j];
+    }
+#pragma unroll
+    for (int j = 0; j < 4; j++) sx(r, c0 + j) = a[j];
+  }
 }
 
 // Tile (i,j), i >= j:  A_ij <- (A_ij - sum_{k<j} L_ik L_jk^T) [chol | * L_jj^-T], then flag it.
@@ -333,14 +373,16 @@ __device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, 
     }
   __syncthreads();
   unsigned long long t_ready = a.trace ? gtimer() : 0ull;
+  const TilePad tA{&sA[0][0]}, tB{&sB[0][0]};
   if (i == j) {
-    potrf_tile(sA, sv, j * NB, a.D, a.x + a.Dp, a.hdr);
+    potrf_team(tA, tid >> 5, j * NB, a.D, a.x + a.Dp + j * NB, a.hdr, [] { __syncthreads(); });
   } else {
     wait_flag(a.flags + j * a.nb + j, epoch);
     if (a.trace) t_ready = gtimer();
     load_tile(a.A, a.Dp, j, j, sB);
+    if (tid < NB) sv[tid] = __ldcg(a.x + a.Dp + j * NB + tid);
     __syncthreads();
-    trsm_tile(sA, sB, sv, sred, a.x + a.Dp + j * NB);
+    if (tid < 32) trsm_warp(tA, tB, sv);
   }
   __syncthreads();
   for (int idx = tid; idx < NB * NB; idx += kCholThreads) {
