@@ -165,24 +165,11 @@ __device__ __forceinline__ void load_tile(const double* __restrict__ A, int Dp, 
   }
 }
 
-// Tile accessors.  `TilePad` is the [32][33] staging layout of the multi-CTA kernel; `TileSw` is
-// the unpadded 8 KB tile of the single-CTA kernel with its 16-byte units XOR-swizzled by the row,
-// so that a warp reading one column (lane = row) or one row pair per lane hits distinct banks.
+// Tile accessor: the [32][33] staging layout (a warp reading one column, lane = row, hits 32 banks).
 struct TilePad {
   double* p;
   __device__ __forceinline__ double& operator()(int r, int c) const { return p[r * (NB + 1) + c]; }
 };
-struct TileSw {
-  double* p;
-  __device__ __forceinline__ double& operator()(int r, int c) const {
-    return p[r * NB + ((((c >> 1) ^ (r & 15)) << 1) | (c & 1))];
-  }
-  // columns 2u, 2u+1 of row r as one 16-byte word
-  __device__ __forceinline__ double2 pair(int r, int u) const {
-    return *reinterpret_cast<const double2*>(p + r * NB + ((u ^ (r & 15)) << 1));
-  }
-};
-
 // 4x4 Cholesky of a diagonal block held (lower) in b, redundantly by every lane: the only
 // rsqrt chain of the factorisation.  Rows whose global index is >= D (augmented rhs row,
 // padding) and non-positive pivots take pivot 1.
@@ -439,11 +426,13 @@ __device__ __forceinline__ void chol_back_task(const CholArgs& a, int c, int epo
   trace_put(a, slot, 2, c, c, t_begin, t_ready);
 }
 
-// dx = -x (zeros on failure), retract, |dx| test  (gn_kernels.cu:1209-1222) — one CTA.
+// dx = -x (zeros on failure), retract, |dx| test  (gn_kernels.cu:1209-1222) — one team of
+// `nthr` threads (`sync` = barrier over exactly those threads).
+template <class Sync>
 __device__ __forceinline__ void gn_update_block(float* __restrict__ Twc, const double* __restrict__ x,
                                                 int N, int D, float delta_thresh,
-                                                float* __restrict__ dx, GnHeader* hdr, float* red) {
-  const int nthr = blockDim.x, tid = threadIdx.x;
+                                                float* __restrict__ dx, GnHeader* hdr, float* red,
+                                                int nthr, int tid, Sync sync) {
   const bool fail = *reinterpret_cast<volatile int*>(&hdr->chol_fail) != 0 ||
                     *reinterpret_cast<volatile int*>(&hdr->peer_timeout) != 0;
   float ss = 0.f;
@@ -452,7 +441,7 @@ __device__ __forceinline__ void gn_update_block(float* __restrict__ Twc, const d
     dx[i] = v;
     ss += v * v;
   }
-  __syncthreads();  // dx visible to the retraction below (same CTA)
+  sync();  // dx visible to the retraction below (same team)
   for (int p = 1 + tid; p < N; p += nthr) {
     float pose[8], xi[7];
 #pragma unroll
@@ -465,7 +454,7 @@ __device__ __forceinline__ void gn_update_block(float* __restrict__ Twc, const d
   }
   ss = warp_sum(ss);
   if ((tid & 31) == 0) red[tid >> 5] = ss;
-  __syncthreads();
+  sync();
   if (tid == 0) {
     float tot = 0.f;
     for (int w = 0; w < (nthr + 31) / 32; w++) tot += red[w];
@@ -495,7 +484,8 @@ chol_dataflow_kernel(const CholArgs a) {
       chol_back_task(a, c, epoch, sA, sv, sred, t + c);
       if (c == 0) {  // x complete: this CTA finishes the iteration
         __syncthreads();
-        gn_update_block(a.Twc, a.x, a.N, a.D, a.delta_thresh, a.dx, a.hdr, red);
+        gn_update_block(a.Twc, a.x, a.N, a.D, a.delta_thresh, a.dx, a.hdr, red, kCholThreads, threadIdx.x,
+                        [] { __syncthreads(); });
       }
     }
 }

@@ -38,6 +38,8 @@ lines = [f"N={N} nb={nb} solve_step {a.elapsed_time(z) * 1e3:.1f} us (event); ke
 kinds = {0: "potrf", 1: "trsm ", 2: "back "}
 order = sorted(range(cap), key=lambda r: t[r, 3])
 for r in order:
+    if t[r, 3] == 0:
+        continue
     k, i, j = int(t[r, 0] >> 32), int((t[r, 0] >> 16) & 0xFFFF), int(t[r, 0] & 0xFFFF)
     if nb > 16 and not (k != 1 or i == j + 1):
         continue
