@@ -32,12 +32,20 @@ constexpr int NB = kGnNB;
 //   H[ii,ii] += S, H[ii,jj] -= S, H[jj,ii] -= S, H[jj,jj] += S ; b[ii] -= v, b[jj] += v
 // (update_lhs/update_rhs with the reference's Hs/gs layout, gn_kernels.cu:1201-1206).
 // ---------------------------------------------------------------------------------
-__global__ void __launch_bounds__(64)
+constexpr int kAsmThreads = 128;
+constexpr int kAsmChunk = 64;               // incident edges whose indices are staged per round
+constexpr int kAsmSmemMax = 96 * 1024;      // row buffer: 7 x (7r+7) doubles (pose rows up to r = 249)
+
+__global__ void __launch_bounds__(kAsmThreads)
 gn_assemble_kernel(const double* __restrict__ blocks, const int* __restrict__ ie,
                    const int* __restrict__ je, const int* __restrict__ row_ptr,
                    const int* __restrict__ adj, int M, int N, int D, int Dp, double* __restrict__ A,
-                   GnHeader* hdr, const int* wait_flags, int wait_world, int wait_epoch) {
+                   GnHeader* hdr, const int* wait_flags, int wait_world, int wait_epoch,
+                   int smem_bytes) {
   if (hdr->done) return;
+  extern __shared__ __align__(16) double rowbuf[];  // [7][7r+7]: this pose's rows of the lower triangle
+  __shared__ int s_e[kAsmChunk], s_other[kAsmChunk];
+  __shared__ unsigned char s_role[kAsmChunk];
   if (wait_flags) {  // peer-memory exchange: all ranks' blocks of this iteration must have landed
     if (threadIdx.x == 0) {
       unsigned long long t0;
@@ -60,40 +68,77 @@ gn_assemble_kernel(const double* __restrict__ blocks, const int* __restrict__ ie
   const int r = blockIdx.x;  // free index; pose row r+1
   if (r == N - 1) {          // augmented row diagonal + identity padding
     if (t == 0) hdr->chol_fail = 0;
-    for (int row = D + t; row < Dp; row += 64) {
+    for (int row = D + t; row < Dp; row += kAsmThreads) {
       if (row > D)
         for (int c = 0; c < row; c++) A[(size_t)row * Dp + c] = 0.0;
       A[(size_t)row * Dp + row] = 1.0;
     }
     return;
   }
-  // zero the lower-triangular part of this pose's 7 rows
+  // The off-diagonal blocks are read-modify-write targets (an edge and its reverse hit the same
+  // block).  They are accumulated in shared memory — a global RMW is an L2 round trip per edge,
+  // which made this kernel 17 us at N = 32 — and written out once, coalesced.  Rows too long
+  // for the buffer (r >= 250) fall back to accumulating in global memory.
   const int ncols = 7 * r + 7;
-  for (int k = 0; k < 7; k++)
-    for (int c = t; c < ncols; c += 64) A[(size_t)(7 * r + k) * Dp + c] = 0.0;
+  const bool in_smem = (size_t)7 * ncols * sizeof(double) <= (size_t)smem_bytes;
+  if (in_smem) {
+    for (int c = t; c < 7 * ncols; c += kAsmThreads) rowbuf[c] = 0.0;
+  } else {
+    for (int k = 0; k < 7; k++)
+      for (int c = t; c < ncols; c += kAsmThreads) A[(size_t)(7 * r + k) * Dp + c] = 0.0;
+  }
   __syncthreads();
   const int s0 = row_ptr[r + 1], s1 = row_ptr[r + 2];
   double acc = 0.0;  // t<49: diagonal block entry; 49<=t<56: b entry
   const int k = t / 7, l = t % 7;
-  for (int s = s0; s < s1; s++) {
-    const int slot = adj[s];
-    const bool role_i = slot < M;
-    const int e = role_i ? slot : slot - M;
-    const int other = (role_i ? je[e] : ie[e]) - 1;  // free index of the other end (-1: fixed)
-    if (t < 49) {
-      const double v = __ldcg(blocks + (size_t)e * kGnBlock + t);
-      acc += v;
-      if (other == r) acc -= v;  // self edge
-      else if (other >= 0 && other < r) A[(size_t)(7 * r + k) * Dp + 7 * other + l] -= v;
-    } else if (t < 56) {
-      const double v = __ldcg(blocks + (size_t)e * kGnBlock + t);
-      acc += role_i ? -v : v;
+  for (int base = s0; base < s1; base += kAsmChunk) {
+    const int cnt = min(kAsmChunk, s1 - base);
+    if (base > s0) __syncthreads();  // previous round consumed
+    if (t < cnt) {
+      const int slot = adj[base + t];
+      const bool role_i = slot < M;
+      const int e = role_i ? slot : slot - M;
+      s_e[t] = e;
+      s_role[t] = role_i ? 1 : 0;
+      s_other[t] = (role_i ? je[e] : ie[e]) - 1;  // free index of the other end (-1: fixed)
+    }
+    __syncthreads();
+    if (t < 56) {
+      for (int q0 = 0; q0 < cnt; q0 += 4) {
+        double v[4];
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+          v[q] = (q0 + q < cnt) ? __ldcg(blocks + (size_t)s_e[q0 + q] * kGnBlock + t) : 0.0;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+          if (q0 + q >= cnt) break;
+          const int other = s_other[q0 + q];
+          if (t < 49) {
+            acc += v[q];
+            if (other == r) acc -= v[q];  // self edge
+            else if (other >= 0 && other < r) {
+              if (in_smem) rowbuf[k * ncols + 7 * other + l] -= v[q];
+              else A[(size_t)(7 * r + k) * Dp + 7 * other + l] -= v[q];
+            }
+          } else {
+            acc += s_role[q0 + q] ? -v[q] : v[q];
+          }
+        }
+      }
     }
   }
   if (t < 49) {
-    if (l <= k) A[(size_t)(7 * r + k) * Dp + 7 * r + l] = acc;
+    if (l <= k) {
+      if (in_smem) rowbuf[k * ncols + 7 * r + l] = acc;
+      else A[(size_t)(7 * r + k) * Dp + 7 * r + l] = acc;
+    }
   } else if (t < 56) {
     A[(size_t)D * Dp + 7 * r + (t - 49)] = acc;
+  }
+  if (in_smem) {
+    __syncthreads();
+    for (int kk = 0; kk < 7; kk++)
+      for (int c = t; c < ncols; c += kAsmThreads) A[(size_t)(7 * r + kk) * Dp + c] = rowbuf[kk * ncols + c];
   }
 }
 
@@ -426,6 +471,95 @@ __device__ __forceinline__ void chol_back_task(const CholArgs& a, int c, int epo
   trace_put(a, slot, 2, c, c, t_begin, t_ready);
 }
 
+// Back substitution of a small system (nb <= kBackSingleMax) by ONE CTA — the one that factored
+// the last diagonal tile, so every tile is final and nothing is waited for.  The distributed
+// form above costs a flag hop, an L2 round trip for x_m and a fence per block column (3.7 us
+// each); here x stays in shared memory and the L tiles of a block column are fetched four at a
+// time (32 independent loads per thread in flight).
+constexpr int kBackSingleMax = 16;
+
+struct BackLoads {  // global loads of one block column, issued before they are needed
+  double v[4][NB / (kCholThreads / 32)];  // rows part*kRows.. of up to four L_mc tiles, column t
+  double2 d[NB * NB / 2 / kCholThreads];  // this thread's share of the diagonal tile L_cc
+  double rhs, dinv;
+};
+
+__device__ __forceinline__ void back_issue(const CholArgs& a, int c, int m0, bool with_diag, BackLoads& L) {
+  constexpr int kRows = NB / (kCholThreads / 32);
+  const int tid = threadIdx.x, t = tid & 31, part = tid >> 5;
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    if (m0 + q < a.nb) {
+      const double* Lmc = a.A + (size_t)(m0 + q) * NB * a.Dp + (size_t)c * NB;
+#pragma unroll
+      for (int rr = 0; rr < kRows; rr++) L.v[q][rr] = __ldcg(Lmc + (size_t)(part * kRows + rr) * a.Dp + t);
+    }
+  }
+  if (with_diag) {
+    const double* src = a.A + (size_t)c * NB * a.Dp + (size_t)c * NB;
+#pragma unroll
+    for (int q = 0; q < NB * NB / 2 / kCholThreads; q++) {
+      const int idx = tid + q * kCholThreads;
+      L.d[q] = __ldcg(reinterpret_cast<const double2*>(src + (size_t)(idx / (NB / 2)) * a.Dp + (idx % (NB / 2)) * 2));
+    }
+    const int g = c * NB + t;
+    L.rhs = (tid < NB && g < a.D) ? __ldcg(a.A + (size_t)a.D * a.Dp + g) : 0.0;
+    L.dinv = (tid < NB) ? __ldcg(a.x + a.Dp + g) : 0.0;
+  }
+}
+
+__device__ __forceinline__ void chol_back_all(const CholArgs& a, double (*sA)[NB + 1], double* xs,
+                                              double* sred, int slot) {
+  constexpr int kParts = kCholThreads / 32, kRows = NB / kParts;
+  const int tid = threadIdx.x, t = tid & 31, part = tid >> 5;
+  BackLoads L;
+  back_issue(a, a.nb - 1, a.nb, true, L);
+  for (int c = a.nb - 1; c >= 0; c--) {
+    const unsigned long long t_top = a.trace ? gtimer() : 0ull;
+#pragma unroll
+    for (int q = 0; q < NB * NB / 2 / kCholThreads; q++) {
+      const int idx = tid + q * kCholThreads;
+      const int r = idx / (NB / 2), c2 = (idx % (NB / 2)) * 2;
+      sA[r][c2] = L.d[q].x; sA[r][c2 + 1] = L.d[q].y;
+    }
+    const double rhs0 = L.rhs, dinv = L.dinv;
+    double s = 0.0;
+    for (int m0 = c + 1; m0 < a.nb; m0 += 4) {
+      if (m0 > c + 1) back_issue(a, c, m0, false, L);  // further batches of a long column
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        if (m0 + q < a.nb) {
+#pragma unroll
+          for (int rr = 0; rr < kRows; rr++) s = fma(L.v[q][rr], xs[(m0 + q) * NB + part * kRows + rr], s);
+        }
+      }
+    }
+    if (part > 0) sred[(part - 1) * NB + t] = s;
+    __syncthreads();  // partial sums and the diagonal tile are in shared memory
+    const unsigned long long t_mid = a.trace ? gtimer() : 0ull;
+    if (c > 0) back_issue(a, c - 1, c, true, L);  // next column's loads fly during the triangular solve
+    if (tid < NB) {
+      const int g = c * NB + t;
+      double tot = s;
+#pragma unroll
+      for (int pp = 1; pp < kParts; pp++) tot += sred[(pp - 1) * NB + t];
+      double rhs = (g < a.D) ? rhs0 - tot : 0.0;
+      double xo = 0.0;
+#pragma unroll
+      for (int k = NB - 1; k >= 0; k--) {
+        double xk = __shfl_sync(0xffffffffu, rhs * dinv, k);
+        if (c * NB + k >= a.D) xk = 0.0;
+        if (t == k) xo = xk;
+        if (t < k) rhs = fma(-sA[k][t], xk, rhs);
+      }
+      xs[g] = xo;
+      a.x[g] = xo;
+    }
+    __syncthreads();  // x_c visible; sA / sred free for the next block column
+    trace_put(a, slot + c, 2, c, c, t_top, t_mid);
+  }
+}
+
 // dx = -x (zeros on failure), retract, |dx| test  (gn_kernels.cu:1209-1222) — one team of
 // `nthr` threads (`sync` = barrier over exactly those threads).
 template <class Sync>
@@ -478,6 +612,14 @@ chol_dataflow_kernel(const CholArgs a) {
   for (int j = 0; j < a.nb; j++)
     for (int i = j; i < a.nb; i++, t++)
       if (t % G == cta) chol_tile_task(a, i, j, epoch, sA, sB, sv, sred, t);
+  if (a.nb <= kBackSingleMax) {  // small system: the owner of the last diagonal tile finishes alone
+    if ((t - 1) % G == cta) {
+      chol_back_all(a, sA, &sB[0][0], sred, t);
+      gn_update_block(a.Twc, a.x, a.N, a.D, a.delta_thresh, a.dx, a.hdr, red, kCholThreads, threadIdx.x,
+                      [] { __syncthreads(); });
+    }
+    return;
+  }
   // block columns of the back substitution, last to first (all after every tile)
   for (int c = a.nb - 1; c >= 0; c--)
     if (c % G == cta) {
@@ -526,9 +668,17 @@ int gn_solve_launch(float* Twc, const double* blocks, int N, int M, float delta_
   GnHeader* hdr = ws_ptr<GnHeader>(ws, L.hdr);
   double* A = ws_ptr<double>(ws, L.A);
   const int D = L.D, Dp = L.Dp, nb = Dp / NB;
-  gn_assemble_kernel<<<N, 64, 0, st>>>(blocks, ws_ptr<int>(ws, L.ie), ws_ptr<int>(ws, L.je),
-                                       ws_ptr<int>(ws, L.row_ptr), ws_ptr<int>(ws, L.adj), M, N, D,
-                                       Dp, A, hdr, wait_flags, wait_world, wait_epoch);
+  size_t asm_smem = (size_t)7 * (7 * (size_t)N) * sizeof(double);  // longest row: r = N-2
+  if (asm_smem > (size_t)kAsmSmemMax) asm_smem = kAsmSmemMax;
+  static bool asm_configured = false;
+  if (!asm_configured) {
+    M3R_TRY(check_cuda(cudaFuncSetAttribute(gn_assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            kAsmSmemMax)));
+    asm_configured = true;
+  }
+  gn_assemble_kernel<<<N, kAsmThreads, asm_smem, st>>>(
+      blocks, ws_ptr<int>(ws, L.ie), ws_ptr<int>(ws, L.je), ws_ptr<int>(ws, L.row_ptr), ws_ptr<int>(ws, L.adj),
+      M, N, D, Dp, A, hdr, wait_flags, wait_world, wait_epoch, (int)asm_smem);
   M3R_TRY(after_launch());
   CholArgs a;
   a.A = A; a.Dp = Dp; a.D = D; a.nb = nb;
