@@ -395,6 +395,23 @@ def bench_gn(be, synth, dev, rank, world, peak, barrier, max_over_ranks):
         same = torch.tensor([1 if (torch.equal(T_sh, T_one) and torch.equal(T_nc, T_one)) else 0], device=dev)
         dist.all_reduce(same, op=dist.ReduceOp.MIN)
         out["gn_rays_sharded_equals_single_gpu"] = bool(same.item())
+
+        # BASELINE configs[4], second half: independent graphs, one per GPU (no exchange at all)
+        def run_one():
+            T = g["Twc"].clone()
+            be.gauss_newton_rays(T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
+                                 0.003, 10.0, 0.0, 1.5, iters, 0.0)
+        for _ in range(2):
+            run_one()
+        barrier()
+        a.record()
+        for _ in range(reps):
+            run_one()
+        z.record()
+        barrier()
+        ms_ind = max_over_ranks(a.elapsed_time(z)) / reps
+        out["gn_rays_independent_graphs"] = {"graphs": world, "iters_per_s_aggregate": world * iters / (ms_ind * 1e-3),
+                                             "ms_per_solve": ms_ind}
     out["gn_rays"] = {"workload": "gauss_newton_rays N=32, 200 directed edges, 512x384, 10 iterations "
                                   "(BASELINE configs[2])" + (f", edge-sharded x{world}, block exchange fused into the "
                                                              "kernels over NVLink peer memory" if world > 1 else ""),

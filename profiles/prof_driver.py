@@ -1,5 +1,6 @@
 """Short single-GPU driver for ncu captures: one warm pass + a few passes of every hot-path
 kernel at the BASELINE sizes (matching b=8 512x384; GN rays N=32, 200 directed edges; tracker).
+`all` also runs GN calib (N=64), the calibrated tracker and the two front-end kernels once each.
 Usage: python profiles/prof_driver.py [match|gn|track|all] [reps] [gn_iters]"""
 import os
 import sys
@@ -35,5 +36,32 @@ if what in ("track", "all"):
     for _ in range(reps):
         T = torch.tensor([0, 0, 0, 0, 0, 0, 1, 1], dtype=torch.float32, device=dev)
         be.track_ray_dist(d["Xf"], d["Xk"], d["Qk"], d["valid"], T, 0.003, 10.0, 1.345, 50, 1e-3, 1e-3)
+    torch.cuda.synchronize()
+if what == "all":
+    g = synth.make_graph(N=64, counts={1: None, 2: 62, 5: 59, "random": 16}, seed=1237, device=dev)
+    Xs = synth.constrain_points_to_ray(g["Xs"], H, W, g["K"])
+    T = g["Twc"].clone()
+    be.gauss_newton_calib(T, Xs, g["Cs"], g["K"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
+                          H, W, -10, 1e-6, 1.0, 10.0, 0.0, 1.5, 1, 0.0)
+    d = synth.make_tracker_calib_inputs(H, W, seed=1234, device=dev)
+    from mast3r_slam.tracker import FrameTracker
+    from mast3r_slam.sim3 import Sim3
+    trk = FrameTracker(None, None, dev)
+    I = Sim3(torch.tensor([[0, 0, 0, 0, 0, 0, 1, 1.0]], device=dev))
+    uv = torch.stack(torch.meshgrid(torch.arange(W, device=dev), torch.arange(H, device=dev), indexing="xy"), -1)
+    meas = torch.cat((uv.reshape(-1, 2).float(), torch.log(d["Xk"][..., 2:3])), -1)
+    try:
+        trk.opt_pose_calib_sim3(d["Xf"], d["Xk"], I, Sim3(I.data.clone()), d["Qk"], d["valid"], meas,
+                                d["Xk"][..., 2:3] > 1e-6, d["K"], (H, W))
+    except RuntimeError as e:
+        print("calib tracker:", e)
+    E, n = 8, H * W
+    idx = torch.randint(0, n, (E, n), device=dev)
+    vm = torch.rand(E, n, 1, device=dev) > 0.1
+    Qa, Qb = torch.rand(E, n, 1, device=dev) + 1, torch.rand(E, n, 1, device=dev) + 1
+    be.edge_build(idx, vm, Qa, Qb, 1.5)
+    X0, C0 = torch.randn(n, 3, device=dev), torch.rand(n, 1, device=dev) + 0.5
+    be.pointmap_update(X0, C0, torch.randn(n, 3, device=dev), torch.rand(n, 1, device=dev) + 0.5,
+                       "weighted_pointmap", torch.tensor([0.1, 0, 0, 0, 0, 0, 1, 1.0], device=dev))
     torch.cuda.synchronize()
 print("prof_driver ok", what, be.launch_count())
