@@ -233,7 +233,7 @@ def main():
     ms_step = ms_total / K
     value = world * b * N_PIX / (ms_step * 1e-3) / 1e9
     k_ms = [sum(evs[k][i].elapsed_time(evs[k][i + 1]) for k in range(K)) / K for i in range(3)]
-    names = ["match_prep (2 launches)", "iter_proj_fused", "refine_fused"]
+    names = ["match_prep", "iter_proj_fused", "refine_fused"]
     dom = max(range(3), key=lambda i: k_ms[i])
     alg = {0: None, 1: B_ITER_PROJ, 2: B_REFINE}[dom]
     achieved = (alg * b * N_PIX / (k_ms[dom] * 1e-3) / 1e9) if alg else None

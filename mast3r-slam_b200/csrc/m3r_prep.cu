@@ -17,15 +17,17 @@ __device__ __forceinline__ int reflect(int i, int n) {  // F.pad(mode="reflect")
   return i;
 }
 
-__global__ void __launch_bounds__(kPrepTX * kPrepTY)
-prep_rays_kernel(const float* __restrict__ X11, int H, int W, float* __restrict__ out) {
+// One 32x8 pixel tile (bx, by) of image bz; 256 threads, tid = ty*32 + tx.
+__device__ __forceinline__ void prep_rays_tile(const float* __restrict__ X11, int H, int W,
+                                               float* __restrict__ out, int bx, int by, int bz) {
   __shared__ float tile[kPrepTY + 2][kPrepTX + 2][3];
   // output staging: one tile row is kPrepTX*9 contiguous floats in the (b,H,W,9) image, written
   // back as coalesced 16-B words (9 scalar 36-B-strided stores per thread kept the LSU 69 % busy)
   __shared__ __align__(16) float stage[kPrepTY][kPrepTX * 9];
-  const int x0 = blockIdx.x * kPrepTX, y0 = blockIdx.y * kPrepTY;
-  const float* Xb = X11 + (size_t)blockIdx.z * H * W * 3;
-  const int tid = threadIdx.y * kPrepTX + threadIdx.x;
+  const int tid = threadIdx.x;
+  const int thx = tid % kPrepTX, thy = tid / kPrepTX;
+  const int x0 = bx * kPrepTX, y0 = by * kPrepTY;
+  const float* Xb = X11 + (size_t)bz * H * W * 3;
   for (int idx = tid; idx < (kPrepTY + 2) * (kPrepTX + 2); idx += kPrepTX * kPrepTY) {
     const int ty = idx / (kPrepTX + 2), tx = idx % (kPrepTX + 2);
     const int y = reflect(min(y0 + ty - 1, H), H), x = reflect(min(x0 + tx - 1, W), W);
@@ -37,8 +39,8 @@ prep_rays_kernel(const float* __restrict__ X11, int H, int W, float* __restrict_
   }
   __syncthreads();
   {
-    const int tx = threadIdx.x + 1, ty = threadIdx.y + 1;
-    float* o = &stage[threadIdx.y][threadIdx.x * 9];
+    const int tx = thx + 1, ty = thy + 1;
+    float* o = &stage[thy][thx * 9];
     const float k3 = 3.0f / 32.0f, k10 = 10.0f / 32.0f;  // (1/32)*[-3,0,3;-10,0,10;-3,0,3]
 #pragma unroll
     for (int c = 0; c < 3; c++) {
@@ -54,7 +56,7 @@ prep_rays_kernel(const float* __restrict__ X11, int H, int W, float* __restrict_
   const int cols = min(kPrepTX, W - x0);   // valid pixels of this tile row
   const int rows = min(kPrepTY, H - y0);
   const int nfl = cols * 9;                // valid floats per row
-  float* dst0 = out + (((size_t)blockIdx.z * H + y0) * W + x0) * 9;
+  float* dst0 = out + (((size_t)bz * H + y0) * W + x0) * 9;
   const size_t row_stride = (size_t)W * 9;
   if ((nfl & 3) == 0 && (row_stride & 3) == 0 && ((reinterpret_cast<uintptr_t>(dst0) & 15) == 0)) {
     const int per_row = nfl / 4;
@@ -70,11 +72,11 @@ prep_rays_kernel(const float* __restrict__ X11, int H, int W, float* __restrict_
   }
 }
 
-// fp32 -> fp16 (round to nearest even == Tensor.half()), 8 elements per thread.
-__global__ void __launch_bounds__(256)
-cast_f16_kernel(const float* __restrict__ src, size_t count8, size_t count, uint16_t* __restrict__ dst) {
-  const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < count8; i += stride) {
+// fp32 -> fp16 (round to nearest even == Tensor.half()), 8 elements per thread; block `blk` of `nblk`.
+__device__ __forceinline__ void cast_f16_block(const float* __restrict__ src, size_t count8, size_t count,
+                                               uint16_t* __restrict__ dst, int blk, int nblk) {
+  const size_t stride = (size_t)nblk * 256;
+  for (size_t i = (size_t)blk * 256 + threadIdx.x; i < count8; i += stride) {
     const float4 a = ld_stream_f4(src + i * 8), b = ld_stream_f4(src + i * 8 + 4);
     __half2 h0 = __floats2half2_rn(a.x, a.y), h1 = __floats2half2_rn(a.z, a.w);
     __half2 h2 = __floats2half2_rn(b.x, b.y), h3 = __floats2half2_rn(b.z, b.w);
@@ -83,9 +85,43 @@ cast_f16_kernel(const float* __restrict__ src, size_t count8, size_t count, uint
     o.z = *reinterpret_cast<uint32_t*>(&h2); o.w = *reinterpret_cast<uint32_t*>(&h3);
     reinterpret_cast<uint4*>(dst)[i] = o;
   }
-  if (blockIdx.x == 0) {
-    for (size_t i = count8 * 8 + threadIdx.x; i < count; i += blockDim.x)
+  if (blk == 0) {
+    for (size_t i = count8 * 8 + threadIdx.x; i < count; i += 256)
       dst[i] = __half_as_ushort(__float2half_rn(src[i]));
+  }
+}
+
+__global__ void __launch_bounds__(256)
+prep_rays_kernel(const float* __restrict__ X11, int H, int W, int tiles_x, int tiles_y, float* __restrict__ out) {
+  const int t = blockIdx.x, per = tiles_x * tiles_y;
+  prep_rays_tile(X11, H, W, out, (t % per) % tiles_x, (t % per) / tiles_x, t / per);
+}
+
+__global__ void __launch_bounds__(256)
+cast_f16_kernel(const float* __restrict__ src, size_t count8, size_t count, uint16_t* __restrict__ dst) {
+  cast_f16_block(src, count8, count, dst, blockIdx.x, gridDim.x);
+}
+
+// Both jobs of m3r_match_prep in ONE launch: they are independent, one is bound by L1/shared
+// and instruction issue, the other by HBM, so their CTAs overlap on the SMs instead of running
+// back to back with a launch gap in between.  Cast blocks are interleaved 1:2 with ray tiles.
+__global__ void __launch_bounds__(256)
+match_prep_kernel(const float* __restrict__ X11, int H, int W, int tiles_x, int tiles_y, int ray_blocks,
+                  float* __restrict__ rays, const float* __restrict__ D11, size_t count8, size_t count,
+                  int cast_blocks, uint16_t* __restrict__ D11h) {
+  const int t = blockIdx.x;
+  const int trio = t / 3, pos = t % 3;
+  // blocks 3k+2 (while cast blocks last) are cast blocks; everything else is a ray tile
+  const bool is_cast = pos == 2 && trio < cast_blocks;
+  if (is_cast) {
+    cast_f16_block(D11, count8, count, D11h, trio, cast_blocks);
+  } else {
+    const int casts_before = min(trio + (pos == 2 ? 1 : 0), cast_blocks);
+    const int r = t - casts_before;
+    if (r < ray_blocks) {
+      const int per = tiles_x * tiles_y;
+      prep_rays_tile(X11, H, W, rays, (r % per) % tiles_x, (r % per) / tiles_x, r / per);
+    }
   }
 }
 
@@ -98,20 +134,28 @@ extern "C" int m3r_match_prep(const float* X11, const float* D11, int b, int H, 
   if (b < 0 || H < 2 || W < 2 || b > 65535) return M3R_EINVAL;
   if (b == 0) return M3R_OK;
   cudaStream_t st = as_stream(stream);
+  if (rays_img_with_grad && !X11) return M3R_EINVAL;
+  if (D11h && (!D11 || F <= 0)) return M3R_EINVAL;
+  const int tiles_x = (W + kPrepTX - 1) / kPrepTX, tiles_y = (H + kPrepTY - 1) / kPrepTY;
+  const long long ray_blocks_ll = (long long)tiles_x * tiles_y * b;
+  const size_t count = D11h ? (size_t)b * H * W * F : 0;
+  const size_t count8 = count / 8;
+  size_t cast_blocks = (count8 + 255) / 256;
+  if (cast_blocks > (size_t)kNumSMs * 16) cast_blocks = (size_t)kNumSMs * 16;
+  if (cast_blocks < 1) cast_blocks = 1;
+  if (ray_blocks_ll + (long long)cast_blocks > 0x7fffffffLL) return M3R_EINVAL;
+  const int ray_blocks = (int)ray_blocks_ll;
+  if (rays_img_with_grad && D11h && ray_blocks >= 2 * (int)cast_blocks) {
+    match_prep_kernel<<<ray_blocks + (int)cast_blocks, 256, 0, st>>>(
+        X11, H, W, tiles_x, tiles_y, ray_blocks, rays_img_with_grad, D11, count8, count, (int)cast_blocks, D11h);
+    return after_launch();
+  }
   if (rays_img_with_grad) {
-    if (!X11) return M3R_EINVAL;
-    dim3 grid((W + kPrepTX - 1) / kPrepTX, (H + kPrepTY - 1) / kPrepTY, b);
-    prep_rays_kernel<<<grid, dim3(kPrepTX, kPrepTY), 0, st>>>(X11, H, W, rays_img_with_grad);
+    prep_rays_kernel<<<ray_blocks, 256, 0, st>>>(X11, H, W, tiles_x, tiles_y, rays_img_with_grad);
     M3R_TRY(after_launch());
   }
   if (D11h) {
-    if (!D11 || F <= 0) return M3R_EINVAL;
-    const size_t count = (size_t)b * H * W * F;
-    const size_t count8 = count / 8;
-    size_t blocks = (count8 + 255) / 256;
-    if (blocks > (size_t)kNumSMs * 16) blocks = (size_t)kNumSMs * 16;
-    if (blocks < 1) blocks = 1;
-    cast_f16_kernel<<<(int)blocks, 256, 0, st>>>(D11, count8, count, D11h);
+    cast_f16_kernel<<<(int)cast_blocks, 256, 0, st>>>(D11, count8, count, D11h);
     M3R_TRY(after_launch());
   }
   return M3R_OK;
