@@ -182,9 +182,11 @@ def test_rays_full_size_vs_reference_and_properties(backends, ref_ext):
     assert torch.equal(Ta, Tb)
 
 
-@pytest.mark.parametrize("N", [40, 150])
+@pytest.mark.parametrize("N", [40, 150, 260])
 def test_many_keyframes_dense_cholesky(backends, orc, N):
-    """Graphs whose normal equations span many 32x32 tiles (N=40: 9x9 tiles, N=150: 33x33): the
+    """Graphs whose normal equations span many 32x32 tiles (N=40: 9x9 tiles, single-CTA back
+    substitution; N=150: 33x33, distributed back substitution; N=260: 57x57, pose rows beyond the
+    assembly kernel's shared-memory row buffer take its global-memory path): the
     device assembly + tile-dataflow Cholesky (flags across >100 CTAs, back-substitution chain)
     against a numpy fp64 assembly + solve of the SAME per-edge blocks (SparseBlock semantics,
     gn_kernels.cu:71-153), which isolates the solver from the conditioning of these tiny-image
