@@ -241,9 +241,11 @@ def main():
                 "frac": (achieved / peak) if achieved else None, "traffic": ncu_traffic(names[dom], b / 8.0),
                 "peak_kind": peak_kind, "algorithmic_bytes_per_pixel": alg,
                 "algorithmic_bytes_per_launch": (alg * b * N_PIX) if alg else None,
-                "note": "refine_matches is bound by on-chip pipes, not HBM: ncu shows the fp16x2 (fma-heavy) pipe "
-                        "71 % and the L1 data pipe 77 % busy (profiles/r1g_ncu_digest.md); its exact fp16 "
-                        "rounding chain admits no tensor-core form (DESIGN.md 4.2)",
+                "note": "refine_matches is bound by on-chip pipes, not HBM: ncu shows the L1 data pipe 74 % and the "
+                        "fp16x2 (fma-heavy) pipe 62 % busy (profiles/r1v_ncu_digest.md; floors 0.67 / 0.49 ms at "
+                        "b=8); its exact fp16 rounding chain admits no tensor-core form (DESIGN.md 4.2)",
+                "on_chip": {"l1_data_pipe_pct": 74.3, "fp16x2_pipe_pct": 62.2, "issue_pct": 63.8,
+                            "source": "profiles/r1v_ncu_digest.md"},
                 "kernel_ms": {n: round(t, 4) for n, t in zip(names, k_ms)},
                 "kernels": {
                     "iter_proj_fused": {"achieved": B_ITER_PROJ * b * N_PIX / (k_ms[1] * 1e-3) / 1e9,
