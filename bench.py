@@ -310,6 +310,7 @@ def main():
                 extra.update(bench_gn_calib(be, synth, dev))
                 extra.update(bench_tracker(be, synth, dev, peak))
                 extra.update(bench_frontend(be, synth, dev, peak))
+                extra.update(bench_viewer(be, synth, dev, peak, cpu=not args.no_cpu))
             if not args.no_large:
                 extra.update(bench_gn_large(be, synth, dev, rank, world, peak, barrier, max_over_ranks))
         except Exception as e:  # keep the headline line even if an extra fails
@@ -319,9 +320,10 @@ def main():
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
-        t = cpu_match_sample(2, threads)
-        cpu = {"value": 2 * N_PIX / t / 1e9, "unit": "Gpix/s", "cores": threads, "kind": "port",
-               "sample": f"2 frame pairs of {W}x{H}, one pass ({t:.1f} s): oracle C port of iter_proj + "
+        nb = 6  # ~10 s of host work
+        t = cpu_match_sample(nb, threads)
+        cpu = {"value": nb * N_PIX / t / 1e9, "unit": "Gpix/s", "cores": threads, "kind": "port",
+               "sample": f"{nb} frame pairs of {W}x{H}, one pass ({t:.1f} s): oracle C port of iter_proj + "
                          "refine_matches (OpenMP) + torch-CPU glue"}
 
     if rank == 0:
@@ -591,6 +593,50 @@ def bench_frontend(be, synth, dev, peak):
     out["tracker_calib"] = {"workload": "opt_pose_calib_sim3 512x384, known Sim3 offset", "iterations": its,
                             "ms_per_solve": ms, "iters_per_s": its / (ms * 1e-3)}
     return {"frontend": out}
+
+
+def bench_viewer(be, synth, dev, peak, cpu=True):
+    """SURVEY 8f last row: the viewer's surfel / triangle pointmap programs splatted into a device
+    buffer (csrc/m3r_render.cu), all keyframes of a map in one launch."""
+    import time
+
+    import torch
+
+    nk, w, h = 24, 1024, 768  # 24 keyframes x 196608 points x 28 B = 132 MB > L2
+    sc = synth.make_render_scene(K=nk, seed=1242, device=dev)
+    fb = torch.empty((h, w), dtype=torch.int64, device=dev)
+    out = {"workload": f"{nk} keyframes of 512x384 (X, C, image) drawn into a {w}x{h} buffer, viewer behind keyframe 0",
+           "algorithmic_bytes_per_point": 28}
+    by = 28 * nk * N_PIX
+    for program, kw in (("surfelmap", dict(radius=0.004)), ("trianglemap", dict())):
+        opts = be.render_opts(**kw)
+
+        def draw():
+            be.render_clear(fb)
+            be.render_pointmaps(program, sc["X"], sc["C"], sc["img"], sc["models"], sc["camera"], sc["proj"], fb, opts)
+        for _ in range(3):
+            draw()
+        a = torch.cuda.Event(enable_timing=True); z = torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(); a.record()
+        for _ in range(10):
+            draw()
+        z.record(); torch.cuda.synchronize()
+        ms = a.elapsed_time(z) / 10
+        _, depth = be.render_resolve(fb)
+        out[program] = {"ms_clear_plus_draw": ms, "Mpoints_per_s": nk * N_PIX / (ms * 1e-3) / 1e6,
+                        "achieved": by / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                        "frac": by / (ms * 1e-3) / 1e9 / peak,
+                        "covered_fraction": float((depth < 1).float().mean())}
+    if cpu:
+        from oracle import render as orender
+        one = {k: (v[:1].cpu().numpy() if k in ("X", "C", "img", "models") else v) for k, v in sc.items()}
+        t0 = time.perf_counter()
+        orender.render("trianglemap", one["X"], one["C"], one["img"], one["models"], sc["camera"].cpu().numpy(),
+                       sc["proj"].cpu().numpy(), w, h)
+        t = time.perf_counter() - t0
+        out["cpu_port"] = {"program": "trianglemap", "sample": "1 keyframe, 1 thread (oracle C restatement)",
+                           "Mpoints_per_s": N_PIX / t / 1e6}
+    return {"viewer_splat": out}
 
 
 if __name__ == "__main__":

@@ -284,6 +284,52 @@ int m3r_edge_build(const int64_t* idx_src2dst, const uint8_t* valid_match, const
 int m3r_pointmap_update(float* X_canon, float* C, const float* X_new, const float* C_new,
                         const float* T_act, int n, int mode, m3r_stream_t stream);
 
+/* ------------------------------------------------------------------------- *
+ * Headless splat of the viewer's pointmap shaders (last row)
+ * ------------------------------------------------------------------------- *
+ * Replaces, for a device buffer instead of a window, the two GLSL programs the viewer draws
+ * keyframe pointmaps with — resources/programs/surfelmap.glsl and trianglemap.glsl — as driven
+ * by Window.render_pointmap (visualization.py:334-356) under DEPTH_TEST + CULL_FACE
+ * (visualization.py:100-103).  No graphics API is involved.
+ *   fb (height*width) u64, caller-owned: word = (float bits of window depth << 32) | RGBA8
+ *   (R in the low byte), row 0 = BOTTOM row (GL window coordinates).  m3r_render_clear sets
+ *   depth 1.0 + the clear colour; the render calls depth-test with one 64-bit atomicMin per
+ *   fragment, so any number of them may be enqueued on the same buffer in any order;
+ *   m3r_render_resolve unpacks to a top-down RGBA8 image and/or a float depth image.
+ * Matrices are ROW-MAJOR 4x4 (clip = proj * camera * model * [p,1]); the reference passes the
+ * transposes to GL (visualization.py:340-344).  models: (K,4,4) f32 on the DEVICE, one per
+ * keyframe = T_WC.matrix(); X (K,H,W,3), C (K,H,W), img (K,H,W,3) f32 device.
+ * Deviations from a GL rasteriser are listed at the top of csrc/m3r_render.cu. */
+typedef struct m3r_render_view {
+  float camera[16];  /* world -> view  (m_camera) */
+  float proj[16];    /* view -> clip   (m_proj)   */
+  int width, height; /* target size in pixels */
+} m3r_render_view;
+
+typedef struct m3r_render_opts {
+  float conf_threshold;  /* uniform conf_threshold (WindowMsg.C_conf_threshold = 1.5) */
+  float radius;          /* surfelmap.glsl:17, 0.003 */
+  float slant_threshold; /* trianglemap.glsl:17, 0.1 */
+  float depth_bias;      /* trianglemap.glsl:18 */
+  float lightpos[3];     /* (0.1, 0.1, 0) */
+  float phong[3];        /* (0.3, 0.5, 0.4) */
+  float spec;            /* 32 */
+  float base_color[3];   /* (1, 1, 1) */
+  int use_img, show_normal, cull_face;
+} m3r_render_opts;
+
+void m3r_render_default_opts(m3r_render_opts* opts);
+int m3r_render_clear(uint64_t* fb, int width, int height, uint32_t clear_rgba,
+                     m3r_stream_t stream);
+int m3r_render_surfels(const float* X, const float* C, const float* img, const float* models,
+                       int num_keyframes, int H, int W, const m3r_render_view* view,
+                       const m3r_render_opts* opts, uint64_t* fb, m3r_stream_t stream);
+int m3r_render_triangles(const float* X, const float* C, const float* img, const float* models,
+                         int num_keyframes, int H, int W, const m3r_render_view* view,
+                         const m3r_render_opts* opts, uint64_t* fb, m3r_stream_t stream);
+int m3r_render_resolve(const uint64_t* fb, int width, int height, uint8_t* rgba, float* depth,
+                       m3r_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -42,6 +42,18 @@ class _GNPeers(C.Structure):
 
 GN_RAYS, GN_CALIB, GN_POINTS = 0, 1, 2
 
+
+class _RenderView(C.Structure):
+    _fields_ = [("camera", C.c_float * 16), ("proj", C.c_float * 16), ("width", C.c_int),
+                ("height", C.c_int)]
+
+
+class _RenderOpts(C.Structure):
+    _fields_ = [("conf_threshold", C.c_float), ("radius", C.c_float), ("slant_threshold", C.c_float),
+                ("depth_bias", C.c_float), ("lightpos", C.c_float * 3), ("phong", C.c_float * 3),
+                ("spec", C.c_float), ("base_color", C.c_float * 3), ("use_img", C.c_int),
+                ("show_normal", C.c_int), ("cull_face", C.c_int)]
+
 EXPORTS = [
     "m3r_version", "m3r_error_string", "m3r_last_cuda_error", "m3r_launch_count",
     "m3r_iter_proj", "m3r_refine_matches_f16", "m3r_refine_matches_f32", "m3r_match_prep",
@@ -49,6 +61,8 @@ EXPORTS = [
     "m3r_gn_workspace_bytes", "m3r_gauss_newton", "m3r_gn_prepare", "m3r_gn_accumulate",
     "m3r_gn_solve_step", "m3r_gn_done_flag", "m3r_gn_blocks", "m3r_track_workspace_bytes",
     "m3r_track_ray_dist", "m3r_track_calib", "m3r_debug_chol_trace", "m3r_edge_build", "m3r_pointmap_update", "m3r_gn_accumulate_p2p", "m3r_gn_solve_step_p2p",
+    "m3r_render_default_opts", "m3r_render_clear", "m3r_render_surfels", "m3r_render_triangles",
+    "m3r_render_resolve",
 ]
 
 
@@ -96,6 +110,13 @@ def _load():
     lib.m3r_gn_solve_step_p2p.argtypes = [vp, pp, i32, i32, f32, vp, vp, sz, vp]
     lib.m3r_edge_build.argtypes = [vp, vp, vp, vp, i32, i32, f32, vp, vp, vp]
     lib.m3r_pointmap_update.argtypes = [vp, vp, vp, vp, vp, i32, i32, vp]
+    rv, ro = C.POINTER(_RenderView), C.POINTER(_RenderOpts)
+    lib.m3r_render_default_opts.restype = None
+    lib.m3r_render_default_opts.argtypes = [ro]
+    lib.m3r_render_clear.argtypes = [vp, i32, i32, C.c_uint32, vp]
+    lib.m3r_render_surfels.argtypes = [vp, vp, vp, vp, i32, i32, i32, rv, ro, vp, vp]
+    lib.m3r_render_triangles.argtypes = [vp, vp, vp, vp, i32, i32, i32, rv, ro, vp, vp]
+    lib.m3r_render_resolve.argtypes = [vp, i32, i32, vp, vp, vp]
     return lib
 
 
@@ -572,3 +593,70 @@ def pointmap_update(X_canon, C, X_new, C_new, mode="weighted_pointmap", T_act=No
         _check(_lib.m3r_pointmap_update(_ptr(Xc), _ptr(Cc), _ptr(Xn), _ptr(Cn), _ptr(T_act), Xc.shape[0],
                                         POINTMAP_MODES[mode], _stream(Xc)), "pointmap_update")
     return Xc, Cc
+
+
+# --------------------------------------------------------------------------- headless viewer splat
+
+def render_opts(**kw):
+    """m3r_render_opts with the shaders' uniform defaults (surfelmap.glsl:17,99-104,
+    trianglemap.glsl:17-18) and the viewer's state (visualization.py:38,77), overridden by kw."""
+    o = _RenderOpts()
+    _lib.m3r_render_default_opts(C.byref(o))
+    for k, v in kw.items():
+        if not hasattr(o, k):
+            raise TypeError(f"render_opts: unknown option {k}")
+        if k in ("lightpos", "phong", "base_color"):
+            getattr(o, k)[:] = [float(x) for x in v]
+        else:
+            setattr(o, k, v)
+    return o
+
+
+def render_clear(fb, clear_rgba=0xFF26231E):
+    """fb (height,width) int64 CUDA (packed depth|RGBA8 words): depth 1.0 + clear colour
+    (default #1E2326, visualization.py:53)."""
+    fb = _req(fb, "fb", torch.int64, 2)
+    _check(_lib.m3r_render_clear(_ptr(fb), fb.shape[1], fb.shape[0], C.c_uint32(clear_rgba), _stream(fb)),
+           "render_clear")
+    return fb
+
+
+def render_pointmaps(program, X, Cf, img, models, camera, proj, fb, opts=None):
+    """Splat K keyframe pointmaps into fb with the arithmetic of `program` ("surfelmap" |
+    "trianglemap": resources/programs/*.glsl).  X (K,H,W,3), Cf (K,H,W), img (K,H,W,3), models
+    (K,4,4) f32 CUDA; camera, proj: 16 floats each, row-major, host."""
+    X = _req(X, "X", torch.float32, 4)
+    Cf = _req(Cf, "C", torch.float32, 3)
+    img = _req(img, "img", torch.float32, 4)
+    models = _req(models, "models", torch.float32, 3)
+    fb = _req(fb, "fb", torch.int64, 2)
+    K, H, W, _ = X.shape
+    if Cf.shape != (K, H, W) or img.shape != (K, H, W, 3) or models.shape != (K, 4, 4) or X.shape[3] != 3:
+        raise RuntimeError("render_pointmaps: X (K,H,W,3), C (K,H,W), img (K,H,W,3), models (K,4,4)")
+    if program not in ("surfelmap", "trianglemap"):
+        raise RuntimeError("render_pointmaps: program must be 'surfelmap' or 'trianglemap'")
+    view = _RenderView()
+    cam = [float(x) for x in torch.as_tensor(camera, dtype=torch.float32).reshape(-1).tolist()]
+    prj = [float(x) for x in torch.as_tensor(proj, dtype=torch.float32).reshape(-1).tolist()]
+    if len(cam) != 16 or len(prj) != 16:
+        raise RuntimeError("render_pointmaps: camera and proj must be 4x4")
+    view.camera[:] = cam
+    view.proj[:] = prj
+    view.width, view.height = fb.shape[1], fb.shape[0]
+    o = opts if opts is not None else render_opts()
+    fn = _lib.m3r_render_surfels if program == "surfelmap" else _lib.m3r_render_triangles
+    with torch.cuda.device(X.device):
+        _check(fn(_ptr(X), _ptr(Cf), _ptr(img), _ptr(models), K, H, W, C.byref(view), C.byref(o),
+                  _ptr(fb), _stream(X)), "render_pointmaps")
+    return fb
+
+
+def render_resolve(fb, want_depth=True):
+    """-> (rgba (h,w,4) u8 top-down, depth (h,w) f32 top-down or None)"""
+    fb = _req(fb, "fb", torch.int64, 2)
+    h, w = fb.shape
+    with torch.cuda.device(fb.device):
+        rgba = torch.empty((h, w, 4), dtype=torch.uint8, device=fb.device)
+        depth = torch.empty((h, w), dtype=torch.float32, device=fb.device) if want_depth else None
+        _check(_lib.m3r_render_resolve(_ptr(fb), w, h, _ptr(rgba), _ptr(depth), _stream(fb)), "render_resolve")
+    return rgba, depth

@@ -1,7 +1,8 @@
 """Short single-GPU driver for ncu captures: one warm pass + a few passes of every hot-path
 kernel at the BASELINE sizes (matching b=8 512x384; GN rays N=32, 200 directed edges; tracker).
 `all` also runs GN calib (N=64), the calibrated tracker and the two front-end kernels once each.
-Usage: python profiles/prof_driver.py [match|gn|track|all] [reps] [gn_iters]"""
+`render` (also part of `all`) draws 24 keyframes with both viewer programs into a 1024x768 buffer.
+Usage: python profiles/prof_driver.py [match|gn|track|render|all] [reps] [gn_iters]"""
 import os
 import sys
 
@@ -63,5 +64,15 @@ if what == "all":
     X0, C0 = torch.randn(n, 3, device=dev), torch.rand(n, 1, device=dev) + 0.5
     be.pointmap_update(X0, C0, torch.randn(n, 3, device=dev), torch.rand(n, 1, device=dev) + 0.5,
                        "weighted_pointmap", torch.tensor([0.1, 0, 0, 0, 0, 0, 1, 1.0], device=dev))
+    torch.cuda.synchronize()
+if what in ("render", "all"):
+    sc = synth.make_render_scene(K=24, seed=1242, device=dev)
+    fb = torch.empty((768, 1024), dtype=torch.int64, device=dev)
+    for _ in range(reps):
+        for program, kw in (("surfelmap", dict(radius=0.004)), ("trianglemap", dict())):
+            be.render_clear(fb)
+            be.render_pointmaps(program, sc["X"], sc["C"], sc["img"], sc["models"], sc["camera"], sc["proj"], fb,
+                                be.render_opts(**kw))
+    be.render_resolve(fb)
     torch.cuda.synchronize()
 print("prof_driver ok", what, be.launch_count())

@@ -305,3 +305,53 @@ def make_symmetric_match_outputs(E, H=H0, W=W0, seed=77, device="cpu", weak=()):
         q = smooth_noise((E, 1, H, W), 4.0 * W / W0, gen, device).view(E, n, 1)
         out[name] = (1.0 + torch.exp(0.7 + 0.5 * q)).contiguous()
     return out
+
+
+# ----------------------------------------------------------------------------- headless viewer
+
+def sim3_matrix(T):
+    """(N,8) [t, q(xyzw), s] -> (N,4,4) row-major [sR t; 0 1]  (lietorch Sim3.matrix())."""
+    N = T.shape[0]
+    M = torch.zeros((N, 4, 4), dtype=torch.float32, device=T.device)
+    eye = torch.eye(3, device=T.device).expand(N, 3, 3)
+    for c in range(3):
+        M[:, :3, c] = T[:, 7:8] * quat_rot(T[:, 3:7], eye[:, :, c])
+    M[:, :3, 3] = T[:, 0:3]
+    M[:, 3, 3] = 1.0
+    return M.contiguous()
+
+
+def gl_perspective(fov_y_deg, aspect, near, far):
+    t = 1.0 / math.tan(math.radians(fov_y_deg) / 2.0)
+    return torch.tensor([[t / aspect, 0, 0, 0], [0, t, 0, 0],
+                         [0, 0, -(far + near) / (far - near), -2.0 * far * near / (far - near)],
+                         [0, 0, -1, 0]], dtype=torch.float32)
+
+
+def gl_view_of_pose(T):
+    """GL view matrix (row-major) of a viewer camera at the CV-convention pose T (8,), scale ignored."""
+    eye = torch.eye(3, device=T.device)
+    R = torch.stack([quat_rot(T[None, 3:7], eye[None, :, c])[0] for c in range(3)], -1)  # columns
+    V = torch.eye(4, device=T.device)
+    V[:3, :3] = R.T
+    V[:3, 3] = -(R.T @ T[0:3])
+    flip = torch.diag(torch.tensor([1.0, -1.0, -1.0, 1.0], device=T.device))
+    return (flip @ V).float().contiguous()
+
+
+def make_render_scene(K=3, H=H0, W=W0, seed=1240, device="cpu"):
+    """K keyframes looking at the analytic surface (same generator as the graph configs) with
+    colours, confidences (a low-confidence band below the viewer's 1.5 threshold) and a viewer
+    camera placed behind keyframe 0, slightly off-axis.  Returns the tensors the viewer uploads
+    as textures (visualization.py:150-152: X, C, uimg) plus model/view/projection matrices."""
+    Kc = intrinsics(H, W, device)
+    T = make_poses(max(K, 2), seed, device)[:K]
+    X = render_pointmaps(T, H, W, Kc).view(K, H, W, 3).contiguous()
+    gen = _gen(seed + 3, device)
+    cn = smooth_noise((K, 1, H, W), 6.0 * W / W0, gen, device)[:, 0]
+    C = (1.0 + torch.exp(0.9 + 0.8 * cn)).contiguous()  # ~8 % below 1.5
+    img = torch.sigmoid(1.5 * smooth_noise((K, 3, H, W), 3.0 * W / W0, gen, device)).permute(0, 2, 3, 1).contiguous()
+    viewer = T[0].clone()
+    viewer[0:3] = viewer[0:3] + quat_rot(viewer[None, 3:7], torch.tensor([[0.15, -0.1, -0.6]], device=device))[0]
+    return dict(X=X, C=C, img=img, models=sim3_matrix(T), camera=gl_view_of_pose(viewer),
+                proj=gl_perspective(55.0, 4.0 / 3.0, 0.05, 50.0), T=T, H=H, W=W, K=K)
