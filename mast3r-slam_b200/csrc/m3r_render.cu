@@ -19,8 +19,11 @@
 //     dropped instead of clipped; near/far clipping is per fragment (0 <= depth < 1);
 //   * equal depths are resolved by the smaller colour word, not by draw order (deterministic);
 //   * pow(x, spec) is evaluated by repeated squaring when spec is a small integer (the
-//     defaults 32, 2, 3), so that every operation is an IEEE single-rounding one: the CPU
-//     restatement (oracle/m3r_render_oracle.c) then reproduces the image bit for bit.
+//     defaults 32, 2, 3), normalize(v) as v * (1 / sqrt(v.v)), the perspective divide and the
+//     attribute interpolation with one reciprocal each, length(t) > 1 as t.t > 1 — so that every
+//     operation is an IEEE single-rounding one and divisions are few: the CPU restatement
+//     (oracle/m3r_render_oracle.c) then reproduces the image bit for bit;
+//   * targets are limited to 2^24 pixels (4096 x 4096).
 // Every float operation is an explicit round-to-nearest intrinsic (no FMA contraction except the
 // fmaf written here), mirrored one to one by the oracle.
 #include "m3r_common.cuh"
@@ -50,10 +53,6 @@ __device__ __forceinline__ V3 cross3(V3 a, V3 b) {
   return v3(fmaf_(a.y, b.z, -mulf(a.z, b.y)), fmaf_(a.z, b.x, -mulf(a.x, b.z)),
             fmaf_(a.x, b.y, -mulf(a.y, b.x)));
 }
-__device__ __forceinline__ V3 normalize3v(V3 a) {
-  const float len = __fsqrt_rn(dot3(a, a));
-  return v3(divf(a.x, len), divf(a.y, len), divf(a.z, len));
-}
 // rows 0..2 of a row-major 4x4 applied to [p, 1]
 __device__ __forceinline__ float row_apply(const float* m, V3 p) {
   return fmaf_(m[0], p.x, fmaf_(m[1], p.y, fmaf_(m[2], p.z, m[3])));
@@ -71,19 +70,11 @@ __device__ void mat4_mul(const float* a, const float* b, float* out) {
     }
 }
 
-struct Vtx {
-  float cx, cy, cz, cw;  // clip position
-  V3 pos;                // view-space position (mv * p)
-  V3 col;                // vertex colour (triangle map)
-  float tu, tv;          // fragTexCoord (surfel map)
-};
-
-struct Shade {
-  V3 normal;   // view-space normal, constant over the primitive
-  V3 col;      // constant colour (surfel map)
-  bool disk;   // surfel: discard |texcoord| > 1, colour constant; triangle: colour interpolated
-  float spec_power_noimg;
-};
+// normalize(v) := v * (1 / sqrt(v.v))  — one square root, one division (GLSL leaves the precision open)
+__device__ __forceinline__ V3 normalize_rcp(V3 a) {
+  const float inv = divf(1.f, __fsqrt_rn(dot3(a, a)));
+  return v3(mulf(a.x, inv), mulf(a.y, inv), mulf(a.z, inv));
+}
 
 __device__ __forceinline__ float pow_spec(float x, float p) {
   const int n = (int)p;
@@ -105,14 +96,14 @@ __device__ __forceinline__ uint32_t to_unorm8(float c) {
   return (uint32_t)(int)addf(mulf(c, 255.f), 0.5f);
 }
 
-// Fragment shader (surfelmap.glsl:106-135, trianglemap.glsl:118-143).
-__device__ __forceinline__ uint32_t shade(const RenderParams& P, const Shade& S, V3 position, V3 color) {
+// Fragment shader (surfelmap.glsl:106-135, trianglemap.glsl:118-143).  N is the view-space normal,
+// already normalised (it is constant over the primitive).
+__device__ __forceinline__ uint32_t shade(const RenderParams& P, float spec_noimg, V3 N, V3 position, V3 color) {
   const bool ui = P.use_img != 0;
   const float kA = ui ? P.phong[0] : 0.1f, kD = ui ? P.phong[1] : 0.2f, kS = ui ? P.phong[2] : 1.3f;
   const V3 fc = ui ? color : v3(P.base_color[0], P.base_color[1], P.base_color[2]);
-  const float sp = ui ? P.spec : S.spec_power_noimg;
-  const V3 L = normalize3v(sub3(v3(P.light[0], P.light[1], P.light[2]), position));
-  V3 N = normalize3v(S.normal);
+  const float sp = ui ? P.spec : spec_noimg;
+  const V3 L = normalize_rcp(sub3(v3(P.light[0], P.light[1], P.light[2]), position));
   const float lambertian = fmaxf(dot3(N, L), 0.f);
   float specular = 0.f;
   if (lambertian > 0.f) {
@@ -120,7 +111,7 @@ __device__ __forceinline__ uint32_t shade(const RenderParams& P, const Shade& S,
     const V3 R = v3(subf(mulf(mulf(2.f, mulf(L.x, N.x)), N.x), L.x),
                     subf(mulf(mulf(2.f, mulf(L.y, N.y)), N.y), L.y),
                     subf(mulf(mulf(2.f, mulf(L.z, N.z)), N.z), L.z));
-    const V3 V = normalize3v(v3(-position.x, -position.y, -position.z));
+    const V3 V = normalize_rcp(v3(-position.x, -position.y, -position.z));
     specular = pow_spec(fmaxf(dot3(R, V), 0.f), sp);
   }
   const float diff = addf(kA, mulf(lambertian, kD)), sadd = mulf(kS, specular);
@@ -131,90 +122,25 @@ __device__ __forceinline__ uint32_t shade(const RenderParams& P, const Shade& S,
   return to_unorm8(out.x) | (to_unorm8(out.y) << 8) | (to_unorm8(out.z) << 16) | 0xFF000000u;
 }
 
-struct Snap { long long x, y; float zndc, w; bool ok; };
+constexpr int kRenderThreads = 128;
 
-__device__ __forceinline__ Snap snap_vertex(const RenderParams& P, const Vtx& v) {
-  Snap s;
-  s.w = v.cw;
-  s.ok = v.cw > 0.f;
-  const float nx = divf(v.cx, v.cw), ny = divf(v.cy, v.cw);
-  s.zndc = divf(v.cz, v.cw);
-  const float wx = mulf(fmaf_(nx, 0.5f, 0.5f), (float)P.fbw), wy = mulf(fmaf_(ny, 0.5f, 0.5f), (float)P.fbh);
-  const float lim = 1048576.f;
-  s.ok = s.ok && (fabsf(wx) <= lim) && (fabsf(wy) <= lim) && (s.zndc == s.zndc) && (fabsf(s.zndc) <= 3.0e38f);
-  s.x = s.ok ? (long long)__float2int_rn(mulf(wx, 256.f)) : 0;
-  s.y = s.ok ? (long long)__float2int_rn(mulf(wy, 256.f)) : 0;
-  return s;
-}
+// Per-primitive record in shared memory, one column per thread (word-major: lanes that read
+// the same word of different primitives hit different banks, lanes on the same primitive broadcast).
+//   ints  : X[4], Y[4] snapped window coordinates (1/256 px), x0, y0, bw (bounding box), flags
+//   floats: zndc[4], rw[4] (1/w_clip), pos[4][3], N[3] (normalised view-space normal),
+//           inv_area[2], col[3] (surfel) or col[4][3] (triangle map)
+enum { I_X = 0, I_Y = 4, I_X0 = 8, I_Y0 = 9, I_BW = 10, I_FLAGS = 11, kPrimInts = 12 };
+enum { F_Z = 0, F_RW = 4, F_POS = 8, F_N = 20, F_IA = 23, F_COL = 25 };
+template <int PROGRAM> struct PrimWords { static constexpr int kFloats = PROGRAM == 0 ? 28 : 37; };
+// flags: bit 0/1 = triangle 0/1 drawn, bit 2/3 = triangle 0/1 flipped to CCW (culling off)
 
-__device__ __forceinline__ long long edge_fn(long long ax, long long ay, long long bx, long long by,
-                                             long long px, long long py) {
-  return (bx - ax) * (py - ay) - (by - ay) * (px - ax);
+struct PrimVertex { float cx, cy, cz, cw; V3 pos; };
+
+__device__ __forceinline__ long long edge_fn(int ax, int ay, int bx, int by, int px, int py) {
+  return (long long)(bx - ax) * (long long)(py - ay) - (long long)(by - ay) * (long long)(px - ax);
 }
 // pixel centres exactly on an edge belong to the triangle iff the edge is a left or a top edge
-__device__ __forceinline__ bool owns_edge(long long dx, long long dy) { return dy < 0 || (dy == 0 && dx < 0); }
-
-__device__ __forceinline__ long long floor_div256(long long v) { return v >> 8; }  // arithmetic shift
-
-__device__ void raster_triangle(const RenderParams& P, const Shade& S, unsigned long long* __restrict__ fb,
-                                Vtx a, Vtx b, Vtx c) {
-  Snap sa = snap_vertex(P, a), sb = snap_vertex(P, b), sc = snap_vertex(P, c);
-  if (!(sa.ok && sb.ok && sc.ok)) return;
-  long long area2 = edge_fn(sa.x, sa.y, sb.x, sb.y, sc.x, sc.y);
-  if (area2 == 0) return;
-  if (area2 < 0) {
-    if (P.cull) return;  // back face (CCW is front, GL default)
-    const Vtx tv = b; b = c; c = tv;
-    const Snap ts = sb; sb = sc; sc = ts;
-    area2 = -area2;
-  }
-  const long long minx = min(sa.x, min(sb.x, sc.x)), maxx = max(sa.x, max(sb.x, sc.x));
-  const long long miny = min(sa.y, min(sb.y, sc.y)), maxy = max(sa.y, max(sb.y, sc.y));
-  // pixel (px, py) has its centre at (256 px + 128, 256 py + 128)
-  const int x0 = (int)max(0LL, floor_div256(minx - 128 + 255)), x1 = (int)min((long long)P.fbw - 1, floor_div256(maxx - 128));
-  const int y0 = (int)max(0LL, floor_div256(miny - 128 + 255)), y1 = (int)min((long long)P.fbh - 1, floor_div256(maxy - 128));
-  if (x0 > x1 || y0 > y1) return;
-  const bool own_a = owns_edge(sc.x - sb.x, sc.y - sb.y);  // edge b->c, opposite a
-  const bool own_b = owns_edge(sa.x - sc.x, sa.y - sc.y);
-  const bool own_c = owns_edge(sb.x - sa.x, sb.y - sa.y);
-  const float fa2 = (float)area2;
-  for (int py = y0; py <= y1; py++) {
-    for (int px = x0; px <= x1; px++) {
-      const long long cx = 256LL * px + 128, cy = 256LL * py + 128;
-      const long long wa = edge_fn(sb.x, sb.y, sc.x, sc.y, cx, cy);
-      const long long wb = edge_fn(sc.x, sc.y, sa.x, sa.y, cx, cy);
-      const long long wc = edge_fn(sa.x, sa.y, sb.x, sb.y, cx, cy);
-      if (wa < 0 || wb < 0 || wc < 0) continue;
-      if ((wa == 0 && !own_a) || (wb == 0 && !own_b) || (wc == 0 && !own_c)) continue;
-      const float la = divf((float)wa, fa2), lb = divf((float)wb, fa2), lc = divf((float)wc, fa2);
-      const float zn = fmaf_(lc, sc.zndc, fmaf_(lb, sb.zndc, mulf(la, sa.zndc)));
-      const float zw = fmaf_(zn, 0.5f, 0.5f);
-      if (!(zw >= 0.f && zw < 1.f)) continue;
-      unsigned long long* dst = fb + (size_t)py * P.fbw + px;
-      const uint32_t zbits = __float_as_uint(zw);
-      // early depth test: the stored word only ever decreases, so a stale read is conservative
-      if ((uint32_t)(*reinterpret_cast<volatile unsigned long long*>(dst) >> 32) < zbits) continue;
-      // perspective-correct weights
-      const float qa = divf(la, sa.w), qb = divf(lb, sb.w), qc = divf(lc, sc.w);
-      const float qs = addf(addf(qa, qb), qc);
-#define M3R_INTERP(fa_, fb_, fc_) divf(fmaf_(qc, fc_, fmaf_(qb, fb_, mulf(qa, fa_))), qs)
-      if (S.disk) {  // surfelmap.glsl:107-111
-        const float tu = M3R_INTERP(a.tu, b.tu, c.tu), tv = M3R_INTERP(a.tv, b.tv, c.tv);
-        const float dist = __fsqrt_rn(fmaf_(tu, tu, mulf(tv, tv)));
-        if (dist > 1.0f) continue;
-      }
-      const V3 pos = v3(M3R_INTERP(a.pos.x, b.pos.x, c.pos.x), M3R_INTERP(a.pos.y, b.pos.y, c.pos.y),
-                        M3R_INTERP(a.pos.z, b.pos.z, c.pos.z));
-      V3 col = S.col;
-      if (!S.disk)
-        col = v3(M3R_INTERP(a.col.x, b.col.x, c.col.x), M3R_INTERP(a.col.y, b.col.y, c.col.y),
-                 M3R_INTERP(a.col.z, b.col.z, c.col.z));
-#undef M3R_INTERP
-      const uint32_t rgba = shade(P, S, pos, col);
-      atomicMin(dst, ((unsigned long long)zbits << 32) | rgba);
-    }
-  }
-}
+__device__ __forceinline__ bool owns_edge(int dx, int dy) { return dy < 0 || (dy == 0 && dx < 0); }
 
 // per-CTA: mv = camera * model, mvp = proj * mv for keyframe blockIdx.y
 __device__ __forceinline__ void block_matrices(const RenderParams& P, const float* __restrict__ models,
@@ -228,7 +154,7 @@ __device__ __forceinline__ void block_matrices(const RenderParams& P, const floa
   __syncthreads();
 }
 
-__device__ __forceinline__ void transform_vertex(const float* mv, const float* mvp, V3 p, Vtx& v) {
+__device__ __forceinline__ void transform_vertex(const float* mv, const float* mvp, V3 p, PrimVertex& v) {
   v.pos = v3(row_apply(mv, p), row_apply(mv + 4, p), row_apply(mv + 8, p));
   v.cx = row_apply(mvp, p); v.cy = row_apply(mvp + 4, p); v.cz = row_apply(mvp + 8, p);
   v.cw = row_apply(mvp + 12, p);
@@ -239,89 +165,221 @@ __device__ __forceinline__ V3 mat3_apply(const float* mv, V3 n) {
             fmaf_(mv[8], n.x, fmaf_(mv[9], n.y, mulf(mv[10], n.z))));
 }
 
-constexpr int kRenderThreads = 128;
-
-// surfelmap.glsl geometry shader (:28-90): a camera-facing-independent square of half-side
-// `radius` in the tangent plane of the surface, emitted as the strip p1 p2 p3 p4.
-__global__ void __launch_bounds__(kRenderThreads)
-render_surfel_kernel(const RenderParams P, const float* __restrict__ X, const float* __restrict__ Cf,
-                     const float* __restrict__ img, const float* __restrict__ models,
-                     unsigned long long* __restrict__ fb) {
-  __shared__ float mv[16], mvp[16];
-  block_matrices(P, models, mv, mvp);
-  const int id = blockIdx.x * kRenderThreads + threadIdx.x;
-  if (id >= P.H * P.W) return;
-  const int y = id / P.W, x = id - y * P.W;
-  if (x < 1 || x >= P.W - 1 || y < 1 || y >= P.H - 1) return;
-  const size_t base = (size_t)blockIdx.y * P.H * P.W;
-  if (__ldg(Cf + base + id) < P.conf_threshold) return;
-  const float* Xk = X + base * 3;
-  const V3 p00 = ld3(Xk + (size_t)id * 3), p01 = ld3(Xk + (size_t)(id + P.W) * 3), p10 = ld3(Xk + (size_t)(id + 1) * 3);
-  const V3 right = sub3(p10, p00), down = sub3(p01, p00);
-  const V3 N = normalize3v(cross3(down, right));
-  const V3 tangent = normalize3v(cross3(N, v3(0.f, -1.f, 0.f)));  // "assume y up"
-  const V3 bitangent = cross3(N, tangent);
-  Shade S;
-  S.normal = mat3_apply(mv, N);
-  S.col = ld3(img + (base + id) * 3);
-  S.disk = true;
-  S.spec_power_noimg = 2.f;
-  Vtx v[4];
+// Viewport transform + snapping of the 4 strip vertices, triangle set-up (orientation, cull,
+// 1/area), bounding box of what will be drawn.  Writes the record; returns its pixel count.
+template <int PROGRAM>
+__device__ __forceinline__ int prim_setup(const RenderParams& P, const PrimVertex* v, int* sI, float* sF) {
+  int X[4], Y[4];
+  unsigned okm = 0;  // bit k: strip vertex k is drawable
 #pragma unroll
   for (int k = 0; k < 4; k++) {
-    const float st = (k & 1) ? 1.f : -1.f, sb = (k & 2) ? 1.f : -1.f;  // p1..p4: (-,-) (+,-) (-,+) (+,+)
-    // xyz00 + (+-tangent +- bitangent) * radius, as written (surfelmap.glsl:55-58)
-    const V3 p = v3(addf(p00.x, mulf(addf(mulf(st, tangent.x), mulf(sb, bitangent.x)), P.radius)),
-                    addf(p00.y, mulf(addf(mulf(st, tangent.y), mulf(sb, bitangent.y)), P.radius)),
-                    addf(p00.z, mulf(addf(mulf(st, tangent.z), mulf(sb, bitangent.z)), P.radius)));
-    transform_vertex(mv, mvp, p, v[k]);
-    v[k].tu = st; v[k].tv = sb;
-    v[k].col = S.col;
+    const float rw = divf(1.f, v[k].cw);
+    const float nx = mulf(v[k].cx, rw), ny = mulf(v[k].cy, rw), nz = mulf(v[k].cz, rw);
+    const float wx = mulf(fmaf_(nx, 0.5f, 0.5f), (float)P.fbw), wy = mulf(fmaf_(ny, 0.5f, 0.5f), (float)P.fbh);
+    const bool ok = (v[k].cw > 0.f) && (fabsf(wx) <= 1048576.f) && (fabsf(wy) <= 1048576.f) && (fabsf(nz) <= 3.0e38f);
+    okm |= (ok ? 1u : 0u) << k;
+    X[k] = ok ? __float2int_rn(mulf(wx, 256.f)) : 0;
+    Y[k] = ok ? __float2int_rn(mulf(wy, 256.f)) : 0;
+    sI[(I_X + k) * kRenderThreads] = X[k];
+    sI[(I_Y + k) * kRenderThreads] = Y[k];
+    sF[(F_Z + k) * kRenderThreads] = nz;
+    sF[(F_RW + k) * kRenderThreads] = rw;
+    sF[(F_POS + 3 * k + 0) * kRenderThreads] = v[k].pos.x;
+    sF[(F_POS + 3 * k + 1) * kRenderThreads] = v[k].pos.y;
+    sF[(F_POS + 3 * k + 2) * kRenderThreads] = v[k].pos.z;
   }
-  raster_triangle(P, S, fb, v[0], v[1], v[2]);  // strip: (0,1,2), (2,1,3)
-  raster_triangle(P, S, fb, v[2], v[1], v[3]);
+  int flags = 0, minx = 0x7fffffff, maxx = -0x7fffffff, miny = 0x7fffffff, maxy = -0x7fffffff;
+  {
+#pragma unroll
+    for (int t = 0; t < 2; t++) {  // strip: (0,1,2), (2,1,3)
+      const int a = t ? 2 : 0, b = 1, c = t ? 3 : 2;
+      long long area2 = edge_fn(X[a], Y[a], X[b], Y[b], X[c], Y[c]);
+      bool draw = area2 != 0 && ((okm >> a) & (okm >> b) & (okm >> c) & 1u);
+      if (area2 < 0) {
+        if (P.cull) draw = false;  // back face (CCW is front, GL default)
+        else { flags |= 4 << t; area2 = -area2; }
+      }
+      if (draw) {
+        flags |= 1 << t;
+        minx = min(minx, min(X[a], min(X[b], X[c]))); maxx = max(maxx, max(X[a], max(X[b], X[c])));
+        miny = min(miny, min(Y[a], min(Y[b], Y[c]))); maxy = max(maxy, max(Y[a], max(Y[b], Y[c])));
+      }
+      sF[(F_IA + t) * kRenderThreads] = draw ? divf(1.f, (float)area2) : 0.f;
+    }
+  }
+  int count = 0, x0 = 0, y0 = 0, bw = 0;
+  if (flags & 3) {  // pixel (px, py) has its centre at (256 px + 128, 256 py + 128)
+    x0 = max(0, (minx - 128 + 255) >> 8);
+    y0 = max(0, (miny - 128 + 255) >> 8);
+    const int x1 = min(P.fbw - 1, (maxx - 128) >> 8), y1 = min(P.fbh - 1, (maxy - 128) >> 8);
+    if (x0 <= x1 && y0 <= y1) {
+      bw = x1 - x0 + 1;
+      const long long c = (long long)bw * (y1 - y0 + 1);
+      count = c > (1LL << 24) ? (1 << 24) : (int)c;  // unreachable for fbw*fbh <= 2^24; larger targets clamp
+    }
+  }
+  sI[I_X0 * kRenderThreads] = x0; sI[I_Y0 * kRenderThreads] = y0; sI[I_BW * kRenderThreads] = bw;
+  sI[I_FLAGS * kRenderThreads] = flags;
+  return count;
 }
 
-// trianglemap.glsl geometry shader (:41-93): the pixel quad TL BL TR BR of the pointmap itself.
-__global__ void __launch_bounds__(kRenderThreads)
-render_triangle_kernel(const RenderParams P, const float* __restrict__ X, const float* __restrict__ Cf,
-                       const float* __restrict__ img, const float* __restrict__ models,
-                       unsigned long long* __restrict__ fb) {
-  __shared__ float mv[16], mvp[16];
-  block_matrices(P, models, mv, mvp);
-  const int id = blockIdx.x * kRenderThreads + threadIdx.x;
-  if (id >= P.H * P.W) return;
-  const int y = id / P.W, x = id - y * P.W;
-  if (x < 10 || x >= P.W - 10 || y < 10 || y >= P.H - 10) return;
-  const size_t base = (size_t)blockIdx.y * P.H * P.W;
-  const float* Xk = X + base * 3;
-  const float* Ik = img + base * 3;
-  const int ids[4] = {id, id + 1, id + P.W, id + P.W + 1};  // TL TR BL BR
-  V3 pos[4], col[4];
+// One (primitive, pixel) work item: coverage of both strip triangles, then the fragment.
+template <int PROGRAM>
+__device__ __forceinline__ void fragment_item(const RenderParams& P, const int* sI, const float* sF, int px, int py,
+                                              unsigned long long* __restrict__ fb) {
+  const int flags = sI[I_FLAGS * kRenderThreads];
+  const int cx = 256 * px + 128, cy = 256 * py + 128;
 #pragma unroll
-  for (int k = 0; k < 4; k++) { pos[k] = ld3(Xk + (size_t)ids[k] * 3); col[k] = ld3(Ik + (size_t)ids[k] * 3); }
-  const V3 n1 = normalize3v(cross3(sub3(pos[2], pos[0]), sub3(pos[1], pos[0])));  // normal(TL, BL, TR)
-  const V3 n2 = normalize3v(cross3(sub3(pos[2], pos[1]), sub3(pos[3], pos[1])));  // normal(TR, BL, BR)
-  const V3 ray1 = normalize3v(pos[0]), ray2 = normalize3v(pos[1]);
-  if (fabsf(dot3(n1, ray1)) < P.slant_threshold) return;
-  if (fabsf(dot3(n2, ray2)) < P.slant_threshold) return;
-  if (__ldg(Cf + base + id) < P.conf_threshold) return;  // the shader reads conf at (x, y) for all four
-  Shade S;
-  S.normal = mat3_apply(mv, v3(divf(addf(n1.x, n2.x), 2.f), divf(addf(n1.y, n2.y), 2.f), divf(addf(n1.z, n2.z), 2.f)));
-  S.col = v3(0.f, 0.f, 0.f);
-  S.disk = false;
-  S.spec_power_noimg = 3.f;
-  Vtx v[4];
-  const int order[4] = {0, 2, 1, 3};  // TL, BL, TR, BR ("CCW")
-#pragma unroll
-  for (int k = 0; k < 4; k++) {
-    transform_vertex(mv, mvp, pos[order[k]], v[k]);
-    v[k].cz = subf(v[k].cz, P.depth_bias);
-    v[k].col = col[order[k]];
-    v[k].tu = 0.f; v[k].tv = 0.f;
+  for (int t = 0; t < 2; t++) {
+    if (!((flags >> t) & 1)) continue;
+    const bool flip = (flags >> (2 + t)) & 1;
+    const int ia = t ? 2 : 0, ib = flip ? (t ? 3 : 2) : 1, ic = flip ? 1 : (t ? 3 : 2);
+    const int ax = sI[(I_X + ia) * kRenderThreads], ay = sI[(I_Y + ia) * kRenderThreads];
+    const int bx = sI[(I_X + ib) * kRenderThreads], by = sI[(I_Y + ib) * kRenderThreads];
+    const int ex = sI[(I_X + ic) * kRenderThreads], ey = sI[(I_Y + ic) * kRenderThreads];
+    const long long wa = edge_fn(bx, by, ex, ey, cx, cy);
+    const long long wb = edge_fn(ex, ey, ax, ay, cx, cy);
+    const long long wc = edge_fn(ax, ay, bx, by, cx, cy);
+    if (wa < 0 || wb < 0 || wc < 0) continue;
+    if ((wa == 0 && !owns_edge(ex - bx, ey - by)) || (wb == 0 && !owns_edge(ax - ex, ay - ey)) ||
+        (wc == 0 && !owns_edge(bx - ax, by - ay)))
+      continue;
+    const float ia2 = sF[(F_IA + t) * kRenderThreads];
+    const float la = mulf((float)wa, ia2), lb = mulf((float)wb, ia2), lc = mulf((float)wc, ia2);
+    const float zn = fmaf_(lc, sF[(F_Z + ic) * kRenderThreads],
+                           fmaf_(lb, sF[(F_Z + ib) * kRenderThreads], mulf(la, sF[(F_Z + ia) * kRenderThreads])));
+    const float zw = fmaf_(zn, 0.5f, 0.5f);
+    if (!(zw >= 0.f && zw < 1.f)) continue;
+    unsigned long long* dst = fb + (size_t)py * P.fbw + px;
+    const uint32_t zbits = __float_as_uint(zw);
+    // early depth test: the stored word only ever decreases, so a stale read is conservative
+    if ((uint32_t)(*reinterpret_cast<volatile unsigned long long*>(dst) >> 32) < zbits) continue;
+    // perspective-correct weights lambda_i / w_i, normalised by one reciprocal
+    const float qa = mulf(la, sF[(F_RW + ia) * kRenderThreads]), qb = mulf(lb, sF[(F_RW + ib) * kRenderThreads]);
+    const float qc = mulf(lc, sF[(F_RW + ic) * kRenderThreads]);
+    const float iq = divf(1.f, addf(addf(qa, qb), qc));
+#define M3R_INTERP(fa_, fb_, fc_) mulf(fmaf_(qc, fc_, fmaf_(qb, fb_, mulf(qa, fa_))), iq)
+    if (PROGRAM == 0) {  // surfelmap.glsl:107-111: fragTexCoord of strip vertex k is (+-1, +-1)
+      const float tu = M3R_INTERP((ia & 1) ? 1.f : -1.f, (ib & 1) ? 1.f : -1.f, (ic & 1) ? 1.f : -1.f);
+      const float tv = M3R_INTERP((ia & 2) ? 1.f : -1.f, (ib & 2) ? 1.f : -1.f, (ic & 2) ? 1.f : -1.f);
+      if (fmaf_(tu, tu, mulf(tv, tv)) > 1.0f) continue;  // length(t) > 1  <=>  t.t > 1
+    }
+#define M3R_POS(i_, c_) sF[(F_POS + 3 * (i_) + (c_)) * kRenderThreads]
+    const V3 pos = v3(M3R_INTERP(M3R_POS(ia, 0), M3R_POS(ib, 0), M3R_POS(ic, 0)),
+                      M3R_INTERP(M3R_POS(ia, 1), M3R_POS(ib, 1), M3R_POS(ic, 1)),
+                      M3R_INTERP(M3R_POS(ia, 2), M3R_POS(ib, 2), M3R_POS(ic, 2)));
+#undef M3R_POS
+    V3 col;
+    if (PROGRAM == 0) {
+      col = v3(sF[(F_COL + 0) * kRenderThreads], sF[(F_COL + 1) * kRenderThreads], sF[(F_COL + 2) * kRenderThreads]);
+    } else {
+#define M3R_COL(i_, c_) sF[(F_COL + 3 * (i_) + (c_)) * kRenderThreads]
+      col = v3(M3R_INTERP(M3R_COL(ia, 0), M3R_COL(ib, 0), M3R_COL(ic, 0)),
+               M3R_INTERP(M3R_COL(ia, 1), M3R_COL(ib, 1), M3R_COL(ic, 1)),
+               M3R_INTERP(M3R_COL(ia, 2), M3R_COL(ib, 2), M3R_COL(ic, 2)));
+#undef M3R_COL
+    }
+#undef M3R_INTERP
+    const V3 N = v3(sF[(F_N + 0) * kRenderThreads], sF[(F_N + 1) * kRenderThreads], sF[(F_N + 2) * kRenderThreads]);
+    const uint32_t rgba = shade(P, PROGRAM == 0 ? 2.f : 3.f, N, pos, col);
+    atomicMin(dst, ((unsigned long long)zbits << 32) | rgba);
   }
-  raster_triangle(P, S, fb, v[0], v[1], v[2]);
-  raster_triangle(P, S, fb, v[2], v[1], v[3]);
+}
+
+// PROGRAM 0: surfelmap.glsl geometry shader (:28-90) — a square of half-side `radius` in the
+// tangent plane of the surface, emitted as the strip p1 p2 p3 p4.
+// PROGRAM 1: trianglemap.glsl geometry shader (:41-93) — the pixel quad TL BL TR BR itself.
+// Phase 1: one thread = one geometry-shader invocation -> a primitive record in shared memory.
+// Phase 2: the warp flattens the (primitive, bounding-box pixel) pairs of its 32 records with
+// a prefix sum and walks them 32 at a time, so lanes stay converged whatever the primitives'
+// sizes (a lane-per-primitive loop ran at 12.8 active lanes of 32).
+template <int PROGRAM>
+__global__ void __launch_bounds__(kRenderThreads)
+render_kernel(const RenderParams P, const float* __restrict__ X, const float* __restrict__ Cf,
+              const float* __restrict__ img, const float* __restrict__ models,
+              unsigned long long* __restrict__ fb) {
+  __shared__ float mv[16], mvp[16];
+  __shared__ int sI[kPrimInts][kRenderThreads];
+  __shared__ float sF[PrimWords<PROGRAM>::kFloats][kRenderThreads];
+  __shared__ int sPre[kRenderThreads];
+  block_matrices(P, models, mv, mvp);
+  const int tid = threadIdx.x, lane = tid & 31, wbase = tid & ~31;
+  const int id = blockIdx.x * kRenderThreads + tid;
+  int count = 0;
+  const int border = PROGRAM == 0 ? 1 : 10;
+  const int y = id / P.W, x = id - y * P.W;
+  const size_t base = (size_t)blockIdx.y * P.H * P.W;
+  bool emit = id < P.H * P.W && !(x < border || x >= P.W - border || y < border || y >= P.H - border);
+  if (emit && __ldg(Cf + base + id) < P.conf_threshold) emit = false;  // trianglemap reads conf at (x, y) for all four
+  if (emit) {
+    const float* Xk = X + base * 3;
+    PrimVertex v[4];
+    V3 Nv;
+    if (PROGRAM == 0) {
+      const V3 p00 = ld3(Xk + (size_t)id * 3), p01 = ld3(Xk + (size_t)(id + P.W) * 3), p10 = ld3(Xk + (size_t)(id + 1) * 3);
+      const V3 right = sub3(p10, p00), down = sub3(p01, p00);
+      const V3 N = normalize_rcp(cross3(down, right));
+      const V3 tangent = normalize_rcp(cross3(N, v3(0.f, -1.f, 0.f)));  // "assume y up"
+      const V3 bitangent = cross3(N, tangent);
+      Nv = mat3_apply(mv, N);
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const float st = (k & 1) ? 1.f : -1.f, sb = (k & 2) ? 1.f : -1.f;  // p1..p4: (-,-) (+,-) (-,+) (+,+)
+        // xyz00 + (+-tangent +- bitangent) * radius, as written (surfelmap.glsl:55-58)
+        const V3 p = v3(addf(p00.x, mulf(addf(mulf(st, tangent.x), mulf(sb, bitangent.x)), P.radius)),
+                        addf(p00.y, mulf(addf(mulf(st, tangent.y), mulf(sb, bitangent.y)), P.radius)),
+                        addf(p00.z, mulf(addf(mulf(st, tangent.z), mulf(sb, bitangent.z)), P.radius)));
+        transform_vertex(mv, mvp, p, v[k]);
+      }
+      const V3 col = ld3(img + (base + id) * 3);
+      sF[F_COL + 0][tid] = col.x; sF[F_COL + 1][tid] = col.y; sF[F_COL + 2][tid] = col.z;
+    } else {
+      const float* Ik = img + base * 3;
+      const int ids[4] = {id, id + 1, id + P.W, id + P.W + 1};  // TL TR BL BR
+      V3 pos[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) pos[k] = ld3(Xk + (size_t)ids[k] * 3);
+      const V3 n1 = normalize_rcp(cross3(sub3(pos[2], pos[0]), sub3(pos[1], pos[0])));  // normal(TL, BL, TR)
+      const V3 n2 = normalize_rcp(cross3(sub3(pos[2], pos[1]), sub3(pos[3], pos[1])));  // normal(TR, BL, BR)
+      const V3 ray1 = normalize_rcp(pos[0]), ray2 = normalize_rcp(pos[1]);
+      if (fabsf(dot3(n1, ray1)) < P.slant_threshold || fabsf(dot3(n2, ray2)) < P.slant_threshold) emit = false;
+      Nv = mat3_apply(mv, v3(mulf(addf(n1.x, n2.x), 0.5f), mulf(addf(n1.y, n2.y), 0.5f), mulf(addf(n1.z, n2.z), 0.5f)));
+      const int order[4] = {0, 2, 1, 3};  // TL, BL, TR, BR ("CCW")
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        transform_vertex(mv, mvp, pos[order[k]], v[k]);
+        v[k].cz = subf(v[k].cz, P.depth_bias);
+        const V3 col = ld3(Ik + (size_t)ids[order[k]] * 3);
+        sF[F_COL + 3 * k + 0][tid] = col.x; sF[F_COL + 3 * k + 1][tid] = col.y; sF[F_COL + 3 * k + 2][tid] = col.z;
+      }
+    }
+    if (emit) {
+      const V3 Nn = normalize_rcp(Nv);
+      sF[F_N + 0][tid] = Nn.x; sF[F_N + 1][tid] = Nn.y; sF[F_N + 2][tid] = Nn.z;
+      count = prim_setup<PROGRAM>(P, v, &sI[0][tid], &sF[0][tid]);
+    }
+  }
+  // exclusive prefix of the pixel counts over the warp
+  int incl = count;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int nb = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += nb;
+  }
+  const int total = __shfl_sync(0xffffffffu, incl, 31);
+  sPre[tid] = incl - count;
+  __syncwarp();
+  for (int t = lane; t < total; t += 32) {
+    int lo = 0;  // owner = last record whose exclusive prefix is <= t
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1)
+      if (sPre[wbase + lo + s] <= t) lo += s;
+    const int col = wbase + lo;
+    const int local = t - sPre[col];
+    const int bw = sI[I_BW][col];
+    const int ry = local / bw, rx = local - ry * bw;
+    fragment_item<PROGRAM>(P, &sI[0][col], &sF[0][col], sI[I_X0][col] + rx, sI[I_Y0][col] + ry, fb);
+  }
 }
 
 __global__ void __launch_bounds__(256)
@@ -347,7 +405,8 @@ render_resolve_kernel(const unsigned long long* __restrict__ fb, int w, int h, u
 static int fill_params(RenderParams& P, const m3r_render_view* view, int H, int W,
                        const m3r_render_opts* o) {
   if (!view || !o || H <= 0 || W <= 0 || view->width <= 0 || view->height <= 0) return M3R_EINVAL;
-  if ((long long)view->width * view->height > (1LL << 30) || (long long)H * W > (1LL << 30)) return M3R_EINVAL;
+  // <= 2^24 target pixels: 32 bounding boxes then sum to < 2^31 in the warp's prefix sum
+  if ((long long)view->width * view->height > (1LL << 24) || (long long)H * W > (1LL << 30)) return M3R_EINVAL;
   for (int i = 0; i < 16; i++) { P.camera[i] = view->camera[i]; P.proj[i] = view->proj[i]; }
   P.H = H; P.W = W; P.fbw = view->width; P.fbh = view->height;
   P.conf_threshold = o->conf_threshold; P.radius = o->radius;
@@ -396,9 +455,9 @@ static int render_launch(int program, const float* X, const float* C, const floa
   dim3 grid((H * W + kRenderThreads - 1) / kRenderThreads, K);
   auto* f = reinterpret_cast<unsigned long long*>(fb);
   if (program == 0)
-    render_surfel_kernel<<<grid, kRenderThreads, 0, as_stream(stream)>>>(P, X, C, img, models, f);
+    render_kernel<0><<<grid, kRenderThreads, 0, as_stream(stream)>>>(P, X, C, img, models, f);
   else
-    render_triangle_kernel<<<grid, kRenderThreads, 0, as_stream(stream)>>>(P, X, C, img, models, f);
+    render_kernel<1><<<grid, kRenderThreads, 0, as_stream(stream)>>>(P, X, C, img, models, f);
   return after_launch();
 }
 

@@ -19,7 +19,8 @@
  *   fragments outside 0 <= depth < 1 dropped, primitives with a vertex at w <= 0 / non-finite /
  *   beyond 2^20 px dropped (no geometric clipping); depth test LESS, equal depth -> smaller colour
  *   word; RGBA8 = floor(clamp(c,0,1)*255 + 0.5); pow(x, n) for integral 1 <= n <= 64 by
- *   square-and-multiply.
+ *   square-and-multiply; normalize(v) = v * (1/sqrt(v.v)); perspective divide, barycentrics and
+ *   attribute interpolation through one reciprocal each; length(t) > 1 as t.t > 1.
  * Compiled with -ffp-contract=off: every * and + below is one IEEE rounding; fmaf is explicit. */
 #include <math.h>
 #include <stdint.h>
@@ -44,9 +45,10 @@ static float dot(v3 a, v3 b) { return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z));
 static v3 cross(v3 a, v3 b) {
   return V(fmaf(a.y, b.z, -(a.z * b.y)), fmaf(a.z, b.x, -(a.x * b.z)), fmaf(a.x, b.y, -(a.y * b.x)));
 }
+/* normalize(v) := v * (1 / sqrt(v.v)) */
 static v3 normalize(v3 a) {
-  const float len = sqrtf(dot(a, a));
-  return V(a.x / len, a.y / len, a.z / len);
+  const float inv = 1.f / sqrtf(dot(a, a));
+  return V(a.x * inv, a.y * inv, a.z * inv);
 }
 static float row4(const float* m, v3 p) { return fmaf(m[0], p.x, fmaf(m[1], p.y, fmaf(m[2], p.z, m[3]))); }
 static v3 mat3v(const float* mv, v3 n) {
@@ -106,7 +108,7 @@ static uint32_t fragment(const prim* P, v3 position, v3 color) {
   const v3 frag_color = o->use_img ? color : V(o->base_color[0], o->base_color[1], o->base_color[2]);
   const float spec_power = o->use_img ? o->spec : P->spec_noimg;
   const v3 L = normalize(sub(V(o->lightpos[0], o->lightpos[1], o->lightpos[2]), position));
-  const v3 N = normalize(P->normal);
+  const v3 N = P->normal; /* normalised once per primitive: it is constant over it */
   const float lambertian = fmaxf(dot(N, L), 0.f);
   float specular = 0.f;
   if (lambertian > 0.f) {
@@ -120,16 +122,15 @@ static uint32_t fragment(const prim* P, v3 position, v3 color) {
   return unorm8(out.x) | (unorm8(out.y) << 8) | (unorm8(out.z) << 16) | 0xFF000000u;
 }
 
-typedef struct { long long x, y; float zndc, w; int ok; } snapped;
+typedef struct { long long x, y; float zndc, rw; int ok; } snapped;
 
 static snapped snap(const orc_render_view* view, const vtx* v) {
   snapped s;
-  s.w = v->clip[3];
-  s.ok = v->clip[3] > 0.f;
-  const float nx = v->clip[0] / v->clip[3], ny = v->clip[1] / v->clip[3];
-  s.zndc = v->clip[2] / v->clip[3];
+  s.rw = 1.f / v->clip[3];
+  const float nx = v->clip[0] * s.rw, ny = v->clip[1] * s.rw;
+  s.zndc = v->clip[2] * s.rw;
   const float wx = fmaf(nx, 0.5f, 0.5f) * (float)view->width, wy = fmaf(ny, 0.5f, 0.5f) * (float)view->height;
-  s.ok = s.ok && fabsf(wx) <= 1048576.f && fabsf(wy) <= 1048576.f && s.zndc == s.zndc && fabsf(s.zndc) <= 3.0e38f;
+  s.ok = v->clip[3] > 0.f && fabsf(wx) <= 1048576.f && fabsf(wy) <= 1048576.f && fabsf(s.zndc) <= 3.0e38f;
   s.x = s.ok ? (long long)lrintf(wx * 256.f) : 0;
   s.y = s.ok ? (long long)lrintf(wy * 256.f) : 0;
   return s;
@@ -161,7 +162,7 @@ static void raster(const prim* P, vtx a, vtx b, vtx c) {
   const long long y0 = mx(0, fdiv256(miny - 128 + 255)), y1 = mn(view->height - 1, fdiv256(maxy - 128));
   const int own_a = owns(sc.x - sb.x, sc.y - sb.y), own_b = owns(sa.x - sc.x, sa.y - sc.y),
             own_c = owns(sb.x - sa.x, sb.y - sa.y);
-  const float fa2 = (float)area2;
+  const float inv_area = 1.f / (float)area2;
   for (long long py = y0; py <= y1; py++)
     for (long long px = x0; px <= x1; px++) {
       const long long cx = 256 * px + 128, cy = 256 * py + 128;
@@ -169,16 +170,16 @@ static void raster(const prim* P, vtx a, vtx b, vtx c) {
                       wc = edgef(sa.x, sa.y, sb.x, sb.y, cx, cy);
       if (wa < 0 || wb < 0 || wc < 0) continue;
       if ((wa == 0 && !own_a) || (wb == 0 && !own_b) || (wc == 0 && !own_c)) continue;
-      const float la = (float)wa / fa2, lb = (float)wb / fa2, lc = (float)wc / fa2;
+      const float la = (float)wa * inv_area, lb = (float)wb * inv_area, lc = (float)wc * inv_area;
       const float zn = fmaf(lc, sc.zndc, fmaf(lb, sb.zndc, la * sa.zndc));
       const float zw = fmaf(zn, 0.5f, 0.5f);
       if (!(zw >= 0.f && zw < 1.f)) continue;
-      const float qa = la / sa.w, qb = lb / sb.w, qc = lc / sc.w;
-      const float qs = (qa + qb) + qc;
-#define INTERP(A, B, C) (fmaf(qc, C, fmaf(qb, B, qa * (A))) / qs)
+      const float qa = la * sa.rw, qb = lb * sb.rw, qc = lc * sc.rw;
+      const float iq = 1.f / ((qa + qb) + qc);
+#define INTERP(A, B, C) (fmaf(qc, C, fmaf(qb, B, qa * (A))) * iq)
       if (P->disk) { /* surfelmap.glsl:107-111 */
         const float tu = INTERP(a.tu, b.tu, c.tu), tv = INTERP(a.tv, b.tv, c.tv);
-        if (sqrtf(fmaf(tu, tu, tv * tv)) > 1.0f) continue;
+        if (fmaf(tu, tu, tv * tv) > 1.0f) continue; /* length(t) > 1 <=> t.t > 1 */
       }
       const v3 pos = V(INTERP(a.pos.x, b.pos.x, c.pos.x), INTERP(a.pos.y, b.pos.y, c.pos.y),
                        INTERP(a.pos.z, b.pos.z, c.pos.z));
@@ -229,7 +230,7 @@ void orc_render(int program, const float* X, const float* Cf, const float* img, 
         const v3 N = normalize(cross(down, right));
         const v3 tangent = normalize(cross(N, V(0.f, -1.f, 0.f)));
         const v3 bitangent = cross(N, tangent);
-        P.normal = mat3v(mv, N);
+        P.normal = normalize(mat3v(mv, N));
         P.col = ld(Ik + 3 * (size_t)id);
         P.disk = 1; P.spec_noimg = 2.f;
         for (int k = 0; k < 4; k++) { /* p1..p4, :55-58, texcoords :64,71,78,85 */
@@ -251,7 +252,7 @@ void orc_render(int program, const float* X, const float* Cf, const float* img, 
         if (fabsf(dot(n1, ray1)) < o->slant_threshold) continue;
         if (fabsf(dot(n2, ray2)) < o->slant_threshold) continue;
         if (Ck[id] < o->conf_threshold) continue; /* conf fetched at (x,y) for all four, :58 */
-        P.normal = mat3v(mv, V((n1.x + n2.x) / 2.f, (n1.y + n2.y) / 2.f, (n1.z + n2.z) / 2.f));
+        P.normal = normalize(mat3v(mv, V((n1.x + n2.x) / 2.f, (n1.y + n2.y) / 2.f, (n1.z + n2.z) / 2.f)));
         P.col = V(0.f, 0.f, 0.f);
         P.disk = 0; P.spec_noimg = 3.f;
         const int order[4] = {0, 2, 1, 3}; /* TL, BL, TR, BR, :81 */
