@@ -23,7 +23,7 @@
 //     attribute interpolation with one reciprocal each, length(t) > 1 as t.t > 1 — so that every
 //     operation is an IEEE single-rounding one and divisions are few: the CPU restatement
 //     (oracle/m3r_render_oracle.c) then reproduces the image bit for bit;
-//   * targets are limited to 2^24 pixels (4096 x 4096).
+//   * targets are limited to 2^24 pixels and 8192 per side.
 // Every float operation is an explicit round-to-nearest intrinsic (no FMA contraction except the
 // fmaf written here), mirrored one to one by the oracle.
 #include "m3r_common.cuh"
@@ -223,67 +223,87 @@ __device__ __forceinline__ int prim_setup(const RenderParams& P, const PrimVerte
   return count;
 }
 
-// One (primitive, pixel) work item: coverage of both strip triangles, then the fragment.
+// A fragment that survived coverage, depth range, the early depth test and (surfel) the disk test,
+// queued for shading: which record / triangle / pixel, its depth bits and perspective weights.
+struct FragEntry { uint32_t where; uint32_t zbits; float qa, qb, qc, iq; };
+constexpr int kFragQueue = 64;  // per warp: at most 31 waiting + 32 pushed
+
+__device__ __forceinline__ void tri_indices(int flags, int t, int& ia, int& ib, int& ic) {
+  const bool flip = (flags >> (2 + t)) & 1;
+  ia = t ? 2 : 0; ib = flip ? (t ? 3 : 2) : 1; ic = flip ? 1 : (t ? 3 : 2);
+}
+
+// Coverage of strip triangle t of record (sI, sF) at pixel (px, py); fills `e` when a fragment results.
 template <int PROGRAM>
-__device__ __forceinline__ void fragment_item(const RenderParams& P, const int* sI, const float* sF, int px, int py,
-                                              unsigned long long* __restrict__ fb) {
+__device__ __forceinline__ bool coverage_item(const RenderParams& P, const int* sI, const float* sF, int t, int px,
+                                              int py, const unsigned long long* __restrict__ fb, FragEntry& e) {
   const int flags = sI[I_FLAGS * kRenderThreads];
+  if (!((flags >> t) & 1)) return false;
+  int ia, ib, ic;
+  tri_indices(flags, t, ia, ib, ic);
   const int cx = 256 * px + 128, cy = 256 * py + 128;
-#pragma unroll
-  for (int t = 0; t < 2; t++) {
-    if (!((flags >> t) & 1)) continue;
-    const bool flip = (flags >> (2 + t)) & 1;
-    const int ia = t ? 2 : 0, ib = flip ? (t ? 3 : 2) : 1, ic = flip ? 1 : (t ? 3 : 2);
-    const int ax = sI[(I_X + ia) * kRenderThreads], ay = sI[(I_Y + ia) * kRenderThreads];
-    const int bx = sI[(I_X + ib) * kRenderThreads], by = sI[(I_Y + ib) * kRenderThreads];
-    const int ex = sI[(I_X + ic) * kRenderThreads], ey = sI[(I_Y + ic) * kRenderThreads];
-    const long long wa = edge_fn(bx, by, ex, ey, cx, cy);
-    const long long wb = edge_fn(ex, ey, ax, ay, cx, cy);
-    const long long wc = edge_fn(ax, ay, bx, by, cx, cy);
-    if (wa < 0 || wb < 0 || wc < 0) continue;
-    if ((wa == 0 && !owns_edge(ex - bx, ey - by)) || (wb == 0 && !owns_edge(ax - ex, ay - ey)) ||
-        (wc == 0 && !owns_edge(bx - ax, by - ay)))
-      continue;
-    const float ia2 = sF[(F_IA + t) * kRenderThreads];
-    const float la = mulf((float)wa, ia2), lb = mulf((float)wb, ia2), lc = mulf((float)wc, ia2);
-    const float zn = fmaf_(lc, sF[(F_Z + ic) * kRenderThreads],
-                           fmaf_(lb, sF[(F_Z + ib) * kRenderThreads], mulf(la, sF[(F_Z + ia) * kRenderThreads])));
-    const float zw = fmaf_(zn, 0.5f, 0.5f);
-    if (!(zw >= 0.f && zw < 1.f)) continue;
-    unsigned long long* dst = fb + (size_t)py * P.fbw + px;
-    const uint32_t zbits = __float_as_uint(zw);
-    // early depth test: the stored word only ever decreases, so a stale read is conservative
-    if ((uint32_t)(*reinterpret_cast<volatile unsigned long long*>(dst) >> 32) < zbits) continue;
-    // perspective-correct weights lambda_i / w_i, normalised by one reciprocal
-    const float qa = mulf(la, sF[(F_RW + ia) * kRenderThreads]), qb = mulf(lb, sF[(F_RW + ib) * kRenderThreads]);
-    const float qc = mulf(lc, sF[(F_RW + ic) * kRenderThreads]);
-    const float iq = divf(1.f, addf(addf(qa, qb), qc));
-#define M3R_INTERP(fa_, fb_, fc_) mulf(fmaf_(qc, fc_, fmaf_(qb, fb_, mulf(qa, fa_))), iq)
-    if (PROGRAM == 0) {  // surfelmap.glsl:107-111: fragTexCoord of strip vertex k is (+-1, +-1)
-      const float tu = M3R_INTERP((ia & 1) ? 1.f : -1.f, (ib & 1) ? 1.f : -1.f, (ic & 1) ? 1.f : -1.f);
-      const float tv = M3R_INTERP((ia & 2) ? 1.f : -1.f, (ib & 2) ? 1.f : -1.f, (ic & 2) ? 1.f : -1.f);
-      if (fmaf_(tu, tu, mulf(tv, tv)) > 1.0f) continue;  // length(t) > 1  <=>  t.t > 1
-    }
-#define M3R_POS(i_, c_) sF[(F_POS + 3 * (i_) + (c_)) * kRenderThreads]
-    const V3 pos = v3(M3R_INTERP(M3R_POS(ia, 0), M3R_POS(ib, 0), M3R_POS(ic, 0)),
-                      M3R_INTERP(M3R_POS(ia, 1), M3R_POS(ib, 1), M3R_POS(ic, 1)),
-                      M3R_INTERP(M3R_POS(ia, 2), M3R_POS(ib, 2), M3R_POS(ic, 2)));
-#undef M3R_POS
-    V3 col;
-    if (PROGRAM == 0) {
-      col = v3(sF[(F_COL + 0) * kRenderThreads], sF[(F_COL + 1) * kRenderThreads], sF[(F_COL + 2) * kRenderThreads]);
-    } else {
-#define M3R_COL(i_, c_) sF[(F_COL + 3 * (i_) + (c_)) * kRenderThreads]
-      col = v3(M3R_INTERP(M3R_COL(ia, 0), M3R_COL(ib, 0), M3R_COL(ic, 0)),
-               M3R_INTERP(M3R_COL(ia, 1), M3R_COL(ib, 1), M3R_COL(ic, 1)),
-               M3R_INTERP(M3R_COL(ia, 2), M3R_COL(ib, 2), M3R_COL(ic, 2)));
-#undef M3R_COL
-    }
-#undef M3R_INTERP
-    const V3 N = v3(sF[(F_N + 0) * kRenderThreads], sF[(F_N + 1) * kRenderThreads], sF[(F_N + 2) * kRenderThreads]);
-    const uint32_t rgba = shade(P, PROGRAM == 0 ? 2.f : 3.f, N, pos, col);
-    atomicMin(dst, ((unsigned long long)zbits << 32) | rgba);
+  const int ax = sI[(I_X + ia) * kRenderThreads], ay = sI[(I_Y + ia) * kRenderThreads];
+  const int bx = sI[(I_X + ib) * kRenderThreads], by = sI[(I_Y + ib) * kRenderThreads];
+  const int ex = sI[(I_X + ic) * kRenderThreads], ey = sI[(I_Y + ic) * kRenderThreads];
+  const long long wa = edge_fn(bx, by, ex, ey, cx, cy);
+  const long long wb = edge_fn(ex, ey, ax, ay, cx, cy);
+  const long long wc = edge_fn(ax, ay, bx, by, cx, cy);
+  if (wa < 0 || wb < 0 || wc < 0) return false;
+  if ((wa == 0 && !owns_edge(ex - bx, ey - by)) || (wb == 0 && !owns_edge(ax - ex, ay - ey)) ||
+      (wc == 0 && !owns_edge(bx - ax, by - ay)))
+    return false;
+  const float ia2 = sF[(F_IA + t) * kRenderThreads];
+  const float la = mulf((float)wa, ia2), lb = mulf((float)wb, ia2), lc = mulf((float)wc, ia2);
+  const float zn = fmaf_(lc, sF[(F_Z + ic) * kRenderThreads],
+                         fmaf_(lb, sF[(F_Z + ib) * kRenderThreads], mulf(la, sF[(F_Z + ia) * kRenderThreads])));
+  const float zw = fmaf_(zn, 0.5f, 0.5f);
+  if (!(zw >= 0.f && zw < 1.f)) return false;
+  e.zbits = __float_as_uint(zw);
+  // early depth test: the stored word only ever decreases, so a stale read is conservative
+  const unsigned long long cur = *reinterpret_cast<const volatile unsigned long long*>(fb + (size_t)py * P.fbw + px);
+  if ((uint32_t)(cur >> 32) < e.zbits) return false;
+  // perspective-correct weights lambda_i / w_i, normalised by one reciprocal
+  e.qa = mulf(la, sF[(F_RW + ia) * kRenderThreads]);
+  e.qb = mulf(lb, sF[(F_RW + ib) * kRenderThreads]);
+  e.qc = mulf(lc, sF[(F_RW + ic) * kRenderThreads]);
+  e.iq = divf(1.f, addf(addf(e.qa, e.qb), e.qc));
+  if (PROGRAM == 0) {  // surfelmap.glsl:107-111: fragTexCoord of strip vertex k is (+-1, +-1)
+    const float tu = mulf(fmaf_(e.qc, (ic & 1) ? 1.f : -1.f, fmaf_(e.qb, (ib & 1) ? 1.f : -1.f, mulf(e.qa, (ia & 1) ? 1.f : -1.f))), e.iq);
+    const float tv = mulf(fmaf_(e.qc, (ic & 2) ? 1.f : -1.f, fmaf_(e.qb, (ib & 2) ? 1.f : -1.f, mulf(e.qa, (ia & 2) ? 1.f : -1.f))), e.iq);
+    if (fmaf_(tu, tu, mulf(tv, tv)) > 1.0f) return false;  // length(t) > 1  <=>  t.t > 1
   }
+  return true;
+}
+
+// Fragment shader + commit for one queued fragment of record column `col` (lanes fully converged).
+template <int PROGRAM>
+__device__ __forceinline__ void shade_item(const RenderParams& P, const int* sIw, const float* sFw,
+                                           const FragEntry& e, unsigned long long* __restrict__ fb) {
+  const int col = e.where & 31, t = (e.where >> 5) & 1, px = (e.where >> 6) & 0x1FFF, py = e.where >> 19;
+  const int* sI = sIw + col;
+  const float* sF = sFw + col;
+  int ia, ib, ic;
+  tri_indices(sI[I_FLAGS * kRenderThreads], t, ia, ib, ic);
+#define M3R_INTERP(fa_, fb_, fc_) mulf(fmaf_(e.qc, fc_, fmaf_(e.qb, fb_, mulf(e.qa, fa_))), e.iq)
+#define M3R_POS(i_, c_) sF[(F_POS + 3 * (i_) + (c_)) * kRenderThreads]
+  const V3 pos = v3(M3R_INTERP(M3R_POS(ia, 0), M3R_POS(ib, 0), M3R_POS(ic, 0)),
+                    M3R_INTERP(M3R_POS(ia, 1), M3R_POS(ib, 1), M3R_POS(ic, 1)),
+                    M3R_INTERP(M3R_POS(ia, 2), M3R_POS(ib, 2), M3R_POS(ic, 2)));
+#undef M3R_POS
+  V3 colr;
+  if (PROGRAM == 0) {
+    colr = v3(sF[(F_COL + 0) * kRenderThreads], sF[(F_COL + 1) * kRenderThreads], sF[(F_COL + 2) * kRenderThreads]);
+  } else {
+#define M3R_COL(i_, c_) sF[(F_COL + 3 * (i_) + (c_)) * kRenderThreads]
+    colr = v3(M3R_INTERP(M3R_COL(ia, 0), M3R_COL(ib, 0), M3R_COL(ic, 0)),
+              M3R_INTERP(M3R_COL(ia, 1), M3R_COL(ib, 1), M3R_COL(ic, 1)),
+              M3R_INTERP(M3R_COL(ia, 2), M3R_COL(ib, 2), M3R_COL(ic, 2)));
+#undef M3R_COL
+  }
+#undef M3R_INTERP
+  const V3 N = v3(sF[(F_N + 0) * kRenderThreads], sF[(F_N + 1) * kRenderThreads], sF[(F_N + 2) * kRenderThreads]);
+  const uint32_t rgba = shade(P, PROGRAM == 0 ? 2.f : 3.f, N, pos, colr);
+  atomicMin(fb + (size_t)py * P.fbw + px, ((unsigned long long)e.zbits << 32) | rgba);
 }
 
 // PROGRAM 0: surfelmap.glsl geometry shader (:28-90) — a square of half-side `radius` in the
@@ -302,6 +322,7 @@ render_kernel(const RenderParams P, const float* __restrict__ X, const float* __
   __shared__ int sI[kPrimInts][kRenderThreads];
   __shared__ float sF[PrimWords<PROGRAM>::kFloats][kRenderThreads];
   __shared__ int sPre[kRenderThreads];
+  __shared__ FragEntry sQ[kRenderThreads / 32][kFragQueue];
   block_matrices(P, models, mv, mvp);
   const int tid = threadIdx.x, lane = tid & 31, wbase = tid & ~31;
   const int id = blockIdx.x * kRenderThreads + tid;
@@ -369,17 +390,48 @@ render_kernel(const RenderParams P, const float* __restrict__ X, const float* __
   const int total = __shfl_sync(0xffffffffu, incl, 31);
   sPre[tid] = incl - count;
   __syncwarp();
-  for (int t = lane; t < total; t += 32) {
-    int lo = 0;  // owner = last record whose exclusive prefix is <= t
+  // Phase 2a: coverage for 32 (record, pixel) pairs at a time; survivors are queued (ballot
+  // compaction) and — Phase 2b — shaded 32 at a time, so the fragment shader also runs converged
+  // (a bounding box is ~40 % covered by its disk / triangle).
+  FragEntry* q = sQ[tid >> 5];
+  int qhead = 0, qcount = 0;  // warp-uniform
+  const int* sIw = &sI[0][wbase];
+  const float* sFw = &sF[0][wbase];
+  auto drain = [&](int n) {  // shade the n (<= 32) oldest entries
+    if (lane < n) shade_item<PROGRAM>(P, sIw, sFw, q[(qhead + lane) & (kFragQueue - 1)], fb);
+    qhead = (qhead + n) & (kFragQueue - 1);
+    qcount -= n;
+  };
+  for (int tb = 0; tb < total; tb += 32) {
+    const int t = tb + lane;
+    int colw = 0, px = 0, py = 0;
+    const bool have = t < total;
+    if (have) {
+      int lo = 0;  // owner = last record whose exclusive prefix is <= t
 #pragma unroll
-    for (int s = 16; s > 0; s >>= 1)
-      if (sPre[wbase + lo + s] <= t) lo += s;
-    const int col = wbase + lo;
-    const int local = t - sPre[col];
-    const int bw = sI[I_BW][col];
-    const int ry = local / bw, rx = local - ry * bw;
-    fragment_item<PROGRAM>(P, &sI[0][col], &sF[0][col], sI[I_X0][col] + rx, sI[I_Y0][col] + ry, fb);
+      for (int s = 16; s > 0; s >>= 1)
+        if (sPre[wbase + lo + s] <= t) lo += s;
+      colw = lo;
+      const int local = t - sPre[wbase + lo];
+      const int bw = sI[I_BW][wbase + lo];
+      const int ry = local / bw, rx = local - ry * bw;
+      px = sI[I_X0][wbase + lo] + rx; py = sI[I_Y0][wbase + lo] + ry;
+    }
+#pragma unroll
+    for (int tri = 0; tri < 2; tri++) {
+      FragEntry e;
+      const bool hit = have && coverage_item<PROGRAM>(P, sIw + colw, sFw + colw, tri, px, py, fb, e);
+      const unsigned m = __ballot_sync(0xffffffffu, hit);
+      if (hit) {
+        e.where = (uint32_t)colw | ((uint32_t)tri << 5) | ((uint32_t)px << 6) | ((uint32_t)py << 19);
+        q[(qhead + qcount + __popc(m & ((1u << lane) - 1u))) & (kFragQueue - 1)] = e;
+      }
+      qcount += __popc(m);
+      __syncwarp();
+      if (qcount >= 32) { drain(32); __syncwarp(); }
+    }
   }
+  if (qcount > 0) drain(qcount);
 }
 
 __global__ void __launch_bounds__(256)
@@ -407,6 +459,7 @@ static int fill_params(RenderParams& P, const m3r_render_view* view, int H, int 
   if (!view || !o || H <= 0 || W <= 0 || view->width <= 0 || view->height <= 0) return M3R_EINVAL;
   // <= 2^24 target pixels: 32 bounding boxes then sum to < 2^31 in the warp's prefix sum
   if ((long long)view->width * view->height > (1LL << 24) || (long long)H * W > (1LL << 30)) return M3R_EINVAL;
+  if (view->width > 8192 || view->height > 8192) return M3R_EINVAL;  // 13-bit pixel fields of the fragment queue
   for (int i = 0; i < 16; i++) { P.camera[i] = view->camera[i]; P.proj[i] = view->proj[i]; }
   P.H = H; P.W = W; P.fbw = view->width; P.fbh = view->height;
   P.conf_threshold = o->conf_threshold; P.radius = o->radius;
