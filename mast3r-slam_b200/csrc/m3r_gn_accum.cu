@@ -126,6 +126,13 @@ struct GnDev {  // kernel-side copy of m3r_gn_params with the sigmas pre-inverte
 __device__ __forceinline__ float fast_rcp(float x) {
   float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r;
 }
+// rsqrtf() without its denormal pre/post-scaling (FSETP + 2 predicated FMUL around every
+// MUFU.RSQ: 24 rsqrt per 4 points were 11 % of the loop).  Same bits for normal inputs; a
+// denormal argument (a squared residual below 1.2e-38) flushes to 0 -> +inf -> huber weight 1,
+// which is what the scaled form yields as well.
+__device__ __forceinline__ float fast_rsqrt(float x) {
+  float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r;
+}
 
 // h: upper^T packed 7x7 (index a*(a+1)/2 + c, c <= a); skips Jacobian entries whose bit is
 // clear in MASK (structural zeros of the residual row) at compile time.
@@ -150,7 +157,7 @@ __device__ __forceinline__ void acc_row(float* h, float* g, float w, float e, co
 __device__ __forceinline__ float robust_weight(float wc, float err) {
   const float s2 = wc * err * err;
   // huber = 1 if s2 < k^2 else k / sqrt(s2)  ==  min(1, k * rsqrt(s2))   (rsqrt(0) = +inf)
-  return wc * fminf(1.0f, 1.345f * rsqrtf(s2));
+  return wc * fminf(1.0f, 1.345f * fast_rsqrt(s2));
 }
 
 template <int MODE>
@@ -166,9 +173,9 @@ __device__ __forceinline__ void point_terms(const GnDev& prm, const float* R, co
   const float q = valid ? qm : 0.f;  // weight numerator; 0 switches the point off
   if (MODE == M3R_GN_RAYS) {  // gn_kernels.cu:924-1089
     const float n2i = xi.x * xi.x + xi.y * xi.y + xi.z * xi.z;
-    const float ni_inv = rsqrtf(n2i);
+    const float ni_inv = fast_rsqrt(n2i);
     const float n2j = Px * Px + Py * Py + Pz * Pz;
-    const float nj_inv = rsqrtf(n2j);
+    const float nj_inv = fast_rsqrt(n2j);
     const float nj = n2j * nj_inv;
     const float rx = Px * nj_inv, ry = Py * nj_inv, rz = Pz * nj_inv;
     const float e0 = rx - xi.x * ni_inv, e1 = ry - xi.y * ni_inv, e2 = rz - xi.z * ni_inv;
@@ -389,21 +396,34 @@ gn_accum_stream_kernel(const GnDev prm, const float* __restrict__ Twc, const flo
   for (int k = 0; k < 7; k++) g[k] = 0.f;
   __syncthreads();  // barriers initialised
 
-  // slot of this thread's u-th point inside a stage, -1 when past the end of the split
-  auto slot_of = [&](int st, int u) {
+  // slot of this thread's u-th point inside a stage, -1 when past the end of the split.  Every
+  // stage but the last of the image is full (chunks are multiples of the stage size), and a
+  // full stage needs none of the range tests: `full` is CTA-uniform.
+  auto slot_of = [&](int st, int u, bool full) {
     const int sl = u * kAccThreads + tid;
-    return (p_begin + st * kStagePts + sl < p_end) ? sl : -1;
+    return (full || p_begin + st * kStagePts + sl < p_end) ? sl : -1;
   };
+  auto stage_full = [&](int st) { return p_begin + (st + 1) * kStagePts <= p_end; };
   float4 xi_nxt[kAccUnroll];
   int ind_nxt[kAccUnroll];  // gathered pixel (0 for invalid matches, gn_kernels.cu:913-914)
   auto gather = [&](int st) {
     const unsigned char* buf = stage_mem + (st % kStages) * kStageBytes;
+    if (stage_full(st)) {
 #pragma unroll
-    for (int u = 0; u < kAccUnroll; u++) {
-      const int sl = slot_of(st, u);
-      const bool vm = sl >= 0 && buf[kOffVm + (sl < 0 ? 0 : sl)] != 0;
-      ind_nxt[u] = vm ? (int)reinterpret_cast<const long long*>(buf + kOffIdx)[sl] : 0;
-      xi_nxt[u] = __ldg(xi_base + ind_nxt[u]);
+      for (int u = 0; u < kAccUnroll; u++) {
+        const int sl = u * kAccThreads + tid;
+        const bool vm = buf[kOffVm + sl] != 0;
+        ind_nxt[u] = vm ? (int)reinterpret_cast<const long long*>(buf + kOffIdx)[sl] : 0;
+        xi_nxt[u] = __ldg(xi_base + ind_nxt[u]);
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < kAccUnroll; u++) {
+        const int sl = slot_of(st, u, false);
+        const bool vm = sl >= 0 && buf[kOffVm + (sl < 0 ? 0 : sl)] != 0;
+        ind_nxt[u] = vm ? (int)reinterpret_cast<const long long*>(buf + kOffIdx)[sl] : 0;
+        xi_nxt[u] = __ldg(xi_base + ind_nxt[u]);
+      }
     }
   };
   mbar_wait(&full[0], 0);
@@ -418,14 +438,24 @@ gn_accum_stream_kernel(const GnDev prm, const float* __restrict__ Twc, const flo
       gather(it + 1);
     }
     const unsigned char* buf = stage_mem + (it % kStages) * kStageBytes;
+    if (stage_full(it)) {
 #pragma unroll
-    for (int u = 0; u < kAccUnroll; u++) {
-      const int sl = slot_of(it, u);
-      const int s0 = sl < 0 ? 0 : sl;  // past-the-end lanes re-read slot 0 with weight 0
-      const bool vm = sl >= 0 && buf[kOffVm + s0] != 0;
-      const float qv = vm ? reinterpret_cast<const float*>(buf + kOffQ)[s0] : -3.0e38f;
-      const float4 xj = reinterpret_cast<const float4*>(buf)[s0];
-      point_terms<MODE>(prm, R, t, xi[u], xj, (long long)ind[u], qv, h, g);
+      for (int u = 0; u < kAccUnroll; u++) {
+        const int s0 = u * kAccThreads + tid;
+        const float qv = buf[kOffVm + s0] != 0 ? reinterpret_cast<const float*>(buf + kOffQ)[s0] : -3.0e38f;
+        const float4 xj = reinterpret_cast<const float4*>(buf)[s0];
+        point_terms<MODE>(prm, R, t, xi[u], xj, (long long)ind[u], qv, h, g);
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < kAccUnroll; u++) {
+        const int sl = slot_of(it, u, false);
+        const int s0 = sl < 0 ? 0 : sl;  // past-the-end lanes re-read slot 0 with weight 0
+        const bool vm = sl >= 0 && buf[kOffVm + s0] != 0;
+        const float qv = vm ? reinterpret_cast<const float*>(buf + kOffQ)[s0] : -3.0e38f;
+        const float4 xj = reinterpret_cast<const float4*>(buf)[s0];
+        point_terms<MODE>(prm, R, t, xi[u], xj, (long long)ind[u], qv, h, g);
+      }
     }
     __syncthreads();  // every thread is done with stage `it`: its buffer may be refilled
     if (tid == 0 && it + kStages < T) issue(it + kStages);
