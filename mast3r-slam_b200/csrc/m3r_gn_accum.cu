@@ -121,6 +121,7 @@ struct GnDev {  // kernel-side copy of m3r_gn_params with the sigmas pre-inverte
   float u_lo, u_hi, v_lo, v_hi;  // pixel_border, width-1-border, ... as floats
   float z_eps;
   int width;
+  unsigned width_magic;  // ceil(2^32 / width): idx / width by one multiply-high and a fix-up
 };
 
 __device__ __forceinline__ float fast_rcp(float x) {
@@ -193,7 +194,13 @@ __device__ __forceinline__ void point_terms(const GnDev& prm, const float* R, co
     { const float J[7] = {dxz, dyz, dzz, ry, -rx, 0.f, 0.f}; acc_row<0x1Fu>(h, g, w2, e2, J); }
     { const float J[7] = {rx, ry, rz, 0.f, 0.f, 0.f, nj}; acc_row<0x47u>(h, g, w3, e3, J); }
   } else if (MODE == M3R_GN_CALIB) {  // gn_kernels.cu:1360-1495
-    const int u_t = (int)(ind % prm.width), v_t = (int)(ind / prm.width);
+    // (u_t, v_t) = (idx % width, idx / width) for 0 <= idx < 2^31 without a 64-bit division:
+    // q = hi32(idx * ceil(2^32 / width)) is the quotient or one above it
+    const int i32 = (int)ind;
+    int v_t = (int)__umulhi((unsigned)i32, prm.width_magic);
+    int u_t = i32 - v_t * prm.width;
+    if (u_t < 0) { v_t -= 1; u_t += prm.width; }
+    if (u_t >= prm.width) { v_t += 1; u_t -= prm.width; }  // width == 1 (magic saturates)
     const bool valid_z = (Pz > prm.z_eps) && (xi.z > prm.z_eps);
     const float zinv = valid_z ? 1.0f / Pz : 0.f;
     const float zj_log = valid_z ? logf(Pz) : 0.f;
@@ -542,6 +549,7 @@ static GnDev make_dev_params(const m3r_gn_params* p) {
   d.v_lo = (float)p->pixel_border; d.v_hi = (float)(p->height - 1 - p->pixel_border);
   d.z_eps = p->z_eps;
   d.width = p->width > 0 ? p->width : 1;
+  d.width_magic = d.width > 1 ? (unsigned)((0x100000000ULL + (unsigned)d.width - 1) / (unsigned)d.width) : 0xFFFFFFFFu;
   return d;
 }
 
