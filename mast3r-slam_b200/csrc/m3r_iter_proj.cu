@@ -165,7 +165,15 @@ iter_proj_fused_kernel(const float* __restrict__ rays_img, const float* __restri
   const float nrm = fmaxf(sqrtf(x * x + y * y + z * z), 1e-12f);
   const float t0 = x / nrm, t1 = y / nrm, t2 = z / nrm;
   const int64_t lin = idx_init ? __ldg(idx_init + bk) : (int64_t)k;
-  float u = (float)(lin % W), v = (float)(lin / W);  // lin_to_pixel().float(), matching.py:18-22,47-48
+  // lin_to_pixel().float(), matching.py:18-22,47-48; 32-bit division whenever the index fits
+  // (always, for indices into the image) instead of the 64-bit division subroutine
+  float u, v;
+  if ((unsigned long long)lin < 0x80000000ULL) {
+    const unsigned l32 = (unsigned)lin, q = l32 / (unsigned)W;
+    u = (float)(l32 - q * (unsigned)W); v = (float)q;
+  } else {
+    u = (float)(lin % W); v = (float)(lin / W);
+  }
   bool conv;
   lm_pixel(img, H, W, t0, t1, t2, u, v, max_iter, lambda_init, cost_thresh, conv);
   if (p_new) reinterpret_cast<float2*>(p_new)[bk] = make_float2(u, v);
