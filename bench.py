@@ -208,7 +208,7 @@ def main():
     in_bytes = sum(t.numel() * t.element_size() for t in (X11, X21, D11, D21))
 
     def step_kernels(ev=None):
-        rays, D11h = be.match_prep(X11, D11)
+        rays, D11h = be.match_prep(X11, D11, packed=True)
         if ev: ev[1].record()
         p1, valid = be.match_iter_proj_fused(rays, X11, X21, None, MATCH["max_iter"], MATCH["lambda_init"],
                                              MATCH["convergence_thresh"], MATCH["dist_thresh"])

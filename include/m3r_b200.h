@@ -112,6 +112,18 @@ int m3r_match_iter_proj_fused(const float* rays_img_with_grad, const float* X11,
                               float cost_thresh, float dist_thresh, int64_t* p1,
                               uint8_t* valid, float* p_new, m3r_stream_t stream);
 
+/* The same two steps over the PRIVATE float4-packed ray image of the fused pipeline:
+ * rays_packed (b,H,W,12) f32, 16-byte aligned = three 16-B words per pixel
+ * [ray.xyz, 0 | d(ray)/du.xyz, 0 | d(ray)/dv.xyz, 0], so that a bilinear sample of one group is
+ * four 128-bit gathers instead of twelve scalar ones.  Values and arithmetic are those of the
+ * 9-channel form (same results bit for bit); only the layout differs. */
+int m3r_match_prep_packed(const float* X11, const float* D11, int b, int H, int W, int F,
+                          float* rays_packed, uint16_t* D11h, m3r_stream_t stream);
+int m3r_match_iter_proj_packed(const float* rays_packed, const float* X11, const float* X21,
+                               const int64_t* idx_init, int b, int H, int W, int max_iter,
+                               float lambda_init, float cost_thresh, float dist_thresh,
+                               int64_t* p1, uint8_t* valid, float* p_new, m3r_stream_t stream);
+
 /* m3r_match_refine_fused: refine_matches reading D21 as f32 (rounded to f16 on the
  * fly, == .half()) against the f16 copy of D11 made by m3r_match_prep, and writing
  * the linear index idx_1_to_2 = u + W*v (pixel_to_lin, matching.py:13-15).

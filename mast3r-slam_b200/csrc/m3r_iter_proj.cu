@@ -19,14 +19,19 @@ __device__ __forceinline__ void clampf(float& x, const float lo, const float hi)
   x = fminf(fmaxf(x, lo), hi);
 }
 
+// CH = 9: the reference's (b,H,W,9) image, scalar gathers.  CH = 12: the private layout of the
+// fused pipeline, three 16-B words per pixel [ray,0 | d/du,0 | d/dv,0]: a bilinear sample of one
+// group is four LDG.128 instead of twelve scalar loads (same values, same expression).
+template <int CH>
 struct Bilin {
   const float* r11; const float* r12; const float* r21; const float* r22;
   float w11, w12, w21, w22;
 };
 
 // Weights and texel pointers for a sample at (u,v); matching_kernels.cu:155-170.
-__device__ __forceinline__ Bilin bilin_setup(const float* __restrict__ img, int W, float u, float v) {
-  Bilin s;
+template <int CH>
+__device__ __forceinline__ Bilin<CH> bilin_setup(const float* __restrict__ img, int W, float u, float v) {
+  Bilin<CH> s;
   const int u11 = static_cast<int>(floorf(u));
   const int v11 = static_cast<int>(floorf(v));
   const float du = u - static_cast<float>(u11);
@@ -35,17 +40,33 @@ __device__ __forceinline__ Bilin bilin_setup(const float* __restrict__ img, int 
   s.w12 = (1.0 - du) * dv;          // double product, rounded once (as the reference)
   s.w21 = du * (1.0 - dv);
   s.w22 = (1.0 - du) * (1.0 - dv);
-  const float* base = img + ((size_t)v11 * W + u11) * 9;
+  const float* base = img + ((size_t)v11 * W + u11) * CH;
   s.r22 = base;                      // (v11  , u11  )
-  s.r21 = base + 9;                  // (v11  , u11+1)
-  s.r12 = base + (size_t)W * 9;      // (v11+1, u11  )
-  s.r11 = s.r12 + 9;                 // (v11+1, u11+1)
+  s.r21 = base + CH;                 // (v11  , u11+1)
+  s.r12 = base + (size_t)W * CH;     // (v11+1, u11  )
+  s.r11 = s.r12 + CH;                // (v11+1, u11+1)
   return s;
 }
 
-__device__ __forceinline__ float bilin_ch(const Bilin& s, int j) {
-  return s.w11 * __ldg(s.r11 + j) + s.w12 * __ldg(s.r12 + j) + s.w21 * __ldg(s.r21 + j) +
-         s.w22 * __ldg(s.r22 + j);
+// channels 3g .. 3g+2 (g = 0 ray, 1 d/du, 2 d/dv) of the sample
+template <int CH>
+__device__ __forceinline__ void bilin_group(const Bilin<CH>& s, int g, float* out) {
+  if (CH == 12) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(s.r11) + g);
+    const float4 b = __ldg(reinterpret_cast<const float4*>(s.r12) + g);
+    const float4 c = __ldg(reinterpret_cast<const float4*>(s.r21) + g);
+    const float4 d = __ldg(reinterpret_cast<const float4*>(s.r22) + g);
+    out[0] = s.w11 * a.x + s.w12 * b.x + s.w21 * c.x + s.w22 * d.x;
+    out[1] = s.w11 * a.y + s.w12 * b.y + s.w21 * c.y + s.w22 * d.y;
+    out[2] = s.w11 * a.z + s.w12 * b.z + s.w21 * c.z + s.w22 * d.z;
+  } else {
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      const int ch = 3 * g + j;
+      out[j] = s.w11 * __ldg(s.r11 + ch) + s.w12 * __ldg(s.r12 + ch) + s.w21 * __ldg(s.r21 + ch) +
+               s.w22 * __ldg(s.r22 + ch);
+    }
+  }
 }
 
 __device__ __forceinline__ void normalize3(float* r) {  // matching_kernels.cu:186-191
@@ -55,6 +76,7 @@ __device__ __forceinline__ void normalize3(float* r) {  // matching_kernels.cu:1
 }
 
 // The LM loop for one pixel.  Returns the final (u,v) and the `converged` flag.
+template <int CH>
 __device__ __forceinline__ void lm_pixel(const float* __restrict__ img, int H, int W,
                                          const float t0, const float t1, const float t2,
                                          float& u, float& v, int max_iter, float lambda,
@@ -68,19 +90,16 @@ __device__ __forceinline__ void lm_pixel(const float* __restrict__ img, int H, i
   bool have_ray = false;  // err/cost already valid for (u,v)
   for (int i = 0; i < max_iter; i++) {
     if (moved) {
-      const Bilin s = bilin_setup(img, W, u, v);
+      const Bilin<CH> s = bilin_setup<CH>(img, W, u, v);
       if (!have_ray) {
         float r[3];
-#pragma unroll
-        for (int j = 0; j < 3; j++) r[j] = bilin_ch(s, j);
+        bilin_group<CH>(s, 0, r);
         normalize3(r);
         err[0] = r[0] - t0; err[1] = r[1] - t1; err[2] = r[2] - t2;
         cost = err[0] * err[0] + err[1] * err[1] + err[2] * err[2];
       }
-#pragma unroll
-      for (int j = 0; j < 3; j++) gx[j] = bilin_ch(s, 3 + j);
-#pragma unroll
-      for (int j = 0; j < 3; j++) gy[j] = bilin_ch(s, 6 + j);
+      bilin_group<CH>(s, 1, gx);
+      bilin_group<CH>(s, 2, gy);
       A00 = gx[0] * gx[0] + gx[1] * gx[1] + gx[2] * gx[2];
       A01 = gx[0] * gy[0] + gx[1] * gy[1] + gx[2] * gy[2];
       A11 = gy[0] * gy[0] + gy[1] * gy[1] + gy[2] * gy[2];
@@ -104,10 +123,9 @@ __device__ __forceinline__ void lm_pixel(const float* __restrict__ img, int H, i
     if (u_new == u && v_new == v) {
       new_cost = cost;  // same position, same expression => same bits; step is rejected
     } else {
-      const Bilin s = bilin_setup(img, W, u_new, v_new);
+      const Bilin<CH> s = bilin_setup<CH>(img, W, u_new, v_new);
       float r[3];
-#pragma unroll
-      for (int j = 0; j < 3; j++) r[j] = bilin_ch(s, j);
+      bilin_group<CH>(s, 0, r);
       normalize3(r);
       e2[0] = r[0] - t0; e2[1] = r[1] - t1; e2[2] = r[2] - t2;
       new_cost = e2[0] * e2[0] + e2[1] * e2[1] + e2[2] * e2[2];
@@ -141,7 +159,7 @@ iter_proj_kernel(const float* __restrict__ rays_img, const float* __restrict__ p
   float u = p0.x, v = p0.y;
   const float t0 = __ldg(pts + bk * 3 + 0), t1 = __ldg(pts + bk * 3 + 1), t2 = __ldg(pts + bk * 3 + 2);
   bool conv;
-  lm_pixel(img, H, W, t0, t1, t2, u, v, max_iter, lambda_init, cost_thresh, conv);
+  lm_pixel<9>(img, H, W, t0, t1, t2, u, v, max_iter, lambda_init, cost_thresh, conv);
   reinterpret_cast<float2*>(p_new)[bk] = make_float2(u, v);
   converged[bk] = conv ? 1 : 0;
 }
@@ -149,6 +167,7 @@ iter_proj_kernel(const float* __restrict__ rays_img, const float* __restrict__ p
 // Fused form (matching.py:25-76): target = F.normalize(X21) on the fly, p_init from the
 // linear index (identity when idx_init == nullptr), then p1 = trunc(p) and the occlusion
 // test |X11[p1] - X21| < dist_thresh folded into `valid`.
+template <int CH>
 __global__ void __launch_bounds__(kIterProjThreads)
 iter_proj_fused_kernel(const float* __restrict__ rays_img, const float* __restrict__ X11,
                        const float* __restrict__ X21, const int64_t* __restrict__ idx_init,
@@ -159,7 +178,7 @@ iter_proj_fused_kernel(const float* __restrict__ rays_img, const float* __restri
   const int k = blockIdx.x * kIterProjThreads + threadIdx.x;
   if (k >= n) return;
   const size_t bk = (size_t)blockIdx.y * n + k;
-  const float* img = rays_img + (size_t)blockIdx.y * n * 9;
+  const float* img = rays_img + (size_t)blockIdx.y * n * CH;
   const float x = __ldg(X21 + bk * 3 + 0), y = __ldg(X21 + bk * 3 + 1), z = __ldg(X21 + bk * 3 + 2);
   // F.normalize(dim=-1, eps=1e-12): x / max(|x|_2, eps)
   const float nrm = fmaxf(sqrtf(x * x + y * y + z * z), 1e-12f);
@@ -175,7 +194,7 @@ iter_proj_fused_kernel(const float* __restrict__ rays_img, const float* __restri
     u = (float)(lin % W); v = (float)(lin / W);
   }
   bool conv;
-  lm_pixel(img, H, W, t0, t1, t2, u, v, max_iter, lambda_init, cost_thresh, conv);
+  lm_pixel<CH>(img, H, W, t0, t1, t2, u, v, max_iter, lambda_init, cost_thresh, conv);
   if (p_new) reinterpret_cast<float2*>(p_new)[bk] = make_float2(u, v);
   const int ui = (int)u, vi = (int)v;  // .long(): truncation; u,v are within [1,W-2]x[1,H-2]
   const float* Xm = X11 + ((size_t)blockIdx.y * n + (size_t)vi * W + ui) * 3;
@@ -205,18 +224,39 @@ extern "C" int m3r_iter_proj(const float* rays_img_with_grad, const float* pts_3
   return after_launch();
 }
 
+static int iter_proj_fused_launch(int ch, const float* rays, const float* X11, const float* X21,
+                                  const int64_t* idx_init, int b, int H, int W, int max_iter,
+                                  float lambda_init, float cost_thresh, float dist_thresh, int64_t* p1,
+                                  uint8_t* valid, float* p_new, m3r_stream_t stream) {
+  if (b < 0 || H < 3 || W < 3 || max_iter < 0 || b > 65535) return M3R_EINVAL;
+  if (b == 0) return M3R_OK;
+  if (!rays || !X11 || !X21 || !p1 || !valid) return M3R_EINVAL;
+  if (ch == 12 && (reinterpret_cast<uintptr_t>(rays) & 15) != 0) return M3R_EINVAL;
+  const int n = H * W;
+  dim3 grid((n + kIterProjThreads - 1) / kIterProjThreads, b);
+  if (ch == 12)
+    iter_proj_fused_kernel<12><<<grid, kIterProjThreads, 0, as_stream(stream)>>>(
+        rays, X11, X21, idx_init, H, W, max_iter, lambda_init, cost_thresh, dist_thresh, p1, valid, p_new);
+  else
+    iter_proj_fused_kernel<9><<<grid, kIterProjThreads, 0, as_stream(stream)>>>(
+        rays, X11, X21, idx_init, H, W, max_iter, lambda_init, cost_thresh, dist_thresh, p1, valid, p_new);
+  return after_launch();
+}
+
 extern "C" int m3r_match_iter_proj_fused(const float* rays_img_with_grad, const float* X11,
                                          const float* X21, const int64_t* idx_init, int b,
                                          int H, int W, int max_iter, float lambda_init,
                                          float cost_thresh, float dist_thresh, int64_t* p1,
                                          uint8_t* valid, float* p_new, m3r_stream_t stream) {
-  if (b < 0 || H < 3 || W < 3 || max_iter < 0 || b > 65535) return M3R_EINVAL;
-  if (b == 0) return M3R_OK;
-  if (!rays_img_with_grad || !X11 || !X21 || !p1 || !valid) return M3R_EINVAL;
-  const int n = H * W;
-  dim3 grid((n + kIterProjThreads - 1) / kIterProjThreads, b);
-  iter_proj_fused_kernel<<<grid, kIterProjThreads, 0, as_stream(stream)>>>(
-      rays_img_with_grad, X11, X21, idx_init, H, W, max_iter, lambda_init, cost_thresh,
-      dist_thresh, p1, valid, p_new);
-  return after_launch();
+  return iter_proj_fused_launch(9, rays_img_with_grad, X11, X21, idx_init, b, H, W, max_iter, lambda_init,
+                                cost_thresh, dist_thresh, p1, valid, p_new, stream);
+}
+
+extern "C" int m3r_match_iter_proj_packed(const float* rays_packed, const float* X11,
+                                          const float* X21, const int64_t* idx_init, int b,
+                                          int H, int W, int max_iter, float lambda_init,
+                                          float cost_thresh, float dist_thresh, int64_t* p1,
+                                          uint8_t* valid, float* p_new, m3r_stream_t stream) {
+  return iter_proj_fused_launch(12, rays_packed, X11, X21, idx_init, b, H, W, max_iter, lambda_init,
+                                cost_thresh, dist_thresh, p1, valid, p_new, stream);
 }

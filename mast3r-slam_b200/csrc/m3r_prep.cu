@@ -18,12 +18,15 @@ __device__ __forceinline__ int reflect(int i, int n) {  // F.pad(mode="reflect")
 }
 
 // One 32x8 pixel tile (bx, by) of image bz; 256 threads, tid = ty*32 + tx.
+// CH = 9: the reference's (b,H,W,9) layout.  CH = 12: three 16-B words per pixel
+// [ray,0 | d/du,0 | d/dv,0], the layout m3r_match_iter_proj_packed gathers with LDG.128.
+template <int CH>
 __device__ __forceinline__ void prep_rays_tile(const float* __restrict__ X11, int H, int W,
                                                float* __restrict__ out, int bx, int by, int bz) {
   __shared__ float tile[kPrepTY + 2][kPrepTX + 2][3];
   // output staging: one tile row is kPrepTX*9 contiguous floats in the (b,H,W,9) image, written
   // back as coalesced 16-B words (9 scalar 36-B-strided stores per thread kept the LSU 69 % busy)
-  __shared__ __align__(16) float stage[kPrepTY][kPrepTX * 9];
+  __shared__ __align__(16) float stage[kPrepTY][kPrepTX * CH];
   const int tid = threadIdx.x;
   const int thx = tid % kPrepTX, thy = tid / kPrepTX;
   const int x0 = bx * kPrepTX, y0 = by * kPrepTY;
@@ -40,7 +43,9 @@ __device__ __forceinline__ void prep_rays_tile(const float* __restrict__ X11, in
   __syncthreads();
   {
     const int tx = thx + 1, ty = thy + 1;
-    float* o = &stage[thy][thx * 9];
+    float* o = &stage[thy][thx * CH];
+    constexpr int G = CH == 12 ? 4 : 3;  // stride between the ray / d-du / d-dv groups
+    if (CH == 12) { o[3] = 0.f; o[7] = 0.f; o[11] = 0.f; }
     const float k3 = 3.0f / 32.0f, k10 = 10.0f / 32.0f;  // (1/32)*[-3,0,3;-10,0,10;-3,0,3]
 #pragma unroll
     for (int c = 0; c < 3; c++) {
@@ -48,16 +53,16 @@ __device__ __forceinline__ void prep_rays_tile(const float* __restrict__ X11, in
       const float ml = tile[ty][tx - 1][c], mr = tile[ty][tx + 1][c];
       const float bl = tile[ty + 1][tx - 1][c], bc = tile[ty + 1][tx][c], br = tile[ty + 1][tx + 1][c];
       o[c] = tile[ty][tx][c];
-      o[3 + c] = -k3 * tl + k3 * tr - k10 * ml + k10 * mr - k3 * bl + k3 * br;   // gx
-      o[6 + c] = -k3 * tl - k10 * tc - k3 * tr + k3 * bl + k10 * bc + k3 * br;   // gy
+      o[G + c] = -k3 * tl + k3 * tr - k10 * ml + k10 * mr - k3 * bl + k3 * br;   // gx
+      o[2 * G + c] = -k3 * tl - k10 * tc - k3 * tr + k3 * bl + k10 * bc + k3 * br;   // gy
     }
   }
   __syncthreads();
   const int cols = min(kPrepTX, W - x0);   // valid pixels of this tile row
   const int rows = min(kPrepTY, H - y0);
-  const int nfl = cols * 9;                // valid floats per row
-  float* dst0 = out + (((size_t)bz * H + y0) * W + x0) * 9;
-  const size_t row_stride = (size_t)W * 9;
+  const int nfl = cols * CH;               // valid floats per row
+  float* dst0 = out + (((size_t)bz * H + y0) * W + x0) * CH;
+  const size_t row_stride = (size_t)W * CH;
   if ((nfl & 3) == 0 && (row_stride & 3) == 0 && ((reinterpret_cast<uintptr_t>(dst0) & 15) == 0)) {
     const int per_row = nfl / 4;
     for (int i = tid; i < rows * per_row; i += kPrepTX * kPrepTY) {
@@ -91,10 +96,11 @@ __device__ __forceinline__ void cast_f16_block(const float* __restrict__ src, si
   }
 }
 
+template <int CH>
 __global__ void __launch_bounds__(256)
 prep_rays_kernel(const float* __restrict__ X11, int H, int W, int tiles_x, int tiles_y, float* __restrict__ out) {
   const int t = blockIdx.x, per = tiles_x * tiles_y;
-  prep_rays_tile(X11, H, W, out, (t % per) % tiles_x, (t % per) / tiles_x, t / per);
+  prep_rays_tile<CH>(X11, H, W, out, (t % per) % tiles_x, (t % per) / tiles_x, t / per);
 }
 
 __global__ void __launch_bounds__(256)
@@ -105,6 +111,7 @@ cast_f16_kernel(const float* __restrict__ src, size_t count8, size_t count, uint
 // Both jobs of m3r_match_prep in ONE launch: they are independent, one is bound by L1/shared
 // and instruction issue, the other by HBM, so their CTAs overlap on the SMs instead of running
 // back to back with a launch gap in between.  Cast blocks are interleaved 1:2 with ray tiles.
+template <int CH>
 __global__ void __launch_bounds__(256)
 match_prep_kernel(const float* __restrict__ X11, int H, int W, int tiles_x, int tiles_y, int ray_blocks,
                   float* __restrict__ rays, const float* __restrict__ D11, size_t count8, size_t count,
@@ -120,7 +127,7 @@ match_prep_kernel(const float* __restrict__ X11, int H, int W, int tiles_x, int 
     const int r = t - casts_before;
     if (r < ray_blocks) {
       const int per = tiles_x * tiles_y;
-      prep_rays_tile(X11, H, W, rays, (r % per) % tiles_x, (r % per) / tiles_x, r / per);
+      prep_rays_tile<CH>(X11, H, W, rays, (r % per) % tiles_x, (r % per) / tiles_x, r / per);
     }
   }
 }
@@ -129,13 +136,15 @@ match_prep_kernel(const float* __restrict__ X11, int H, int W, int tiles_x, int 
 
 using namespace m3r;
 
-extern "C" int m3r_match_prep(const float* X11, const float* D11, int b, int H, int W, int F,
-                              float* rays_img_with_grad, uint16_t* D11h, m3r_stream_t stream) {
+template <int CH>
+static int match_prep_launch(const float* X11, const float* D11, int b, int H, int W, int F,
+                             float* rays, uint16_t* D11h, m3r_stream_t stream) {
   if (b < 0 || H < 2 || W < 2 || b > 65535) return M3R_EINVAL;
   if (b == 0) return M3R_OK;
   cudaStream_t st = as_stream(stream);
-  if (rays_img_with_grad && !X11) return M3R_EINVAL;
+  if (rays && !X11) return M3R_EINVAL;
   if (D11h && (!D11 || F <= 0)) return M3R_EINVAL;
+  if (CH == 12 && rays && (reinterpret_cast<uintptr_t>(rays) & 15) != 0) return M3R_EINVAL;
   const int tiles_x = (W + kPrepTX - 1) / kPrepTX, tiles_y = (H + kPrepTY - 1) / kPrepTY;
   const long long ray_blocks_ll = (long long)tiles_x * tiles_y * b;
   const size_t count = D11h ? (size_t)b * H * W * F : 0;
@@ -145,13 +154,13 @@ extern "C" int m3r_match_prep(const float* X11, const float* D11, int b, int H, 
   if (cast_blocks < 1) cast_blocks = 1;
   if (ray_blocks_ll + (long long)cast_blocks > 0x7fffffffLL) return M3R_EINVAL;
   const int ray_blocks = (int)ray_blocks_ll;
-  if (rays_img_with_grad && D11h && ray_blocks >= 2 * (int)cast_blocks) {
-    match_prep_kernel<<<ray_blocks + (int)cast_blocks, 256, 0, st>>>(
-        X11, H, W, tiles_x, tiles_y, ray_blocks, rays_img_with_grad, D11, count8, count, (int)cast_blocks, D11h);
+  if (rays && D11h && ray_blocks >= 2 * (int)cast_blocks) {
+    match_prep_kernel<CH><<<ray_blocks + (int)cast_blocks, 256, 0, st>>>(
+        X11, H, W, tiles_x, tiles_y, ray_blocks, rays, D11, count8, count, (int)cast_blocks, D11h);
     return after_launch();
   }
-  if (rays_img_with_grad) {
-    prep_rays_kernel<<<ray_blocks, 256, 0, st>>>(X11, H, W, tiles_x, tiles_y, rays_img_with_grad);
+  if (rays) {
+    prep_rays_kernel<CH><<<ray_blocks, 256, 0, st>>>(X11, H, W, tiles_x, tiles_y, rays);
     M3R_TRY(after_launch());
   }
   if (D11h) {
@@ -159,4 +168,14 @@ extern "C" int m3r_match_prep(const float* X11, const float* D11, int b, int H, 
     M3R_TRY(after_launch());
   }
   return M3R_OK;
+}
+
+extern "C" int m3r_match_prep(const float* X11, const float* D11, int b, int H, int W, int F,
+                              float* rays_img_with_grad, uint16_t* D11h, m3r_stream_t stream) {
+  return match_prep_launch<9>(X11, D11, b, H, W, F, rays_img_with_grad, D11h, stream);
+}
+
+extern "C" int m3r_match_prep_packed(const float* X11, const float* D11, int b, int H, int W, int F,
+                                     float* rays_packed, uint16_t* D11h, m3r_stream_t stream) {
+  return match_prep_launch<12>(X11, D11, b, H, W, F, rays_packed, D11h, stream);
 }

@@ -40,7 +40,8 @@ def match_iterative_proj(X11, X21, D11, D21, idx_1_to_2_init=None):
     b, h, w = X21.shape[:3]
     X11, X21 = X11.contiguous(), X21.contiguous()
     refine = cfg["radius"] > 0
-    rays, D11h = _be.match_prep(X11, D11.contiguous() if refine else None)
+    # float4-packed private ray image: the LM loop gathers it with 128-bit loads
+    rays, D11h = _be.match_prep(X11, D11.contiguous() if refine else None, packed=True)
     if idx_1_to_2_init is not None:
         idx_1_to_2_init = idx_1_to_2_init.contiguous()
     p1, valid = _be.match_iter_proj_fused(rays, X11, X21, idx_1_to_2_init, cfg["max_iter"],

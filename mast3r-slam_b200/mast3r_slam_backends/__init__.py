@@ -61,6 +61,7 @@ EXPORTS = [
     "m3r_gn_workspace_bytes", "m3r_gauss_newton", "m3r_gn_prepare", "m3r_gn_accumulate",
     "m3r_gn_solve_step", "m3r_gn_done_flag", "m3r_gn_blocks", "m3r_track_workspace_bytes",
     "m3r_track_ray_dist", "m3r_track_calib", "m3r_debug_chol_trace", "m3r_edge_build", "m3r_pointmap_update", "m3r_gn_accumulate_p2p", "m3r_gn_solve_step_p2p",
+    "m3r_match_prep_packed", "m3r_match_iter_proj_packed",
     "m3r_render_default_opts", "m3r_render_clear", "m3r_render_surfels", "m3r_render_triangles",
     "m3r_render_resolve",
 ]
@@ -83,6 +84,8 @@ def _load():
     lib.m3r_match_prep.argtypes = [vp, vp, i32, i32, i32, i32, vp, vp, vp]
     lib.m3r_match_iter_proj_fused.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, f32, f32, f32,
                                               vp, vp, vp, vp]
+    lib.m3r_match_prep_packed.argtypes = lib.m3r_match_prep.argtypes
+    lib.m3r_match_iter_proj_packed.argtypes = lib.m3r_match_iter_proj_fused.argtypes
     lib.m3r_match_refine_fused.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp]
     lib.m3r_pose_retr.argtypes = [vp, vp, i32, i32, vp]
     lib.m3r_gn_workspace_bytes.restype = sz
@@ -198,20 +201,22 @@ def refine_matches(D11, D21, p1, radius, dilation_max):
     return [out]
 
 
-def match_prep(X11, D11=None):
+def match_prep(X11, D11=None, packed=False):
     """Fused prep_for_iter_proj (matching.py:25-50) + D11.half() (matching.py:80).
-    -> (rays_img_with_grad (b,H,W,9) f32, D11h (b,H,W,F) f16 or None)"""
+    -> (rays_img_with_grad (b,H,W,9) f32, D11h (b,H,W,F) f16 or None); packed=True gives the
+    private (b,H,W,12) float4 layout [ray,0 | d/du,0 | d/dv,0] that match_iter_proj_fused gathers
+    with 128-bit loads."""
     X11 = _req(X11, "X11", torch.float32, 4)
     b, H, W, _ = X11.shape
     with torch.cuda.device(X11.device):
-        rays = torch.empty((b, H, W, 9), dtype=torch.float32, device=X11.device)
+        rays = torch.empty((b, H, W, 12 if packed else 9), dtype=torch.float32, device=X11.device)
         D11h, F = None, 0
         if D11 is not None:
             D11 = _req(D11, "D11", torch.float32, 4)
             F = D11.shape[-1]
             D11h = torch.empty(D11.shape, dtype=torch.float16, device=X11.device)
-        _check(_lib.m3r_match_prep(_ptr(X11), _ptr(D11), b, H, W, F, _ptr(rays), _ptr(D11h),
-                                   _stream(X11)), "match_prep")
+        fn = _lib.m3r_match_prep_packed if packed else _lib.m3r_match_prep
+        _check(fn(_ptr(X11), _ptr(D11), b, H, W, F, _ptr(rays), _ptr(D11h), _stream(X11)), "match_prep")
     return rays, D11h
 
 
@@ -221,7 +226,9 @@ def match_iter_proj_fused(rays_img_with_grad, X11, X21, idx_init, max_iter, lamb
     img = _req(rays_img_with_grad, "rays_img_with_grad", torch.float32, 4)
     X11 = _req(X11, "X11", torch.float32, 4)
     X21 = _req(X21, "X21", torch.float32, 4)
-    b, H, W, _ = img.shape
+    b, H, W, ch = img.shape
+    if ch not in (9, 12):
+        raise RuntimeError("rays_img_with_grad must have 9 channels (reference layout) or 12 (packed)")
     n = H * W
     if idx_init is not None:
         idx_init = _req(idx_init, "idx_1_to_2_init", torch.int64, 2)
@@ -229,7 +236,8 @@ def match_iter_proj_fused(rays_img_with_grad, X11, X21, idx_init, max_iter, lamb
         p1 = torch.empty((b, n, 2), dtype=torch.int64, device=img.device)
         valid = torch.empty((b, n), dtype=torch.bool, device=img.device)
         p_new = torch.empty((b, n, 2), dtype=torch.float32, device=img.device) if want_p_new else None
-        _check(_lib.m3r_match_iter_proj_fused(
+        fn = _lib.m3r_match_iter_proj_packed if ch == 12 else _lib.m3r_match_iter_proj_fused
+        _check(fn(
             _ptr(img), _ptr(X11), _ptr(X21), _ptr(idx_init), b, H, W, int(max_iter),
             float(lambda_init), float(cost_thresh), float(dist_thresh), _ptr(p1), _ptr(valid),
             _ptr(p_new), _stream(img)), "match_iter_proj_fused")

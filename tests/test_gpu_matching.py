@@ -235,6 +235,26 @@ def test_fused_prep_matches_torch_glue(backends):
     assert torch.allclose(rays, img_t, rtol=0, atol=2e-6)
 
 
+def test_packed_ray_image_equals_reference_layout(backends):
+    """The float4-packed private ray image (m3r_match_prep_packed / m3r_match_iter_proj_packed)
+    holds the same values as the (b,H,W,9) image and the LM loop over it returns the same bits."""
+    for (b, H, W) in [(2, 96, 128), (1, 33, 47)]:
+        m = synth.make_match_inputs(b, H, W, 24, seed=35, device=DEV)
+        rays9, D11h = backends.match_prep(m["X11"], m["D11"])
+        rays12, D11h2 = backends.match_prep(m["X11"], m["D11"], packed=True)
+        assert torch.equal(D11h, D11h2)
+        r12 = rays12.view(b, H, W, 3, 4)
+        assert torch.equal(r12[..., :3].reshape(b, H, W, 9), rays9)
+        assert bool((r12[..., 3] == 0).all())
+        for init in (None, torch.randint(0, H * W, (b, H * W), device=DEV)):
+            a = backends.match_iter_proj_fused(rays9, m["X11"], m["X21"], init, CFG["max_iter"], CFG["lambda_init"],
+                                               CFG["convergence_thresh"], CFG["dist_thresh"], want_p_new=True)
+            c = backends.match_iter_proj_fused(rays12, m["X11"], m["X21"], init, CFG["max_iter"], CFG["lambda_init"],
+                                               CFG["convergence_thresh"], CFG["dist_thresh"], want_p_new=True)
+            for x, y in zip(a, c):
+                assert torch.equal(x, y)
+
+
 def test_fused_match_equals_unfused_pipeline(backends):
     """m3r_match_prep + m3r_match_iter_proj_fused + m3r_match_refine_fused == the reference
     call sequence of matching.match_iterative_proj (matching.py:52-90) run through the plain
