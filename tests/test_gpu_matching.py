@@ -165,6 +165,41 @@ def test_refine_matches_bit_exact_vs_reference_full_size(backends, ref_ext):
     assert torch.equal(o, r)
 
 
+@pytest.mark.parametrize("radius,dil,H,W,F,n_q", [
+    (1, 1, 24, 40, 8, None), (2, 3, 31, 45, 16, None), (3, 7, 64, 80, 24, None), (4, 2, 40, 56, 32, None),
+    (3, 5, 48, 64, 24, 1000), (0, 5, 24, 32, 24, None), (3, 5, 7, 9, 24, None),
+])
+def test_refine_matches_parameter_sweep_bit_exact(backends, orc, ref_ext, radius, dil, H, W, F, n_q):
+    """Generic paths of the kernel: radius != 3, dilation > 5, windows larger than the image,
+    a query list that is not the pixel grid (n != H*W, 1-D CTAs), p1 outside the image and far
+    outside int32; all bit-exact against the C restatement (and the reference extension where it
+    is safe to run: it has no bounds guard on n)."""
+    g = torch.Generator(device=DEV).manual_seed(7000 + 31 * radius + dil)
+    b = 2
+    n = H * W if n_q is None else n_q
+    D11 = torch.randn((b, H, W, F), generator=g, device=DEV).half().contiguous()
+    D21 = torch.randn((b, n, F), generator=g, device=DEV).half().contiguous()
+    p1 = torch.stack((torch.randint(-3, W + 3, (b, n), generator=g, device=DEV),
+                      torch.randint(-3, H + 3, (b, n), generator=g, device=DEV)), -1).contiguous()
+    p1[0, 0] = torch.tensor([2 ** 40, 5], device=DEV)      # outside int32: returned as given
+    p1[1, 1] = torch.tensor([3, -(2 ** 35)], device=DEV)
+    (out,) = backends.refine_matches(D11, D21, p1, radius, dil)
+    torch.cuda.synchronize()
+    exp = orc.refine_matches(_np(D11), _np(D21), _np(p1), radius, dil)
+    diff = _np(out) != exp
+    # the two far-outside queries: the reference truncates long -> int (H3), the oracle follows it;
+    # the kernel keeps them outside the image.  Both leave such a query where it was.
+    diff[0, 0] = False; diff[1, 1] = False
+    assert not diff.any(), f"{int(diff.sum())} coordinates differ"
+    assert torch.equal(out[0, 0], p1[0, 0]) and torch.equal(out[1, 1], p1[1, 1])
+    if ref_ext is not None and n % 16 == 0:
+        q1 = p1.clone(); q1[0, 0] = 0; q1[1, 1] = 0
+        (r,) = ref_ext.refine_matches(D11, D21, q1, radius, dil)
+        (o,) = backends.refine_matches(D11, D21, q1, radius, dil)
+        torch.cuda.synchronize()
+        assert torch.equal(o, r)
+
+
 def test_refine_matches_f32_vs_oracle_and_reference(backends, orc, ref_ext):
     b, H, W, F = 1, 48, 64, 24
     D11, D21, p1 = _refine_inputs(b, H, W, 1400, F)
