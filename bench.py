@@ -175,10 +175,14 @@ def main():
                          "(use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    json_fd = None
     if world > 1:
-        # NCCL_DEBUG=VERSION makes NCCL print its banner on STDOUT, in front of the JSON line
-        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"
+        # NCCL prints its version banner on STDOUT at communicator creation: keep fd 1 for the ONE
+        # JSON line by pointing it at stderr for the rest of the run (rank 0 writes the line to
+        # the saved descriptor at the end)
+        sys.stdout.flush()
+        json_fd = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
 
     import mast3r_slam_backends as be
@@ -330,7 +334,14 @@ def main():
                          "refine_matches (OpenMP) + torch-CPU glue"}
 
     if rank == 0:
-        print(json.dumps({
+        def emit(obj):
+            line = json.dumps(obj) + "\n"
+            if json_fd is None:
+                sys.stdout.write(line); sys.stdout.flush()
+            else:
+                sys.stdout.flush()
+                os.write(json_fd, line.encode())
+        emit(({
             "metric": "dense matching throughput (match_iterative_proj)", "value": value, "unit": "Gpix/s",
             "n_gpus": world, "steps": K, "warmup": W_, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
