@@ -206,3 +206,43 @@ def test_sharded_exchange_gloo(backends, orc, tmp_path, world):
     assert np.abs(dx1).max() > 0
     for dx, b in outs[world]:
         assert np.array_equal(b, b1) and np.array_equal(dx, dx1)
+
+
+def test_headless_viewer_host_side(backends):
+    """Host logic of the viewer mirror: uniform defaults of the C ABI equal the shader sources'
+    (and the oracle's), colour packing, GL matrices.  No device work."""
+    import math
+
+    from mast3r_slam import visualization as viz
+    from oracle import render as orender
+
+    o, ref = backends.render_opts(), orender.default_opts()
+    for name, _ in ref._fields_:
+        a, b = getattr(o, name), getattr(ref, name)
+        if hasattr(a, "__len__"):
+            assert list(a) == list(b), name
+        else:
+            assert a == b, name
+    assert (o.radius, o.slant_threshold, o.spec) == (pytest.approx(0.003), pytest.approx(0.1), 32.0)
+    assert backends.render_opts(radius=0.01, phong=(1, 0, 0)).phong[0] == 1.0
+    with pytest.raises(TypeError):
+        backends.render_opts(no_such_uniform=1)
+    assert viz.hex2rgba("#1E2326") == 0xFF26231E  # R in the low byte
+    P = viz.perspective(90.0, 2.0, 0.1, 10.0)
+    assert P[1, 1] == pytest.approx(1.0) and P[0, 0] == pytest.approx(0.5) and P[3, 2] == -1.0
+    # a point on the optical axis at the near / far plane maps to NDC z = -1 / +1
+    for z, want in ((-0.1, -1.0), (-10.0, 1.0)):
+        c = P @ torch.tensor([0.0, 0.0, z, 1.0])
+        assert float(c[2] / c[3]) == pytest.approx(want, abs=1e-5)
+    V = viz.look_at((0.0, 0.0, -1.0), (0.0, 0.0, 2.0))
+    p = V @ torch.tensor([0.0, 0.0, 2.0, 1.0])          # the target lies 3 units down the -z axis
+    assert torch.allclose(p, torch.tensor([0.0, 0.0, -3.0, 1.0]), atol=1e-6)
+    up = V @ torch.tensor([0.0, -1.0, 0.0, 0.0])         # the SLAM world's -y is up on screen
+    assert float(up[1]) == pytest.approx(1.0)
+    # a camera sitting at a pose looks along its +z: view = diag(1,-1,-1,1) * T^-1
+    from mast3r_slam.sim3 import Sim3
+    T = Sim3(torch.tensor([[0.3, -0.2, 0.5, 0.0, math.sin(0.2), 0.0, math.cos(0.2), 1.7]]))
+    Vc = viz.view_from_camera_pose(T)
+    fwd = T.matrix().reshape(4, 4).cpu() @ torch.tensor([0.0, 0.0, 1.0, 1.0])  # 1.7 units ahead in the world
+    q = Vc @ fwd
+    assert torch.allclose(q[:3], torch.tensor([0.0, 0.0, -1.7]), atol=1e-5)
