@@ -26,6 +26,7 @@ namespace m3r {
 
 constexpr int kTrkThreads = 256;
 constexpr int kTrkVals = 36;  // 28 H + 7 g + 1 cost
+constexpr int kTrkChunks = kTrkThreads / kTrkVals;  // 7
 
 constexpr int kTrkRays = 0, kTrkCalib = 1;
 
@@ -73,6 +74,7 @@ track_kernel(const TrackArgs a) {
   cg::grid_group grid = cg::this_grid();
   __shared__ float red[kTrkThreads / 32][kTrkVals];
   __shared__ double tot[kTrkVals];
+  __shared__ double tot_part[kTrkChunks][kTrkVals];
   __shared__ float Tsh[8];
   __shared__ int stop_sh;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -170,9 +172,23 @@ track_kernel(const TrackArgs a) {
     __threadfence();
     grid.sync();
     // every CTA: identical fixed-order fp64 reduction + solve
+    // 7 x 36 threads: thread (chunk, value) sums every 7th partial (independent L2 loads in
+    // flight instead of one 296-long dependent walk per value), then the 7 chunk sums are added
+    // in chunk order — the same order in every CTA
+    {
+      const int val = tid % kTrkVals, chunk = tid / kTrkVals;
+      if (chunk < kTrkChunks) {
+        double s = 0.0;
+#pragma unroll 4
+        for (int c = chunk; c < (int)gridDim.x; c += kTrkChunks) s += (double)__ldcg(part + (size_t)c * kTrkVals + val);
+        tot_part[chunk][val] = s;
+      }
+    }
+    __syncthreads();
     if (tid < kTrkVals) {
       double s = 0.0;
-      for (int c = 0; c < (int)gridDim.x; c++) s += (double)__ldcg(part + (size_t)c * kTrkVals + tid);
+#pragma unroll
+      for (int k = 0; k < kTrkChunks; k++) s += tot_part[k][tid];
       tot[tid] = s;
     }
     __syncthreads();
@@ -253,7 +269,10 @@ static int track_grid_size(int mode) {
   else
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel<kTrkCalib>, kTrkThreads, 0);
   if (per_sm < 1) per_sm = 1;
-  if (per_sm > 2) per_sm = 2;
+  // one CTA per SM: the pass itself is a few microseconds (5.7 MB, L2-resident), what an
+  // iteration pays for is the grid barrier and the reduction of the partials, both of which grow
+  // with the CTA count (measured 296 / 148 / 111 / 74 CTAs: 59.7 / 52.7 / 53.0 / 56.1 us per solve)
+  per_sm = 1;
   cached = sms * per_sm;
   return cached;
 }
