@@ -362,64 +362,118 @@ __device__ __forceinline__ void trsm_warp(const Tile sx, const Tile sl, const do
 }
 
 // Tile (i,j), i >= j:  A_ij <- (A_ij - sum_{k<j} L_ik L_jk^T) [chol | * L_jj^-T], then flag it.
+//
+// The critical path of the factorisation is POTRF(j-1) -> TRSM(j,j-1) -> last SYRK term ->
+// POTRF(j).  With the TRSM in another CTA that path crossed two flag hops and moved the 8 KB tile
+// L(j,j-1) through L2 twice (store + fence + flag, acquire + reload: ~2.4 us per block column).
+// The owner of a DIAGONAL tile therefore builds L(j,j-1) itself: it pre-sums the sub-diagonal
+// tile's earlier terms while waiting (they are final one block column earlier), and once
+// POTRF(j-1) is flagged it runs the same one-warp TRSM on its private copy and feeds the result
+// straight from shared memory into the last SYRK term.  Same operations in the same order as the
+// (j,j-1) task, which still publishes the tile for everybody else: identical bits.
+constexpr int kOwnTrsmMaxNb = 8;
 __device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, int epoch,
                                                double (*sA)[NB + 1], double (*sB)[NB + 1],
-                                               double* sv, double* sred, int slot) {
+                                               double (*sC)[NB + 1], double* sv, double* sred, int slot) {
   const int tid = threadIdx.x;
   const unsigned long long t_begin = a.trace ? gtimer() : 0ull;
   const int ty = tid >> 3, tx = tid & 7;  // micro-tile: rows ty+kTY*x, cols tx+8y
   double acc[kRX][4];
-#pragma unroll
-  for (int x = 0; x < kRX; x++)
-#pragma unroll
-    for (int y = 0; y < 4; y++) acc[x][y] = 0.0;
   // Left-looking sum, software-pipelined: the two tiles of term k+1 are fetched from L2 into
   // registers while term k is multiplied out of shared memory (N = 512: 3.31 -> 2.77 ms).
   constexpr int kLd = NB * NB / 2 / kCholThreads;  // double2 words per thread and tile
   double2 pa[kLd], pb[kLd];
-  auto wait2 = [&](int k) {
-    if (threadIdx.x == 0) {
-      while (ld_acquire(a.flags + i * a.nb + k) != epoch) __nanosleep(32);
-      if (i != j) while (ld_acquire(a.flags + j * a.nb + k) != epoch) __nanosleep(32);
-    }
-    __syncthreads();
-  };
-  auto fetch = [&](int k) {
-    const double* srcA = a.A + (size_t)i * NB * a.Dp + (size_t)k * NB;
-    const double* srcB = a.A + (size_t)j * NB * a.Dp + (size_t)k * NB;
+  // acc = sum_{k < nterms} L(ri,k) L(rj,k)^T
+  auto sum_terms = [&](int ri, int rj, int nterms) {
 #pragma unroll
-    for (int q = 0; q < kLd; q++) {
-      const int idx = tid + q * kCholThreads;
-      const size_t off = (size_t)(idx / (NB / 2)) * a.Dp + (idx % (NB / 2)) * 2;
-      pa[q] = __ldcg(reinterpret_cast<const double2*>(srcA + off));
-      if (i != j) pb[q] = __ldcg(reinterpret_cast<const double2*>(srcB + off));
-    }
-  };
-  if (j > 0) { wait2(0); fetch(0); }
-  for (int k = 0; k < j; k++) {
+    for (int x = 0; x < kRX; x++)
 #pragma unroll
-    for (int q = 0; q < kLd; q++) {
-      const int idx = tid + q * kCholThreads;
-      const int r = idx / (NB / 2), c2 = (idx % (NB / 2)) * 2;
-      sA[r][c2] = pa[q].x; sA[r][c2 + 1] = pa[q].y;
-      if (i != j) { sB[r][c2] = pb[q].x; sB[r][c2 + 1] = pb[q].y; }
-    }
-    __syncthreads();
-    if (k + 1 < j) { wait2(k + 1); fetch(k + 1); }
-    const double (*sR)[NB + 1] = (i != j) ? sB : sA;
+      for (int y = 0; y < 4; y++) acc[x][y] = 0.0;
+    auto wait2 = [&](int k) {
+      if (threadIdx.x == 0) {
+        while (ld_acquire(a.flags + ri * a.nb + k) != epoch) __nanosleep(32);
+        if (ri != rj) while (ld_acquire(a.flags + rj * a.nb + k) != epoch) __nanosleep(32);
+      }
+      __syncthreads();
+    };
+    auto fetch = [&](int k) {
+      const double* srcA = a.A + (size_t)ri * NB * a.Dp + (size_t)k * NB;
+      const double* srcB = a.A + (size_t)rj * NB * a.Dp + (size_t)k * NB;
+#pragma unroll
+      for (int q = 0; q < kLd; q++) {
+        const int idx = tid + q * kCholThreads;
+        const size_t off = (size_t)(idx / (NB / 2)) * a.Dp + (idx % (NB / 2)) * 2;
+        pa[q] = __ldcg(reinterpret_cast<const double2*>(srcA + off));
+        if (ri != rj) pb[q] = __ldcg(reinterpret_cast<const double2*>(srcB + off));
+      }
+    };
+    if (nterms > 0) { wait2(0); fetch(0); }
+    for (int k = 0; k < nterms; k++) {
+#pragma unroll
+      for (int q = 0; q < kLd; q++) {
+        const int idx = tid + q * kCholThreads;
+        const int r = idx / (NB / 2), c2 = (idx % (NB / 2)) * 2;
+        sA[r][c2] = pa[q].x; sA[r][c2 + 1] = pa[q].y;
+        if (ri != rj) { sB[r][c2] = pb[q].x; sB[r][c2 + 1] = pb[q].y; }
+      }
+      __syncthreads();
+      if (k + 1 < nterms) { wait2(k + 1); fetch(k + 1); }
+      const double (*sR)[NB + 1] = (ri != rj) ? sB : sA;
 #pragma unroll 8
-    for (int m = 0; m < NB; m++) {
+      for (int m = 0; m < NB; m++) {
+        double li[kRX], lj[4];
+#pragma unroll
+        for (int x = 0; x < kRX; x++) li[x] = sA[ty + kTY * x][m];
+#pragma unroll
+        for (int y = 0; y < 4; y++) lj[y] = sR[tx + 8 * y][m];
+#pragma unroll
+        for (int x = 0; x < kRX; x++)
+#pragma unroll
+          for (int y = 0; y < 4; y++) acc[x][y] = fma(li[x], lj[y], acc[x][y]);
+      }
+      __syncthreads();
+    }
+  };
+  const TilePad tA{&sA[0][0]}, tB{&sB[0][0]}, tC{&sC[0][0]};
+  // diagonal owner builds L(j,j-1) privately — small systems only: the private pre-sum has j-1
+  // terms, which the diagonal CTA runs back to back with its own j-1 SYRK terms; at nb = 14 that
+  // already cancels the gain (calib N = 64: 1121 -> 1112 iters/s) and at nb = 112 it doubles the
+  // longest tasks (N = 512: 14.6 -> 17.8 ms per iteration)
+  const bool own_trsm = (i == j) && j > 0 && a.nb <= kOwnTrsmMaxNb;
+  if (own_trsm) {
+    sum_terms(j, j - 1, j - 1);  // earlier terms of the sub-diagonal tile (j, j-1)
+    const double* src = a.A + (size_t)j * NB * a.Dp + (size_t)(j - 1) * NB;
+#pragma unroll
+    for (int x = 0; x < kRX; x++)
+#pragma unroll
+      for (int y = 0; y < 4; y++) {
+        const int r = ty + kTY * x, c = tx + 8 * y;
+        sC[r][c] = __ldcg(src + (size_t)r * a.Dp + c) - acc[x][y];
+      }
+    __syncthreads();
+  }
+  sum_terms(i, j, own_trsm ? j - 1 : j);
+  unsigned long long t_ready = a.trace ? gtimer() : 0ull;
+  if (own_trsm) {
+    wait_flag(a.flags + (j - 1) * a.nb + (j - 1), epoch);  // POTRF(j-1)
+    if (a.trace) t_ready = gtimer();
+    load_tile(a.A, a.Dp, j - 1, j - 1, sB);
+    if (tid < NB) sv[tid] = __ldcg(a.x + a.Dp + (j - 1) * NB + tid);
+    __syncthreads();
+    if (tid < 32) trsm_warp(tC, tB, sv);
+    __syncthreads();
+#pragma unroll 8
+    for (int m = 0; m < NB; m++) {  // the last SYRK term, L(j,j-1) L(j,j-1)^T, from shared memory
       double li[kRX], lj[4];
 #pragma unroll
-      for (int x = 0; x < kRX; x++) li[x] = sA[ty + kTY * x][m];
+      for (int x = 0; x < kRX; x++) li[x] = sC[ty + kTY * x][m];
 #pragma unroll
-      for (int y = 0; y < 4; y++) lj[y] = sR[tx + 8 * y][m];
+      for (int y = 0; y < 4; y++) lj[y] = sC[tx + 8 * y][m];
 #pragma unroll
       for (int x = 0; x < kRX; x++)
 #pragma unroll
         for (int y = 0; y < 4; y++) acc[x][y] = fma(li[x], lj[y], acc[x][y]);
     }
-    __syncthreads();
   }
   // own tile (assembled by the previous launch; nobody else touches it before the flag)
   double* dst = a.A + (size_t)i * NB * a.Dp + (size_t)j * NB;
@@ -431,8 +485,7 @@ __device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, 
       sA[r][c] = __ldcg(dst + (size_t)r * a.Dp + c) - acc[x][y];
     }
   __syncthreads();
-  unsigned long long t_ready = a.trace ? gtimer() : 0ull;
-  const TilePad tA{&sA[0][0]}, tB{&sB[0][0]};
+  if (!own_trsm && a.trace) t_ready = gtimer();
   if (i == j) {
     potrf_team(tA, tid >> 5, j * NB, a.D, a.x + a.Dp + j * NB, a.hdr, [] { __syncthreads(); });
   } else {
@@ -629,6 +682,7 @@ chol_dataflow_kernel(const CholArgs a) {
   if (a.hdr->done) return;
   __shared__ double sA[NB][NB + 1];
   __shared__ double sB[NB][NB + 1];
+  __shared__ double sC[NB][NB + 1];
   __shared__ double sv[2 * NB], sred[(kCholThreads / 32) * NB];
   __shared__ float red[kCholThreads / 32];
   const int epoch = a.hdr->iters + 1;
@@ -638,7 +692,7 @@ chol_dataflow_kernel(const CholArgs a) {
   int t = 0;
   for (int j = 0; j < a.nb; j++)
     for (int i = j; i < a.nb; i++, t++)
-      if (t % G == cta) chol_tile_task(a, i, j, epoch, sA, sB, sv, sred, t);
+      if (t % G == cta) chol_tile_task(a, i, j, epoch, sA, sB, sC, sv, sred, t);
   if (a.nb <= kBackSingleMax) {  // small system: the owner of the last diagonal tile finishes alone
     if ((t - 1) % G == cta) {
       chol_back_all(a, sA, &sB[0][0], sred, t);
