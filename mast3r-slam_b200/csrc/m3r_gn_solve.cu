@@ -328,46 +328,14 @@ __device__ __forceinline__ void potrf_team(const Tile s, int w, int g0, int D, d
   }
 }
 
-// X <- X * Ljj^-T for the 32x32 tile X by ONE warp: lane r solves row r (rows are independent:
-// no barrier at all); Ljj and 1/diag are broadcast reads.  Four columns per trip: the part
-// against finished columns is a load-only loop, the 4x4 triangle is solved in registers.
-template <class Tile>
-__device__ __forceinline__ void trsm_warp(const Tile sx, const Tile sl, const double* __restrict__ dinv) {
-  const int r = threadIdx.x & 31;
-#pragma unroll 1
-  for (int c0 = 0; c0 < NB; c0 += 4) {
-    double a[4];
-#pragma unroll
-    for (int j = 0; j < 4; j++) a[j] = sx(r, c0 + j);
-#pragma unroll 4
-    for (int m = 0; m < c0; m++) {
-      const double xm = sx(r, m);
-#pragma unroll
-      for (int j = 0; j < 4; j++) a[j] = fma(-xm, sl(c0 + j, m), a[j]);
-    }
-    double l[4][4];
-#pragma unroll
-    for (int j = 1; j < 4; j++)
-#pragma unroll
-      for (int k = 0; k < j; k++) l[j][k] = sl(c0 + j, c0 + k);
-#pragma unroll
-    for (int j = 0; j < 4; j++) {
-#pragma unroll
-      for (int k = 0; k < j; k++) a[j] = fma(-a[k], l[j][k], a[j]);
-      a[j] *= dinv[c0 + j];
-    }
-#pragma unroll
-    for (int j = 0; j < 4; j++) sx(r, c0 + j) = a[j];
-  }
-}
-
-// The same solve by the whole 4-warp team, right-looking in blocks of four columns: lane r of
-// every warp holds row r; warp w owns column blocks w and w+4 (8 columns) in registers.  Per block:
-// its owner solves the 4x4 triangle and writes the four finished columns, one barrier, then every
-// warp applies the rank-4 update to the blocks it still owns.  The sequence of fma's that reaches
-// each element is the one of trsm_warp (finished columns in ascending order, then the triangle),
-// so the result has the same bits — in a quarter of the time: the one-warp form was a chain of
-// 112 x (5 shared-memory loads + 4 fma) per lane, 4.2 us of every block column's critical path.
+// X <- X * Ljj^-T for the 32x32 tile X by the 4-warp team (rows are independent), right-looking in
+// blocks of four columns: lane r of every warp holds row r; warp w owns column blocks w and w+4
+// (8 columns) in registers.  Per block: its owner solves the 4x4 triangle and writes the four
+// finished columns, one barrier, then every warp applies the rank-4 update to the blocks it still
+// owns.  Each element sees its fma's in the order of a plain forward substitution (finished
+// columns ascending, then the triangle), so the bits equal those of the earlier one-warp,
+// barrier-free form — whose chain of 112 x (5 shared-memory loads + 4 fma) per lane cost 4.2 us
+// of every block column's critical path; this one takes 1.2 us.
 template <class Tile, class Sync>
 __device__ __forceinline__ void trsm_team(const Tile sx, const Tile sl, const double* __restrict__ dinv, int w,
                                           Sync sync) {
@@ -421,7 +389,7 @@ __device__ __forceinline__ void trsm_team(const Tile sx, const Tile sl, const do
 // L(j,j-1) through L2 twice (store + fence + flag, acquire + reload: ~2.4 us per block column).
 // The owner of a DIAGONAL tile therefore builds L(j,j-1) itself: it pre-sums the sub-diagonal
 // tile's earlier terms while waiting (they are final one block column earlier), and once
-// POTRF(j-1) is flagged it runs the same one-warp TRSM on its private copy and feeds the result
+// POTRF(j-1) is flagged it runs the same TRSM on its private copy and feeds the result
 // straight from shared memory into the last SYRK term.  Same operations in the same order as the
 // (j,j-1) task, which still publishes the tile for everybody else: identical bits.
 constexpr int kOwnTrsmMaxNb = 8;
