@@ -242,6 +242,11 @@ double* m3r_gn_blocks(void* workspace, int num_poses, int num_edges, int local_e
  * its tile tasks (4 x u64 per task: {kind<<32 | i<<16 | j, t_begin, t_inputs_ready, t_end},
  * globaltimer ns) into device_buf (capacity_tasks entries).  NULL switches it off (default). */
 void m3r_debug_chol_trace(unsigned long long* device_buf, int capacity_tasks);
+/* Diagnostics: every later m3r_gn_solve_step stalls some tile tasks of the dataflow Cholesky for
+ * delay_us microseconds before they start — which = 1: owners of diagonal tiles (j > 0),
+ * which = 2: owners of off-diagonal tiles.  The flag protocol must make the result independent
+ * of such delays (tests/test_gpu_gn.py).  delay_us <= 0 switches it off (default). */
+void m3r_debug_chol_delay(int delay_us, int which);
 
 /* ------------------------------------------------------------------------- *
  * Two-frame tracker solve

@@ -177,6 +177,7 @@ __device__ __forceinline__ void post_flag(int* f, int epoch) {
 // task 4 x u64 = {kind<<32 | i<<16 | j, t_begin, t_inputs_ready, t_end} in globaltimer ns.
 static unsigned long long* g_chol_trace = nullptr;
 static int g_chol_trace_cap = 0;
+static int g_chol_delay_us = 0, g_chol_delay_which = 0;
 __device__ __forceinline__ unsigned long long gtimer() {
   unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t;
 }
@@ -188,6 +189,7 @@ struct CholArgs {
   float* Twc; float* dx; int N; float delta_thresh;
   GnHeader* hdr;
   unsigned long long* trace; int trace_cap;
+  int delay_us, delay_which;  // diagnostics (m3r_debug_chol_delay): stall some tasks before they start
 };
 
 __device__ __forceinline__ void trace_put(const CholArgs& a, int slot, int kind, int i, int j,
@@ -392,11 +394,27 @@ __device__ __forceinline__ void trsm_team(const Tile sx, const Tile sl, const do
 // POTRF(j-1) is flagged it runs the same TRSM on its private copy and feeds the result
 // straight from shared memory into the last SYRK term.  Same operations in the same order as the
 // (j,j-1) task, which still publishes the tile for everybody else: identical bits.
+//
+// That task overwrites H(j,j-1) with L(j,j-1) IN PLACE, and the diagonal owner needs the
+// original: the owner therefore raises flags[(j-1)*nb + j] (the unused upper-triangle mirror
+// of the tile's own flag) once its copy is in shared memory, and the (j,j-1) task waits for it
+// before it stores.  Without it the order was only a matter of timing (the owner reads ~6 us
+// before the store in an undisturbed run; a CTA delayed by 15 us read the factored tile and
+// solved it a second time).  Needs one task per CTA: a CTA owning both tiles would wait for
+// itself.
 constexpr int kOwnTrsmMaxNb = 8;
+__device__ __forceinline__ bool chol_own_trsm(const CholArgs& a) {
+  return a.nb <= kOwnTrsmMaxNb && a.nb * (a.nb + 1) / 2 <= (int)gridDim.x;
+}
 __device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, int epoch,
                                                double (*sA)[NB + 1], double (*sB)[NB + 1],
                                                double (*sC)[NB + 1], double* sv, double* sred, int slot) {
   const int tid = threadIdx.x;
+  if (a.delay_us > 0 && ((i == j && j > 0) ? 1 : (i != j ? 2 : 0)) == a.delay_which) {
+    // protocol test: the result must not depend on when a CTA gets to its task
+    const unsigned long long until = gtimer() + 1000ull * (unsigned long long)a.delay_us;
+    while (gtimer() < until) __nanosleep(200);
+  }
   const unsigned long long t_begin = a.trace ? gtimer() : 0ull;
   const int ty = tid >> 3, tx = tid & 7;  // micro-tile: rows ty+kTY*x, cols tx+8y
   double acc[kRX][4];
@@ -460,7 +478,7 @@ __device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, 
   // terms, which the diagonal CTA runs back to back with its own j-1 SYRK terms; at nb = 14 that
   // already cancels the gain (calib N = 64: 1121 -> 1112 iters/s) and at nb = 112 it doubles the
   // longest tasks (N = 512: 14.6 -> 17.8 ms per iteration)
-  const bool own_trsm = (i == j) && j > 0 && a.nb <= kOwnTrsmMaxNb;
+  const bool own_trsm = (i == j) && j > 0 && chol_own_trsm(a);
   if (own_trsm) {
     sum_terms(j, j - 1, j - 1);  // earlier terms of the sub-diagonal tile (j, j-1)
     const double* src = a.A + (size_t)j * NB * a.Dp + (size_t)(j - 1) * NB;
@@ -471,7 +489,7 @@ __device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, 
         const int r = ty + kTY * x, c = tx + 8 * y;
         sC[r][c] = __ldcg(src + (size_t)r * a.Dp + c) - acc[x][y];
       }
-    __syncthreads();
+    post_flag(a.flags + (j - 1) * a.nb + j, epoch);  // H(j,j-1) consumed: its owner may overwrite it
   }
   sum_terms(i, j, own_trsm ? j - 1 : j);
   unsigned long long t_ready = a.trace ? gtimer() : 0ull;
@@ -515,6 +533,7 @@ __device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, 
     if (tid < NB) sv[tid] = __ldcg(a.x + a.Dp + j * NB + tid);
     __syncthreads();
     trsm_team(tA, tB, sv, tid >> 5, [] { __syncthreads(); });
+    if (i == j + 1 && chol_own_trsm(a)) wait_flag(a.flags + j * a.nb + i, epoch);  // see kOwnTrsmMaxNb
   }
   __syncthreads();
   for (int idx = tid; idx < NB * NB; idx += kCholThreads) {
@@ -572,7 +591,8 @@ __device__ __forceinline__ void chol_back_task(const CholArgs& a, int c, int epo
 }
 
 // Back substitution of a small system (nb <= kBackSingleMax) by ONE CTA — the one that factored
-// the last diagonal tile, so every tile is final and nothing is waited for.  The distributed
+// the last diagonal tile, so every tile is final (the caller waits for the one exception) and
+// nothing is waited for inside.  The distributed
 // form above costs a flag hop, an L2 round trip for x_m and a fence per block column (3.7 us
 // each); here x stays in shared memory and the L tiles of a block column are fetched four at a
 // time (32 independent loads per thread in flight).
@@ -715,6 +735,9 @@ chol_dataflow_kernel(const CholArgs a) {
       if (t % G == cta) chol_tile_task(a, i, j, epoch, sA, sB, sC, sv, sred, t);
   if (a.nb <= kBackSingleMax) {  // small system: the owner of the last diagonal tile finishes alone
     if ((t - 1) % G == cta) {
+      // every tile is final once the last diagonal tile is — except, with the private TRSM, the
+      // tile left of it, which this CTA rebuilt for itself instead of waiting for its owner
+      if (a.nb > 1 && chol_own_trsm(a)) wait_flag(a.flags + (a.nb - 1) * a.nb + (a.nb - 2), epoch);
       chol_back_all(a, sA, &sB[0][0], sred, t);
       gn_update_block(a.Twc, a.x, a.N, a.D, a.delta_thresh, a.dx, a.hdr, red, kCholThreads, threadIdx.x,
                       [] { __syncthreads(); });
@@ -787,6 +810,7 @@ int gn_solve_launch(float* Twc, const double* blocks, int N, int M, float delta_
   a.x = ws_ptr<double>(ws, L.x);
   a.Twc = Twc; a.dx = dx; a.N = N; a.delta_thresh = delta_thresh; a.hdr = hdr;
   a.trace = g_chol_trace; a.trace_cap = g_chol_trace_cap;
+  a.delay_us = g_chol_delay_us; a.delay_which = g_chol_delay_which;
   const int tiles = nb * (nb + 1) / 2;
   int grid = chol_max_ctas();
   if (grid > tiles) grid = tiles;
@@ -804,6 +828,11 @@ using namespace m3r;
 extern "C" void m3r_debug_chol_trace(unsigned long long* device_buf, int capacity_tasks) {
   g_chol_trace = device_buf;
   g_chol_trace_cap = device_buf ? capacity_tasks : 0;
+}
+
+extern "C" void m3r_debug_chol_delay(int delay_us, int which) {
+  g_chol_delay_us = delay_us > 0 ? delay_us : 0;
+  g_chol_delay_which = which;
 }
 
 extern "C" int m3r_pose_retr(float* poses, const float* dx, int num_poses, int num_fix,

@@ -60,7 +60,7 @@ EXPORTS = [
     "m3r_match_iter_proj_fused", "m3r_match_refine_fused", "m3r_pose_retr",
     "m3r_gn_workspace_bytes", "m3r_gauss_newton", "m3r_gn_prepare", "m3r_gn_accumulate",
     "m3r_gn_solve_step", "m3r_gn_done_flag", "m3r_gn_blocks", "m3r_track_workspace_bytes",
-    "m3r_track_ray_dist", "m3r_track_calib", "m3r_debug_chol_trace", "m3r_edge_build", "m3r_pointmap_update", "m3r_gn_accumulate_p2p", "m3r_gn_solve_step_p2p",
+    "m3r_track_ray_dist", "m3r_track_calib", "m3r_debug_chol_trace", "m3r_debug_chol_delay", "m3r_edge_build", "m3r_pointmap_update", "m3r_gn_accumulate_p2p", "m3r_gn_solve_step_p2p",
     "m3r_match_prep_packed", "m3r_match_iter_proj_packed",
     "m3r_render_default_opts", "m3r_render_clear", "m3r_render_surfels", "m3r_render_triangles",
     "m3r_render_resolve",
@@ -102,6 +102,8 @@ def _load():
     lib.m3r_gn_blocks.argtypes = [vp, i32, i32, i32, i32]
     lib.m3r_debug_chol_trace.argtypes = [vp, i32]
     lib.m3r_debug_chol_trace.restype = None
+    lib.m3r_debug_chol_delay.argtypes = [i32, i32]
+    lib.m3r_debug_chol_delay.restype = None
     lib.m3r_track_workspace_bytes.restype = sz
     lib.m3r_track_workspace_bytes.argtypes = [i32]
     lib.m3r_track_ray_dist.argtypes = [vp, vp, vp, vp, i32, f32, f32, f32, i32, f32, f32, vp, vp,

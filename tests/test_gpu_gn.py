@@ -182,6 +182,32 @@ def test_rays_full_size_vs_reference_and_properties(backends, ref_ext):
     assert torch.equal(Ta, Tb)
 
 
+@pytest.mark.parametrize("N", [8, 32, 40, 150])
+def test_cholesky_independent_of_cta_timing(backends, N):
+    """The tile-dataflow Cholesky hands tiles between CTAs through flags only.  Stalling the owners
+    of the diagonal tiles (which = 1) or of the off-diagonal tiles (which = 2) for 40 us before
+    they start must leave every bit of dx and of the poses unchanged (N = 8, 32: private TRSM of
+    the diagonal owners, whose source tile another CTA overwrites in place; N = 40: plain form; N = 150: distributed back substitution)."""
+    g = synth.make_graph(N=N, counts={1: None, 2: N - 2, "random": 2}, H=48, W=64, seed=1250 + N, device=DEV)
+
+    def solve():
+        T = g["Twc"].clone()
+        (dx,) = backends.gauss_newton_rays(T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
+                                           0.003, 10.0, 0.0, 1.5, 3, 0.0)
+        torch.cuda.synchronize()
+        return dx, T
+
+    dx0, T0 = solve()
+    assert torch.isfinite(dx0).all() and float(dx0.abs().max()) > 0
+    try:
+        for which in (1, 2):
+            backends._lib.m3r_debug_chol_delay(40, which)
+            dx1, T1 = solve()
+            assert torch.equal(dx0, dx1) and torch.equal(T0, T1), f"which={which}"
+    finally:
+        backends._lib.m3r_debug_chol_delay(0, 0)
+
+
 @pytest.mark.parametrize("N", [40, 150, 260])
 def test_many_keyframes_dense_cholesky(backends, orc, N):
     """Graphs whose normal equations span many 32x32 tiles (N=40: 9x9 tiles, single-CTA back
