@@ -6,7 +6,6 @@ numpy restatements; (3) known-answer cases."""
 import os
 
 import numpy as np
-import pytest
 
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
 

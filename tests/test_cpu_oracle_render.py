@@ -5,7 +5,6 @@ tests pin the oracle to closed forms of the shader source instead (surfelmap.gls
 import math
 
 import numpy as np
-import pytest
 
 from oracle import render as R
 
