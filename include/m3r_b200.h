@@ -244,8 +244,10 @@ double* m3r_gn_blocks(void* workspace, int num_poses, int num_edges, int local_e
 void m3r_debug_chol_trace(unsigned long long* device_buf, int capacity_tasks);
 /* Diagnostics: every later m3r_gn_solve_step stalls some tile tasks of the dataflow Cholesky for
  * delay_us microseconds before they start — which = 1: owners of diagonal tiles (j > 0),
- * which = 2: owners of off-diagonal tiles.  The flag protocol must make the result independent
- * of such delays (tests/test_gpu_gn.py).  delay_us <= 0 switches it off (default). */
+ * which = 2: owners of off-diagonal tiles; which >= 3: every task, for a pseudo-random
+ * 0..delay_us (seeded by `which`) before it starts and again before it stores its tile.  The flag
+ * protocol must make the result independent of such delays (tests/test_gpu_gn.py).
+ * delay_us <= 0 switches it off (default). */
 void m3r_debug_chol_delay(int delay_us, int which);
 
 /* ------------------------------------------------------------------------- *

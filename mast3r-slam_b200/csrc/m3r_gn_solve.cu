@@ -384,6 +384,26 @@ __device__ __forceinline__ void trsm_team(const Tile sx, const Tile sl, const do
   }
 }
 
+// Protocol test (m3r_debug_chol_delay): the result must not depend on when a CTA gets to a task
+// or how long it takes.  which = 1 / 2: diagonal (j > 0) / off-diagonal owners wait delay_us
+// before they start; which >= 3: every task waits a pseudo-random 0..delay_us (a hash of the
+// tile, the iteration, the stall point and `which` as the seed) before it starts and again
+// before it stores its tile.
+__device__ __forceinline__ void chol_debug_stall(const CholArgs& a, int i, int j, int epoch, int point) {
+  if (a.delay_us <= 0) return;
+  unsigned long long ns = 1000ull * (unsigned long long)a.delay_us;
+  if (a.delay_which >= 3) {
+    unsigned h = (unsigned)(i * 73856093) ^ (unsigned)(j * 19349663) ^ (unsigned)(epoch * 83492791) ^
+                 (unsigned)((2 * a.delay_which + point) * 2654435761u);
+    h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+    ns = ns * (h & 1023u) / 1023u;
+  } else if (point != 0 || ((i == j && j > 0) ? 1 : (i != j ? 2 : 0)) != a.delay_which) {
+    return;
+  }
+  const unsigned long long until = gtimer() + ns;
+  while (gtimer() < until) __nanosleep(200);
+}
+
 // Tile (i,j), i >= j:  A_ij <- (A_ij - sum_{k<j} L_ik L_jk^T) [chol | * L_jj^-T], then flag it.
 //
 // The critical path of the factorisation is POTRF(j-1) -> TRSM(j,j-1) -> last SYRK term ->
@@ -410,11 +430,7 @@ __device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, 
                                                double (*sA)[NB + 1], double (*sB)[NB + 1],
                                                double (*sC)[NB + 1], double* sv, double* sred, int slot) {
   const int tid = threadIdx.x;
-  if (a.delay_us > 0 && ((i == j && j > 0) ? 1 : (i != j ? 2 : 0)) == a.delay_which) {
-    // protocol test: the result must not depend on when a CTA gets to its task
-    const unsigned long long until = gtimer() + 1000ull * (unsigned long long)a.delay_us;
-    while (gtimer() < until) __nanosleep(200);
-  }
+  chol_debug_stall(a, i, j, epoch, 0);
   const unsigned long long t_begin = a.trace ? gtimer() : 0ull;
   const int ty = tid >> 3, tx = tid & 7;  // micro-tile: rows ty+kTY*x, cols tx+8y
   double acc[kRX][4];
@@ -536,6 +552,7 @@ __device__ __forceinline__ void chol_tile_task(const CholArgs& a, int i, int j, 
     if (i == j + 1 && chol_own_trsm(a)) wait_flag(a.flags + j * a.nb + i, epoch);  // see kOwnTrsmMaxNb
   }
   __syncthreads();
+  chol_debug_stall(a, i, j, epoch, 1);
   for (int idx = tid; idx < NB * NB; idx += kCholThreads) {
     const int r = idx / NB, c = idx % NB;
     dst[(size_t)r * a.Dp + c] = sA[r][c];

@@ -186,7 +186,8 @@ def test_rays_full_size_vs_reference_and_properties(backends, ref_ext):
 def test_cholesky_independent_of_cta_timing(backends, N):
     """The tile-dataflow Cholesky hands tiles between CTAs through flags only.  Stalling the owners
     of the diagonal tiles (which = 1) or of the off-diagonal tiles (which = 2) for 40 us before
-    they start must leave every bit of dx and of the poses unchanged (N = 8, 32: private TRSM of
+    they start, or every task for a random time before it starts and before it stores
+    (which >= 3), must leave every bit of dx and of the poses unchanged (N = 8, 32: private TRSM of
     the diagonal owners, whose source tile another CTA overwrites in place; N = 40: plain form; N = 150: distributed back substitution)."""
     g = synth.make_graph(N=N, counts={1: None, 2: N - 2, "random": 2}, H=48, W=64, seed=1250 + N, device=DEV)
 
@@ -200,8 +201,8 @@ def test_cholesky_independent_of_cta_timing(backends, N):
     dx0, T0 = solve()
     assert torch.isfinite(dx0).all() and float(dx0.abs().max()) > 0
     try:
-        for which in (1, 2):
-            backends._lib.m3r_debug_chol_delay(40, which)
+        for which, us in ((1, 40), (2, 40), (3, 20), (4, 20), (5, 60)):  # >= 3: random per task, seed = which
+            backends._lib.m3r_debug_chol_delay(us, which)
             dx1, T1 = solve()
             assert torch.equal(dx0, dx1) and torch.equal(T0, T1), f"which={which}"
     finally:
