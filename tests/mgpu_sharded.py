@@ -42,6 +42,25 @@ for N, H, W, mode in ((9, 48, 64, "rays"), (6, 96, 128, "calib"), (3, 24, 32, "r
             print(f"rank {rank}: N={N} {mode} p2p={p2p} same={same} moved={moved} "
                   f"maxdiff={float((T - T1).abs().max()):.3e}", flush=True)
             ok = False
+    # skewed ranks: in every iteration a different rank reaches its accumulation ~300 us late and another
+    # one its solve step, so fast ranks push iteration k+1 into the peers' buffers while slow ones still
+    # assemble iteration k (the two-buffer / epoch protocol of PeerBlocks must absorb that)
+    peers = be.PeerBlocks.get(g["M"], dev)
+    for pattern in range(2):
+        T = g["Twc"].clone()
+        s = be.GNSolver(prm, T, g["Xs"], g["Cs"], g["ii"], g["jj"], loc[0], loc[1], loc[2], e0, peers=peers)
+        for it in range(6):
+            if (rank + it + pattern) % world == 0:
+                torch.cuda._sleep(600_000)
+            s.accumulate()
+            if (rank + it + pattern) % world == world - 1:
+                torch.cuda._sleep(600_000)
+            s.solve_step(0.0)
+        torch.cuda.synchronize()
+        if not torch.equal(T, T1):
+            print(f"rank {rank}: N={N} {mode} skewed p2p pattern {pattern}: maxdiff={float((T - T1).abs().max()):.3e}",
+                  flush=True)
+            ok = False
 flag = torch.tensor([1 if ok else 0], device=dev)
 dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 if int(flag.item()) == 1:
