@@ -112,6 +112,14 @@ int m3r_match_iter_proj_fused(const float* rays_img_with_grad, const float* X11,
                               float cost_thresh, float dist_thresh, int64_t* p1,
                               uint8_t* valid, float* p_new, m3r_stream_t stream);
 
+/* image.img_gradient (mast3r_slam/image.py:5-38) on its own: reflect-padded depthwise 3x3
+ * gradients (1/32)[[-3,0,3],[-10,0,10],[-3,0,3]] and its transpose of img (planes,H,W) f32,
+ * planes = batch*channels, into gx, gy of the same shape.  H, W >= 2; planes <= 65535.
+ * (match_prep computes the same taps fused with the normalisation; this entry serves callers
+ * of img_gradient itself.) */
+int m3r_img_gradient(const float* img, int planes, int H, int W, float* gx, float* gy,
+                     m3r_stream_t stream);
+
 /* The same two steps over the PRIVATE float4-packed ray image of the fused pipeline:
  * rays_packed (b,H,W,12) f32, 16-byte aligned = three 16-B words per pixel
  * [ray.xyz, 0 | d(ray)/du.xyz, 0 | d(ray)/dv.xyz, 0], so that a bilinear sample of one group is

@@ -132,9 +132,41 @@ match_prep_kernel(const float* __restrict__ X11, int H, int W, int tiles_x, int 
   }
 }
 
+// image.img_gradient (image.py:5-38) as a function of its own: (planes, H, W) f32 -> gx, gy of the
+// same shape, planes = b*c (the convolution is depthwise, so batch and channel are one index).
+// Same taps and the same order of additions as prep_rays_tile.  One thread per pixel, rows of 32
+// pixels per warp: the nine taps of a warp are three 128-B rows shifted by one element, so L1
+// serves the overlap and HBM sees each element once (12 B per element: 4 in, 8 out).
+__global__ void __launch_bounds__(256)
+img_gradient_kernel(const float* __restrict__ img, int H, int W, float* __restrict__ gx, float* __restrict__ gy) {
+  const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+  if (x >= W || y >= H) return;
+  const float* pl = img + (size_t)blockIdx.z * H * W;
+  const int xm = reflect(x - 1, W), xp = reflect(x + 1, W), ym = reflect(y - 1, H), yp = reflect(y + 1, H);
+  const float* r0 = pl + (size_t)ym * W; const float* r1 = pl + (size_t)y * W; const float* r2 = pl + (size_t)yp * W;
+  const float tl = __ldg(r0 + xm), tc = __ldg(r0 + x), tr = __ldg(r0 + xp);
+  const float ml = __ldg(r1 + xm), mr = __ldg(r1 + xp);
+  const float bl = __ldg(r2 + xm), bc = __ldg(r2 + x), br = __ldg(r2 + xp);
+  const float k3 = 3.0f / 32.0f, k10 = 10.0f / 32.0f;
+  const size_t o = (size_t)blockIdx.z * H * W + (size_t)y * W + x;
+  gx[o] = -k3 * tl + k3 * tr - k10 * ml + k10 * mr - k3 * bl + k3 * br;
+  gy[o] = -k3 * tl - k10 * tc - k3 * tr + k3 * bl + k10 * bc + k3 * br;
+}
+
 }  // namespace m3r
 
 using namespace m3r;
+
+extern "C" int m3r_img_gradient(const float* img, int planes, int H, int W, float* gx, float* gy,
+                                m3r_stream_t stream) {
+  if (planes < 0 || H < 2 || W < 2 || planes > 65535) return M3R_EINVAL;  // reflect padding needs 2 rows / columns
+  if (planes == 0) return M3R_OK;
+  if (!img || !gx || !gy) return M3R_EINVAL;
+  const dim3 grid((W + 31) / 32, (H + 7) / 8, planes);
+  if (grid.y > 65535) return M3R_EINVAL;
+  img_gradient_kernel<<<grid, 256, 0, as_stream(stream)>>>(img, H, W, gx, gy);
+  return after_launch();
+}
 
 template <int CH>
 static int match_prep_launch(const float* X11, const float* D11, int b, int H, int W, int F,

@@ -61,7 +61,7 @@ EXPORTS = [
     "m3r_gn_workspace_bytes", "m3r_gauss_newton", "m3r_gn_prepare", "m3r_gn_accumulate",
     "m3r_gn_solve_step", "m3r_gn_done_flag", "m3r_gn_blocks", "m3r_track_workspace_bytes",
     "m3r_track_ray_dist", "m3r_track_calib", "m3r_debug_chol_trace", "m3r_debug_chol_delay", "m3r_edge_build", "m3r_pointmap_update", "m3r_gn_accumulate_p2p", "m3r_gn_solve_step_p2p",
-    "m3r_match_prep_packed", "m3r_match_iter_proj_packed",
+    "m3r_match_prep_packed", "m3r_match_iter_proj_packed", "m3r_img_gradient",
     "m3r_render_default_opts", "m3r_render_clear", "m3r_render_surfels", "m3r_render_triangles",
     "m3r_render_resolve",
 ]
@@ -85,6 +85,7 @@ def _load():
     lib.m3r_match_iter_proj_fused.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, f32, f32, f32,
                                               vp, vp, vp, vp]
     lib.m3r_match_prep_packed.argtypes = lib.m3r_match_prep.argtypes
+    lib.m3r_img_gradient.argtypes = [vp, i32, i32, i32, vp, vp, vp]
     lib.m3r_match_iter_proj_packed.argtypes = lib.m3r_match_iter_proj_fused.argtypes
     lib.m3r_match_refine_fused.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp]
     lib.m3r_pose_retr.argtypes = [vp, vp, i32, i32, vp]
@@ -220,6 +221,17 @@ def match_prep(X11, D11=None, packed=False):
         fn = _lib.m3r_match_prep_packed if packed else _lib.m3r_match_prep
         _check(fn(_ptr(X11), _ptr(D11), b, H, W, F, _ptr(rays), _ptr(D11h), _stream(X11)), "match_prep")
     return rays, D11h
+
+
+def img_gradient(img):
+    """image.img_gradient (image.py:5-38): img (b,c,h,w) f32 -> (gx, gy) of the same shape."""
+    img = _req(img, "img", torch.float32, 4)
+    b, c, h, w = img.shape
+    with torch.cuda.device(img.device):
+        gx = torch.empty_like(img)
+        gy = torch.empty_like(img)
+        _check(_lib.m3r_img_gradient(_ptr(img), b * c, h, w, _ptr(gx), _ptr(gy), _stream(img)), "img_gradient")
+    return gx, gy
 
 
 def match_iter_proj_fused(rays_img_with_grad, X11, X21, idx_init, max_iter, lambda_init,

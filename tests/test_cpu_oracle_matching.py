@@ -181,3 +181,17 @@ def test_iter_proj_kats(orc):
     # max_iter = 0: clamped init, nothing converged
     p, c = orc.iter_proj(img, img[..., :3].reshape(1, H * W, 3), p0 - 5.0, 0, 1e-8, 1e-6)
     assert np.array_equal(p[..., 0], np.clip(p0[..., 0] - 5, 1, W - 2)) and not c.any()
+
+
+def test_img_gradient_restatement_vs_reference_golden():
+    """oracle.matching.img_gradient against the reference's own image.img_gradient
+    (tests/golden/gen_image_golden.py), including a 2x2 image (reflect padding at its minimum)."""
+    import torch
+
+    from oracle import matching as om
+
+    z = np.load(os.path.join(GOLD, "image_ref.npz"))
+    for name in ("a", "b", "c"):
+        gx, gy = om.img_gradient(torch.from_numpy(z[f"{name}_img"]))
+        assert np.allclose(gx.numpy(), z[f"{name}_gx"], rtol=0, atol=1e-6)
+        assert np.allclose(gy.numpy(), z[f"{name}_gy"], rtol=0, atol=1e-6)

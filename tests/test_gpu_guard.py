@@ -111,6 +111,7 @@ def test_matching_entry_points(backends, monkeypatch):
 
     for packed in (False, True):
         _both(backends, monkeypatch, lambda x, d, p=packed: backends.match_prep(x, d, packed=p), [X11, D11])
+    _both(backends, monkeypatch, lambda x: backends.img_gradient(x), [X11.permute(0, 3, 1, 2).contiguous()])
     rays9, D11h = backends.match_prep(X11, D11)
     rays12, _ = backends.match_prep(X11, None, packed=True)
     pts = torch.nn.functional.normalize(X21.view(b, n, 3), dim=-1).contiguous()

@@ -365,3 +365,36 @@ def test_usage_errors(backends):
         backends.refine_matches(torch.zeros((1, 8, 8, 12), device=DEV).half(),
                                 torch.zeros((1, 4, 12), device=DEV).half(),
                                 torch.zeros((1, 4, 2), device=DEV, dtype=torch.int64), 3, 5)  # F % 8
+
+
+def test_img_gradient_vs_reference_golden_and_oracle(backends):
+    """m3r_img_gradient / mast3r_slam.image.img_gradient against the reference's own outputs
+    (golden) and, at 8 x 3 x 384 x 512, against the CPU restatement.  fp32 sums of six terms in a
+    different order than the library convolution: 2e-6 absolute on gradients of O(1)."""
+    import os
+
+    from mast3r_slam import image as mimg
+    from oracle import matching as om
+
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "image_ref.npz"))
+    for name in ("a", "b", "c"):
+        gx, gy = mimg.img_gradient(torch.from_numpy(z[f"{name}_img"]).to(DEV))
+        torch.cuda.synchronize()
+        assert np.allclose(_np(gx), z[f"{name}_gx"], rtol=0, atol=2e-6), name
+        assert np.allclose(_np(gy), z[f"{name}_gy"], rtol=0, atol=2e-6), name
+    img = torch.randn((8, 3, 384, 512), generator=torch.Generator().manual_seed(9))
+    gx, gy = backends.img_gradient(img.to(DEV))
+    ox, oy = om.img_gradient(img)
+    assert float((gx.cpu() - ox).abs().max()) < 4e-6 and float((gy.cpu() - oy).abs().max()) < 4e-6
+    # linearity and the constant image (size-independent properties)
+    gx2, _ = backends.img_gradient((2.0 * img).to(DEV))
+    assert torch.equal(gx2, 2.0 * gx)
+    cx, cy = backends.img_gradient(torch.full((1, 2, 7, 9), 3.25, device=DEV))
+    assert float(cx.abs().max()) == 0.0 and float(cy.abs().max()) == 0.0
+    # empty batch; a single row cannot be reflect-padded (the reference raises as well)
+    ex, ey = backends.img_gradient(torch.empty((0, 3, 5, 6), device=DEV))
+    assert ex.shape == (0, 3, 5, 6) and ey.shape == (0, 3, 5, 6)
+    with pytest.raises(RuntimeError):
+        backends.img_gradient(torch.zeros((1, 1, 1, 8), device=DEV))
+    with pytest.raises(RuntimeError):
+        backends.img_gradient(img)  # CPU tensor: no CPU path
