@@ -164,7 +164,22 @@ typedef struct m3r_gn_params {
   float fx, fy, cx, cy; /* K[0][0], K[1][1], K[0][2], K[1][2]  (gn_kernels.cu:1274-1279) */
   int height, width, pixel_border;
   float z_eps;
+  /* calib only: when non-NULL, a DEVICE pointer to K (3,3) f32 row-major; the kernels read
+   * fx, fy, cx, cy from it (as the reference does, gn_kernels.cu:1274-1279) and the four host
+   * fields above are ignored — the caller never copies K to the host. */
+  const float* K_dev;
 } m3r_gn_params;
+
+/* One correspondence of a directed edge in the PACKED layout FactorGraph stores
+ * (SURVEY 8(f)-3): 8 bytes instead of the reference's idx i64 + valid u8 + Q f32 = 13.
+ *   idx : match index into the other keyframe's pointmap (kept as given, also when invalid)
+ *   q   : valid_match ? Q : -Q   (Q = sqrt(Q_src[idx] * Q_dst) >= 0, so the sign bit IS
+ *         valid_match; -0.0f encodes an invalid match with Q == 0)
+ * m3r_edge_pack / m3r_edge_unpack convert losslessly to and from the reference's three tensors. */
+typedef struct m3r_packed_match {
+  int32_t idx;
+  float q;
+} m3r_packed_match;
 
 /* Bytes of caller-provided scratch needed by the m3r_gn_* calls for a graph with
  * num_poses keyframes, num_edges directed edges (of which at most local_edges are
@@ -217,6 +232,33 @@ int m3r_gn_accumulate(const m3r_gn_params* prm, const float* Twc,
 int m3r_gn_solve_step(float* Twc, const double* blocks, int num_poses, int num_edges,
                       float delta_thresh, float* dx, void* workspace,
                       size_t workspace_bytes, m3r_stream_t stream);
+
+/* The same loop over PACKED edge records held in up to two row blocks: edge e < split is row e of
+ * pk0, edge e >= split row e - split of pk1 (each row n records).  FactorGraph keeps the forward
+ * and the reverse direction of its E undirected edges in two blocks, so
+ *   m3r_gauss_newton_packed(.., ii, jj, two_way = 1, fwd, rev, split = E, .., num_edges = 2E, ..)
+ * is solve_GN_rays / solve_GN_calib (global_opt.py:112-213) WITHOUT prep_two_way_edges'
+ * five concatenations (global_opt.py:104-110): with two_way != 0, ii / jj hold the E undirected
+ * edges and the directed list [ii;jj] -> [jj;ii] is formed inside the index kernel.
+ * 24 B streamed + 16 B gathered = 40 B per (directed edge, point) instead of 45; arithmetic and
+ * reduction order equal the reference-layout path, so blocks, dx and poses are bit-identical.
+ * m3r_gn_accumulate_packed: as m3r_gn_accumulate with pk0 / pk1 / split addressing the LOCAL slice
+ * (row 0 = edge `edge_begin`); peers != NULL selects the peer-memory exchange (then `blocks` is
+ * ignored, as in m3r_gn_accumulate_p2p). */
+int m3r_gn_prepare_two_way(const float* Xs, const float* Cs, const int64_t* ii, const int64_t* jj,
+                           int num_poses, int n, int num_edges, int local_edges, void* workspace,
+                           size_t workspace_bytes, m3r_stream_t stream);
+struct m3r_gn_peers;
+int m3r_gn_accumulate_packed(const m3r_gn_params* prm, const float* Twc,
+                             const m3r_packed_match* pk0, const m3r_packed_match* pk1, int split,
+                             int num_poses, int n, int num_edges, int edge_begin, int edge_count,
+                             double* blocks, const struct m3r_gn_peers* peers, void* workspace,
+                             size_t workspace_bytes, m3r_stream_t stream);
+int m3r_gauss_newton_packed(const m3r_gn_params* prm, float* Twc, const float* Xs, const float* Cs,
+                            const int64_t* ii, const int64_t* jj, int two_way,
+                            const m3r_packed_match* pk0, const m3r_packed_match* pk1, int split,
+                            int num_poses, int n, int num_edges, int max_iter, float delta_thresh,
+                            float* dx, void* workspace, size_t workspace_bytes, m3r_stream_t stream);
 /* Edge-sharded solve with the block exchange FUSED into the kernels over NVLink peer memory
  * (no collective call): every process maps every other process's `blocks` buffer and a small
  * int32 flag array (CUDA peer / symmetric memory; torch.distributed._symmetric_memory in the
@@ -243,6 +285,12 @@ int m3r_gn_solve_step_p2p(float* Twc, const m3r_gn_peers* peers, int num_poses, 
                           size_t workspace_bytes, m3r_stream_t stream);
 /* Device pointer (inside workspace) of the int32 convergence flag: 0 running, 1 done. */
 int* m3r_gn_done_flag(void* workspace);
+/* Device pointer (inside workspace) of the solve's status words, int32[4]:
+ *   [0] done (|dx| < delta_thresh reached), [1] the last factorisation failed (zero step),
+ *   [2] iterations executed, [3] peer_timeout: a peer's blocks did not arrive within ~10 s in a
+ *   peer-memory exchange — that step was zero, `done` was NOT set and every later launch of the
+ *   solve was a no-op; the caller must treat the solve as failed (the Python binding raises). */
+int* m3r_gn_status(void* workspace);
 /* Device pointer (inside workspace) of the per-edge block buffer (num_edges*56 doubles). */
 double* m3r_gn_blocks(void* workspace, int num_poses, int num_edges, int local_edges, int n);
 
@@ -282,10 +330,11 @@ int m3r_track_ray_dist(const float* Xf, const float* Xk, const float* Qk,
  * valid & valid_meas_k & (pixel_border < u < width-1-pixel_border, same for v) & (z > z_eps).
  *   Xf (n,3) f32: the frame's points, already gathered by the match index and ray-constrained ;
  *   meas_k (n,3) f32 = [u_k, v_k, log z_k] and valid_meas_k (n,1) u8 as built by
- *   FrameTracker.get_points_poses (tracker.py:143-152) ; everything else as above. */
+ *   FrameTracker.get_points_poses (tracker.py:143-152) ; K_dev (3,3) f32 row-major on the DEVICE
+ *   (the reference keeps K on the device; nothing is read back) ; everything else as above. */
 int m3r_track_calib(const float* Xf, const float* meas_k, const float* Qk,
-                    const uint8_t* valid, const uint8_t* valid_meas_k, int n, float fx,
-                    float fy, float cx, float cy, int height, int width, int pixel_border,
+                    const uint8_t* valid, const uint8_t* valid_meas_k, int n,
+                    const float* K_dev, int height, int width, int pixel_border,
                     float z_eps, float sigma_pixel, float sigma_depth, float huber_k,
                     int max_iters, float rel_error, float delta_norm, float* T_CkCf,
                     int* status, float* cost, void* workspace, size_t workspace_bytes,
@@ -303,6 +352,19 @@ int m3r_track_calib(const float* Xf, const float* meas_k, const float* Qk,
 int m3r_edge_build(const int64_t* idx_src2dst, const uint8_t* valid_match, const float* Q_src,
                    const float* Q_dst, int num_edges, int n, float Q_conf, float* Q_out,
                    int* valid_count, m3r_stream_t stream);
+/* The same pass writing the PACKED records FactorGraph appends (global_opt.py:88-97 keeps
+ * idx, valid_match and Q as three tensors; here they are one): packed_out (E,n) records with
+ * q = valid_match ? Q : -Q.  Q_out is optional (NULL ok).  16 instead of 21 B per point. */
+int m3r_edge_build_packed(const int64_t* idx_src2dst, const uint8_t* valid_match,
+                          const float* Q_src, const float* Q_dst, int num_edges, int n,
+                          float Q_conf, m3r_packed_match* packed_out, float* Q_out,
+                          int* valid_count, m3r_stream_t stream);
+/* Reference layout <-> packed records, lossless both ways for 0 <= idx < 2^31 and Q >= 0
+ * (count = num_edges * n points; any of the three outputs of unpack may be NULL). */
+int m3r_edge_pack(const int64_t* idx, const uint8_t* valid_match, const float* Q, size_t count,
+                  m3r_packed_match* packed_out, m3r_stream_t stream);
+int m3r_edge_unpack(const m3r_packed_match* packed, size_t count, int64_t* idx,
+                    uint8_t* valid_match, float* Q, m3r_stream_t stream);
 
 /* Frame.update_pointmap for the per-point filtering modes (frame.py:41-105), in place on
  * X_canon (n,3) / C (n,1), optionally applying a Sim3 to the new points first

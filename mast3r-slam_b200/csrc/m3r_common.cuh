@@ -30,6 +30,7 @@ inline int check_cuda(cudaError_t e) {
 #define M3R_TRY(expr) do { int _rc = (expr); if (_rc != M3R_OK) return _rc; } while (0)
 
 constexpr int kNumSMs = 148;  // B200
+constexpr int kMaxDevices = 64;  // per-device caches (occupancy, SM count) are indexed by ordinal
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 

@@ -19,10 +19,19 @@ namespace m3r {
 constexpr int kFeThreads = 256;
 constexpr int kFeUnroll = 4;
 
+// packed record of one correspondence (include/m3r_b200.h, m3r_packed_match)
+__device__ __forceinline__ m3r_packed_match pack_match(long long idx, bool valid, float q) {
+  m3r_packed_match r;
+  r.idx = (int32_t)idx;
+  r.q = valid ? q : -q;  // -0.0f when q == 0: the sign bit alone carries valid_match
+  return r;
+}
+
 __global__ void __launch_bounds__(kFeThreads)
 edge_build_kernel(const int64_t* __restrict__ idx, const uint8_t* __restrict__ vmatch,
                   const float* __restrict__ Qsrc, const float* __restrict__ Qdst, int n,
-                  float Q_conf, float* __restrict__ Qout, int* __restrict__ count) {
+                  float Q_conf, float* __restrict__ Qout, m3r_packed_match* __restrict__ pk,
+                  int* __restrict__ count) {
   const int b = blockIdx.y;
   const size_t row = (size_t)b * n;
   int local = 0;
@@ -43,7 +52,8 @@ edge_build_kernel(const int64_t* __restrict__ idx, const uint8_t* __restrict__ v
     const int k = base + u * kFeThreads;
     if (k < n) {
       const float q = sqrtf(__fmul_rn(__ldg(Qsrc + row + id[u]), qd[u]));  // torch.sqrt(Qii[.., idx] * Qji)
-      Qout[row + k] = q;
+      if (Qout) Qout[row + k] = q;
+      if (pk) pk[row + k] = pack_match(id[u], vm[u], q);
       local += (vm[u] && q > Q_conf) ? 1 : 0;
     }
   }
@@ -68,7 +78,8 @@ constexpr int kEbVec = 2;  // groups of 4 points per thread
 __global__ void __launch_bounds__(kFeThreads)
 edge_build_vec4_kernel(const int64_t* __restrict__ idx, const uint8_t* __restrict__ vmatch,
                        const float* __restrict__ Qsrc, const float* __restrict__ Qdst, int n,
-                       float Q_conf, float* __restrict__ Qout, int* __restrict__ count) {
+                       float Q_conf, float* __restrict__ Qout, m3r_packed_match* __restrict__ pk,
+                       int* __restrict__ count) {
   const int b = blockIdx.y;
   const size_t row = (size_t)b * n;
   int local = 0;
@@ -97,7 +108,14 @@ edge_build_vec4_kernel(const int64_t* __restrict__ idx, const uint8_t* __restric
       q.y = sqrtf(__fmul_rn(__ldg(Qsrc + row + ia[u].y), qd[u].y));
       q.z = sqrtf(__fmul_rn(__ldg(Qsrc + row + ib[u].x), qd[u].z));
       q.w = sqrtf(__fmul_rn(__ldg(Qsrc + row + ib[u].y), qd[u].w));
-      *reinterpret_cast<float4*>(Qout + k) = q;
+      if (Qout) *reinterpret_cast<float4*>(Qout + k) = q;
+      if (pk) {  // four 8-byte records = two 128-bit stores
+        const m3r_packed_match r0 = pack_match(ia[u].x, vm[u] & 0xFFu, q.x), r1 = pack_match(ia[u].y, vm[u] & 0xFF00u, q.y);
+        const m3r_packed_match r2 = pack_match(ib[u].x, vm[u] & 0xFF0000u, q.z), r3 = pack_match(ib[u].y, vm[u] & 0xFF000000u, q.w);
+        float4* o = reinterpret_cast<float4*>(pk + k);
+        o[0] = make_float4(__int_as_float(r0.idx), r0.q, __int_as_float(r1.idx), r1.q);
+        o[1] = make_float4(__int_as_float(r2.idx), r2.q, __int_as_float(r3.idx), r3.q);
+      }
       local += ((vm[u] & 0xFFu) && q.x > Q_conf) + ((vm[u] & 0xFF00u) && q.y > Q_conf) +
                ((vm[u] & 0xFF0000u) && q.z > Q_conf) + ((vm[u] & 0xFF000000u) && q.w > Q_conf);
     }
@@ -112,6 +130,26 @@ edge_build_vec4_kernel(const int64_t* __restrict__ idx, const uint8_t* __restric
 #pragma unroll
     for (int w = 0; w < kFeThreads / 32; w++) s += wsum[w];
     if (s) atomicAdd(count + b, s);
+  }
+}
+
+// reference layout (idx i64, valid u8, Q f32) <-> packed records; grid-stride, one point per thread
+__global__ void __launch_bounds__(kFeThreads)
+edge_pack_kernel(const int64_t* __restrict__ idx, const uint8_t* __restrict__ vmatch,
+                 const float* __restrict__ Q, size_t count, m3r_packed_match* __restrict__ pk) {
+  const size_t stride = (size_t)gridDim.x * kFeThreads;
+  for (size_t k = (size_t)blockIdx.x * kFeThreads + threadIdx.x; k < count; k += stride)
+    pk[k] = pack_match(idx[k], vmatch[k] != 0, Q[k]);
+}
+__global__ void __launch_bounds__(kFeThreads)
+edge_unpack_kernel(const m3r_packed_match* __restrict__ pk, size_t count, int64_t* __restrict__ idx,
+                   uint8_t* __restrict__ vmatch, float* __restrict__ Q) {
+  const size_t stride = (size_t)gridDim.x * kFeThreads;
+  for (size_t k = (size_t)blockIdx.x * kFeThreads + threadIdx.x; k < count; k += stride) {
+    const m3r_packed_match r = pk[k];
+    if (idx) idx[k] = (int64_t)r.idx;
+    if (vmatch) vmatch[k] = (__float_as_int(r.q) >= 0) ? 1 : 0;
+    if (Q) Q[k] = fabsf(r.q);
   }
 }
 
@@ -247,29 +285,67 @@ pointmap_update_vec4_kernel(float* __restrict__ Xc, float* __restrict__ Cc, cons
 
 using namespace m3r;
 
-extern "C" int m3r_edge_build(const int64_t* idx_src2dst, const uint8_t* valid_match,
-                              const float* Q_src, const float* Q_dst, int num_edges, int n,
-                              float Q_conf, float* Q_out, int* valid_count, m3r_stream_t stream) {
+static int edge_build_impl(const int64_t* idx_src2dst, const uint8_t* valid_match, const float* Q_src,
+                           const float* Q_dst, int num_edges, int n, float Q_conf, float* Q_out,
+                           m3r_packed_match* pk, int* valid_count, m3r_stream_t stream) {
   if (num_edges < 0 || n < 0 || num_edges > 65535) return M3R_EINVAL;
   if (num_edges == 0) return M3R_OK;
   if (!valid_count) return M3R_EINVAL;
   cudaStream_t st = as_stream(stream);
   M3R_TRY(check_cuda(cudaMemsetAsync(valid_count, 0, sizeof(int) * (size_t)num_edges, st)));
   if (n == 0) return M3R_OK;
-  if (!idx_src2dst || !valid_match || !Q_src || !Q_dst || !Q_out) return M3R_EINVAL;
+  if (!idx_src2dst || !valid_match || !Q_src || !Q_dst || (!Q_out && !pk)) return M3R_EINVAL;
   const bool vec4 = (n % 4) == 0 &&
                     ((reinterpret_cast<uintptr_t>(idx_src2dst) | reinterpret_cast<uintptr_t>(valid_match) |
-                      reinterpret_cast<uintptr_t>(Q_dst) | reinterpret_cast<uintptr_t>(Q_out)) & 15) == 0;
+                      reinterpret_cast<uintptr_t>(Q_dst) | reinterpret_cast<uintptr_t>(Q_out) |
+                      reinterpret_cast<uintptr_t>(pk)) & 15) == 0;
   if (vec4) {
     const int per = kFeThreads * kEbVec * 4;
     dim3 grid4((n + per - 1) / per, num_edges);
     edge_build_vec4_kernel<<<grid4, kFeThreads, 0, st>>>(idx_src2dst, valid_match, Q_src, Q_dst, n, Q_conf,
-                                                         Q_out, valid_count);
+                                                         Q_out, pk, valid_count);
     return after_launch();
   }
   dim3 grid((n + kFeThreads * kFeUnroll - 1) / (kFeThreads * kFeUnroll), num_edges);
   edge_build_kernel<<<grid, kFeThreads, 0, st>>>(idx_src2dst, valid_match, Q_src, Q_dst, n, Q_conf,
-                                                 Q_out, valid_count);
+                                                 Q_out, pk, valid_count);
+  return after_launch();
+}
+
+extern "C" int m3r_edge_build(const int64_t* idx_src2dst, const uint8_t* valid_match,
+                              const float* Q_src, const float* Q_dst, int num_edges, int n,
+                              float Q_conf, float* Q_out, int* valid_count, m3r_stream_t stream) {
+  if (num_edges > 0 && n > 0 && !Q_out) return M3R_EINVAL;
+  return edge_build_impl(idx_src2dst, valid_match, Q_src, Q_dst, num_edges, n, Q_conf, Q_out, nullptr,
+                         valid_count, stream);
+}
+
+extern "C" int m3r_edge_build_packed(const int64_t* idx_src2dst, const uint8_t* valid_match,
+                                     const float* Q_src, const float* Q_dst, int num_edges, int n,
+                                     float Q_conf, m3r_packed_match* packed_out, float* Q_out,
+                                     int* valid_count, m3r_stream_t stream) {
+  if (num_edges > 0 && n > 0 && !packed_out) return M3R_EINVAL;
+  return edge_build_impl(idx_src2dst, valid_match, Q_src, Q_dst, num_edges, n, Q_conf, Q_out, packed_out,
+                         valid_count, stream);
+}
+
+extern "C" int m3r_edge_pack(const int64_t* idx, const uint8_t* valid_match, const float* Q, size_t count,
+                             m3r_packed_match* packed_out, m3r_stream_t stream) {
+  if (count == 0) return M3R_OK;
+  if (!idx || !valid_match || !Q || !packed_out) return M3R_EINVAL;
+  const size_t blocks = (count + kFeThreads - 1) / kFeThreads;
+  const int grid = (int)(blocks < (size_t)kNumSMs * 16 ? blocks : (size_t)kNumSMs * 16);
+  edge_pack_kernel<<<grid, kFeThreads, 0, as_stream(stream)>>>(idx, valid_match, Q, count, packed_out);
+  return after_launch();
+}
+
+extern "C" int m3r_edge_unpack(const m3r_packed_match* packed, size_t count, int64_t* idx,
+                               uint8_t* valid_match, float* Q, m3r_stream_t stream) {
+  if (count == 0) return M3R_OK;
+  if (!packed) return M3R_EINVAL;
+  const size_t blocks = (count + kFeThreads - 1) / kFeThreads;
+  const int grid = (int)(blocks < (size_t)kNumSMs * 16 ? blocks : (size_t)kNumSMs * 16);
+  edge_unpack_kernel<<<grid, kFeThreads, 0, as_stream(stream)>>>(packed, count, idx, valid_match, Q);
   return after_launch();
 }
 

@@ -13,6 +13,8 @@
 //   A        : double[Dp*Dp] augmented normal matrix [H b; b^T 1], padded to 32
 //   x        : double[3*Dp]  the solution x, 1/diag(L), scratch sink
 //   flags    : int32[nb*nb + nb] tile-ready / x-block-ready epochs of the dataflow Cholesky
+//   tickets  : int32[M+2]    per-edge count of finished point-splits (the last one to arrive runs
+//                            the edge's fp64 epilogue), [M] = edges finished in this pass
 #pragma once
 #include "m3r_common.cuh"
 
@@ -26,11 +28,18 @@ struct GnHeader {
   int done;        // 1 once |dx| < delta_thresh (the reference's `break`)
   int chol_fail;   // set by the factorisation of the current iteration
   int iters;       // iterations actually executed
-  int peer_timeout;  // a peer's blocks did not arrive in time (m3r_gn_solve_step_p2p): zero steps
+  int peer_timeout;  // a peer's blocks did not arrive in time (m3r_gn_solve_step_p2p): the step is
+                     // zero, `done` stays 0 and every later launch of the solve is a no-op
 };
 
+// true once the loop has ended: converged (`done`) or aborted by a peer timeout
+__device__ __forceinline__ bool gn_stopped(const GnHeader* hdr) {
+  return (*reinterpret_cast<const volatile int*>(&hdr->done) |
+          *reinterpret_cast<const volatile int*>(&hdr->peer_timeout)) != 0;
+}
+
 struct GnLayout {
-  size_t hdr, ie, je, keys, rank, row_ptr, adj, xc, part, blocks, A, x, flags, total;
+  size_t hdr, ie, je, keys, rank, row_ptr, adj, xc, part, blocks, A, x, flags, tickets, total;
   int P;       // sort size
   int S;       // point splits per edge
   int chunk;   // points per split
@@ -77,6 +86,7 @@ inline GnLayout gn_layout(int N, int M, int Ml, int n) {
   L.x = take(sizeof(double) * (size_t)3 * L.Dp);
   L.nflags = (L.Dp / kGnNB) * (L.Dp / kGnNB) + (L.Dp / kGnNB);
   L.flags = take(sizeof(int) * (size_t)L.nflags);
+  L.tickets = take(sizeof(int) * ((size_t)M + 2));
   // n- and Ml-dependent arrays last: every offset above depends on (N, M) only, `xc` on
   // (N, M, n), and only the TOTAL depends on how many edges this process accumulates.
   L.xc = take(sizeof(float4) * (size_t)N * n);

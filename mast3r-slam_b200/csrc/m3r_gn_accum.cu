@@ -10,13 +10,18 @@
 //     Since Ji = -Jj and Jj = J_local * Adj(T_i)^-1 with Adj constant per edge, this kernel
 //     accumulates only the LOCAL 7x7 (28 unique values) + 7 gradient values in registers,
 //     skipping the structural zeros of each residual row at compile time, and the adjoint is
-//     applied once per edge afterwards, in fp64 (gn_edge_finish_kernel).  This moves the pass
-//     from ALU/local-memory bound to HBM bound.
+//     applied once per edge afterwards, in fp64, by the last of the edge's CTAs to finish
+//     (edge_epilogue).  This moves the pass from ALU/local-memory bound to HBM bound.
 //   * Each directed edge is split over S CTAs (the reference runs one 256-thread CTA per edge)
 //     and reduced in two fixed-order stages, so the result is deterministic and independent of
 //     how edges are distributed over GPUs.
 //   * (Xs, Cs) are packed once per solve as float4, so the Xi/Ci gather is one aligned 16-B
 //     load and the Xj/Cj stream is a coalesced 128-bit load.
+//   * The per-edge streams are read either in the reference's layout (idx i64, valid u8, Q f32:
+//     13 B/point) or as 8-byte packed records (m3r_packed_match: idx i32 + sign-folded Q) that
+//     FactorGraph stores directly — 40 instead of 45 B per (edge, point), SURVEY 8(f)-3.
+#include <type_traits>
+
 #include "m3r_gn.cuh"
 #include "m3r_sim3.cuh"
 
@@ -51,18 +56,24 @@ __device__ __forceinline__ int lower_bound_i64(const int64_t* a, int len, int64_
 }
 
 __global__ void __launch_bounds__(kIdxThreads)
-gn_index_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, int M, int N, int P,
-                int64_t* keys, int* rank, int* ie, int* je, int* row_ptr, int* adj, int* flags,
-                int nflags, GnHeader* hdr) {
+gn_index_kernel(const int64_t* __restrict__ ii_in, const int64_t* __restrict__ jj_in, int two_way, int M,
+                int N, int P, int64_t* keys, int* rank, int* ie, int* je, int* row_ptr, int* adj,
+                int* flags, int nflags, int* tickets, GnHeader* hdr) {
   __shared__ int64_t skeys[kIdxSmemKeys];
   __shared__ int scan[kIdxThreads];
   const int tid = threadIdx.x;
   if (tid == 0) { hdr->done = 0; hdr->chol_fail = 0; hdr->iters = 0; hdr->peer_timeout = 0; }
   for (int t = tid; t < nflags; t += kIdxThreads) flags[t] = 0;
+  for (int t = tid; t < M + 2; t += kIdxThreads) tickets[t] = 0;
+  // two_way: ii_in / jj_in hold the M/2 UNDIRECTED edges and the directed list is
+  // [ii;jj] -> [jj;ii], i.e. FactorGraph.prep_two_way_edges (global_opt.py:104-110) without the cat
+  const int half = M >> 1;
+  auto ii = [&](int e) { return two_way ? (e < half ? ii_in[e] : jj_in[e - half]) : ii_in[e]; };
+  auto jj = [&](int e) { return two_way ? (e < half ? jj_in[e] : ii_in[e - half]) : jj_in[e]; };
   int64_t* buf = (P <= kIdxSmemKeys) ? skeys : keys;
   const int64_t kMax = 0x7fffffffffffffffLL;
   // 1. sorted keyframe ids  (torch::_unique(cat(ii,jj), sorted), gn_kernels.cu:161-164)
-  for (int t = tid; t < P; t += kIdxThreads) buf[t] = t < M ? ii[t] : (t < 2 * M ? jj[t - M] : kMax);
+  for (int t = tid; t < P; t += kIdxThreads) buf[t] = t < M ? ii(t) : (t < 2 * M ? jj(t - M) : kMax);
   __syncthreads();
   bitonic_sort_block(buf, P);
   // 2. rank[t] = (#distinct ids in buf[0..t]) - 1
@@ -86,8 +97,8 @@ gn_index_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, 
   __syncthreads();
   // 3. searchsorted (create_inds, gn_kernels.cu:166-170)
   for (int e = tid; e < M; e += kIdxThreads) {
-    ie[e] = rank[lower_bound_i64(buf, 2 * M, ii[e])];
-    je[e] = rank[lower_bound_i64(buf, 2 * M, jj[e])];
+    ie[e] = rank[lower_bound_i64(buf, 2 * M, ii(e))];
+    je[e] = rank[lower_bound_i64(buf, 2 * M, jj(e))];
   }
   __syncthreads();
   // 4. CSR: sort (row, slot) pairs; slot < M: pose is the i end of edge slot, else j end of slot-M
@@ -118,6 +129,7 @@ struct GnDev {  // kernel-side copy of m3r_gn_params with the sigmas pre-inverte
   float inv_var_a, inv_var_b;  // 1/sigma^2
   float C_thresh, Q_thresh;
   float fx, fy, cx, cy;
+  const float* Kdev;  // calib: non-null => fx, fy, cx, cy are read from this device 3x3 (row-major)
   float u_lo, u_hi, v_lo, v_hi;  // pixel_border, width-1-border, ... as floats
   float z_eps;
   int width;
@@ -159,6 +171,15 @@ __device__ __forceinline__ float robust_weight(float wc, float err) {
   const float s2 = wc * err * err;
   // huber = 1 if s2 < k^2 else k / sqrt(s2)  ==  min(1, k * rsqrt(s2))   (rsqrt(0) = +inf)
   return wc * fminf(1.0f, 1.345f * fast_rsqrt(s2));
+}
+
+// The reference reads K on the device (gn_kernels.cu:1274-1279); so does this kernel when the
+// caller passes the device matrix: no host read of K, hence no hidden synchronisation.
+__device__ __forceinline__ void resolve_intrinsics(GnDev& prm) {
+  if (prm.Kdev) {
+    prm.fx = __ldg(prm.Kdev + 0); prm.fy = __ldg(prm.Kdev + 4);
+    prm.cx = __ldg(prm.Kdev + 2); prm.cy = __ldg(prm.Kdev + 5);
+  }
 }
 
 template <int MODE>
@@ -254,10 +275,104 @@ __device__ __forceinline__ void edge_transform(const float* __restrict__ Twc, in
   }
 }
 
-// two-stage fixed-order reduction: warp shuffle tree, then 8 warps summed in order
-__device__ __forceinline__ void block_reduce_store(const float* h, const float* g,
-                                                   float* __restrict__ dst) {
+// Peer-memory exchange of the sharded solve (m3r_gn_peers): where the finished blocks go and
+// whose flags are raised when this process's pass is complete.
+struct GnPeerDst { double* blocks[M3R_MAX_PEERS]; int world; };
+struct GnPeerFlags { int* flags[M3R_MAX_PEERS]; int world, rank, epoch; };
+
+__device__ __forceinline__ void peer_signal_all(const GnPeerFlags& f) {
+  __threadfence_system();
+  for (int r = 0; r < f.world; r++)
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(f.flags[r] + f.rank), "r"(f.epoch) : "memory");
+}
+
+// Everything an accumulation launch needs.  The per-edge streams address the LOCAL slice in up
+// to two segments: local edge el < split is row el of segment 0, the others row el - split of
+// segment 1 (FactorGraph keeps the forward and the reverse direction in two blocks; passing both
+// replaces prep_two_way_edges' concatenation, global_opt.py:104-110).
+struct AccArgs {
+  GnDev prm;
+  const float* Twc; const float4* xc; const int* ie; const int* je;
+  const void* idx[2];        // int64 match index (reference layout) or m3r_packed_match records
+  const uint8_t* vmatch[2];  // reference layout only
+  const float* Q[2];         // reference layout only
+  int split;
+  int n, edge_begin, chunk, S, M;
+  int pass_edges;            // edges this process finishes per iteration (peer signal), else 0
+  float* part; const GnHeader* hdr; int* tickets;
+  double* blocks; GnPeerDst dst; GnPeerFlags sig;
+};
+
+// Per edge, by the LAST of its S point-split CTAs to arrive (a ticket per edge): sum the S
+// partials (fp64, fixed order => deterministic whichever CTA is last), apply the adjoint of T_i once:
+//   Jj = J_local * A with A[k][:] = apply_Sim3_adj_inv(T_i, e_k)   (gn_kernels.cu:277-297)
+//   S = A^T H_local A,  v = A^T g_local.
+// With dst.world > 1 the block is stored into EVERY process's buffer through the NVLink peer
+// mappings, and the CTA that finishes this process's last edge raises its flag everywhere: the
+// exchange step of the sharded solve costs no launch of its own.  (Until round 2 this was a
+// separate 64-thread kernel per pass plus a one-warp signal kernel: 2 of 5 launches per iteration.)
+__device__ __forceinline__ void edge_epilogue(const AccArgs& a, int el, int e) {
+  __shared__ double Hl[7][7], gl[7], A[7][7], HA[7][7];
+  const int t = threadIdx.x;
+  if (t < 35) {
+    double s = 0.0;
+    for (int sp = 0; sp < a.S; sp++) s += (double)__ldcg(a.part + ((size_t)el * a.S + sp) * kGnPartStride + t);
+    if (t < 28) {
+      int r = 0;
+      while ((r + 1) * (r + 2) / 2 <= t) r++;
+      const int c = t - r * (r + 1) / 2;
+      Hl[r][c] = s; Hl[c][r] = s;
+    } else {
+      gl[t - 28] = s;
+    }
+  } else if (t >= 64 && t < 71) {
+    const int k = t - 64;
+    const int ix = a.ie[e];
+    double Ti[8], X[7], Y[7];
+    for (int m = 0; m < 8; m++) Ti[m] = (double)a.Twc[ix * 8 + m];
+    for (int m = 0; m < 7; m++) X[m] = (m == k) ? 1.0 : 0.0;
+    adj_inv_row<double>(Ti, Ti + 3, Ti[7], X, Y);
+    for (int m = 0; m < 7; m++) A[k][m] = Y[m];
+  }
+  __syncthreads();
+  if (t < 49) {
+    const int r = t / 7, b = t % 7;
+    double s = 0.0;
+    for (int l = 0; l < 7; l++) s += Hl[r][l] * A[l][b];
+    HA[r][b] = s;
+  }
+  __syncthreads();
+  if (t < 56) {
+    double s = 0.0;
+    if (t < 49) {
+      const int r = t / 7, b = t % 7;
+      for (int k = 0; k < 7; k++) s += A[k][r] * HA[k][b];
+    } else {
+      const int m = t - 49;
+      for (int k = 0; k < 7; k++) s += gl[k] * A[k][m];
+    }
+    if (a.dst.world <= 1) a.blocks[(size_t)e * kGnBlock + t] = s;
+    else for (int r = 0; r < a.dst.world; r++) a.dst.blocks[r][(size_t)e * kGnBlock + t] = s;
+    if (a.dst.world > 1) __threadfence_system();  // peer stores ordered before the flag
+  }
+  if (a.pass_edges > 0) {
+    __syncthreads();
+    if (t == 0) {
+      const int done_edges = atomicAdd(a.tickets + a.M, 1);
+      if (done_edges == a.pass_edges - 1) {
+        a.tickets[a.M] = 0;       // ready for the next pass (stream order separates the passes)
+        peer_signal_all(a.sig);   // fence.sys, then flags[rank] = epoch in every process
+      }
+    }
+  }
+}
+
+// two-stage fixed-order reduction (warp shuffle tree, then 8 warps summed in order) into this
+// CTA's partial, then the ticket: the last split of the edge runs the epilogue.
+__device__ __forceinline__ void block_reduce_finish(const AccArgs& a, const float* h, const float* g,
+                                                    int el, int e, int split) {
   __shared__ float red[kAccThreads / 32][kGnPartStride];
+  __shared__ int s_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
   for (int k = 0; k < 28; k++) { const float v = warp_sum(h[k]); if (lane == 0) red[warp][k] = v; }
@@ -268,39 +383,76 @@ __device__ __forceinline__ void block_reduce_store(const float* h, const float* 
     float s = 0.f;
 #pragma unroll
     for (int w = 0; w < kAccThreads / 32; w++) s += red[w][threadIdx.x];
-    dst[threadIdx.x] = s;
+    a.part[((size_t)el * a.S + split) * kGnPartStride + threadIdx.x] = s;
+    __threadfence();  // the partial is visible device-wide before the ticket is taken
   }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int arrived = atomicAdd(a.tickets + e, 1);
+    const int last = arrived == a.S - 1;
+    if (last) { a.tickets[e] = 0; __threadfence(); }  // acquire side: the other splits' partials
+    s_last = last;
+  }
+  __syncthreads();
+  if (s_last) edge_epilogue(a, el, e);
+}
+
+// A stopped loop (converged or aborted) turns the pass into a no-op; in the peer-memory exchange
+// a converged process still raises its flag so that epochs stay consecutive on every rank (the
+// two-buffer parity rule of the exchange relies on it).
+__device__ __forceinline__ bool acc_stopped(const AccArgs& a) {
+  if (!gn_stopped(a.hdr)) return false;
+  if (a.pass_edges > 0 && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 &&
+      *reinterpret_cast<const volatile int*>(&a.hdr->peer_timeout) == 0)
+    peer_signal_all(a.sig);
+  return true;
+}
+
+template <bool PK>
+__device__ __forceinline__ void edge_rows(const AccArgs& a, int el, const unsigned char*& idx_e,
+                                          const uint8_t*& vm_e, const float*& q_e) {
+  const int seg = el < a.split ? 0 : 1;
+  const size_t row = (size_t)(seg ? el - a.split : el) * a.n;
+  idx_e = static_cast<const unsigned char*>(a.idx[seg]) + row * 8;  // 8 B per point either way
+  vm_e = PK ? nullptr : a.vmatch[seg] + row;
+  q_e = PK ? nullptr : a.Q[seg] + row;
+}
+
+// A packed record (m3r_packed_match): .x = match index (int32), .y = bits of the sign-folded
+// confidence (Q if valid_match else -Q).  valid <=> sign bit clear; an invalid match gathers
+// pixel 0 like the reference (gn_kernels.cu:913-914) and fails `q > Q_thresh` (Q_thresh >= 0 on
+// this path, see make_dev_params).
+__device__ __forceinline__ void unpack_match(const int2 rec, int& ind, float& qm) {
+  ind = rec.y >= 0 ? rec.x : 0;
+  qm = __int_as_float(rec.y);
 }
 
 // Generic accumulation kernel (any n, any alignment): register-staged loads.
-template <int MODE>
+template <int MODE, bool PK>
 __global__ void __launch_bounds__(kAccThreads, 2)
-gn_accum_kernel(const GnDev prm, const float* __restrict__ Twc, const float4* __restrict__ xc,
-                const int* __restrict__ ie, const int* __restrict__ je,
-                const int64_t* __restrict__ idx, const uint8_t* __restrict__ vmatch,
-                const float* __restrict__ Q, int n, int edge_begin, int chunk, int S,
-                float* __restrict__ part, const GnHeader* __restrict__ hdr) {
-  if (hdr->done) return;
-  const int el = blockIdx.y, split = blockIdx.x;
-  const int e = edge_begin + el;
-  const int ix = ie[e], jx = je[e];
+gn_accum_kernel(const AccArgs a) {
+  if (acc_stopped(a)) return;
+  GnDev prm = a.prm;
+  if (MODE == M3R_GN_CALIB) resolve_intrinsics(prm);
+  const int el = blockIdx.y, split = blockIdx.x, n = a.n;
+  const int e = a.edge_begin + el;
+  const int ix = a.ie[e], jx = a.je[e];
   float R[9], t[3];
-  edge_transform(Twc, ix, jx, R, t);
+  edge_transform(a.Twc, ix, jx, R, t);
   float h[28], g[7];
 #pragma unroll
   for (int k = 0; k < 28; k++) h[k] = 0.f;
 #pragma unroll
   for (int k = 0; k < 7; k++) g[k] = 0.f;
 
-  const float4* xi_base = xc + (size_t)ix * n;
-  const float4* xj_base = xc + (size_t)jx * n;
-  const int64_t* idx_e = idx + (size_t)el * n;
-  const uint8_t* vm_e = vmatch + (size_t)el * n;
-  const float* q_e = Q + (size_t)el * n;
-  const int p_begin = split * chunk;
-  const int p_end = min(n, p_begin + chunk);
+  const float4* xi_base = a.xc + (size_t)ix * n;
+  const float4* xj_base = a.xc + (size_t)jx * n;
+  const unsigned char* idx_raw; const uint8_t* vm_e; const float* q_e;
+  edge_rows<PK>(a, el, idx_raw, vm_e, q_e);
+  const int p_begin = split * a.chunk;
+  const int p_end = min(n, p_begin + a.chunk);
   for (int base = p_begin + threadIdx.x; base < p_end; base += kAccThreads * kAccUnroll) {
-    long long ind[kAccUnroll];
+    int ind[kAccUnroll];
     float qv[kAccUnroll];
     float4 xj[kAccUnroll], xi[kAccUnroll];
 #pragma unroll
@@ -308,35 +460,51 @@ gn_accum_kernel(const GnDev prm, const float* __restrict__ Twc, const float4* __
       const int k = base + u * kAccThreads;
       const bool in = k < p_end;
       const int kk = in ? k : p_begin;
-      const bool vm = in && (vm_e[kk] != 0);
-      ind[u] = vm ? idx_e[kk] : 0;  // invalid matches gather pixel 0 (gn_kernels.cu:913-914)
-      const float qq = ld_stream_f(q_e + kk);
-      qv[u] = vm ? qq : -3.0e38f;   // fails q > Q_thresh for any finite threshold
+      if (PK) {
+        unpack_match(reinterpret_cast<const int2*>(idx_raw)[kk], ind[u], qv[u]);
+        if (!in) { ind[u] = 0; qv[u] = -3.0e38f; }
+      } else {
+        const bool vm = in && (vm_e[kk] != 0);
+        ind[u] = vm ? (int)reinterpret_cast<const long long*>(idx_raw)[kk] : 0;  // invalid: pixel 0
+        const float qq = ld_stream_f(q_e + kk);
+        qv[u] = vm ? qq : -3.0e38f;   // fails q > Q_thresh for any finite threshold
+      }
       xj[u] = ld_stream_f4(xj_base + kk);
     }
 #pragma unroll
     for (int u = 0; u < kAccUnroll; u++) xi[u] = __ldg(xi_base + ind[u]);
 #pragma unroll
     for (int u = 0; u < kAccUnroll; u++)
-      point_terms<MODE>(prm, R, t, xi[u], xj[u], ind[u], qv[u], h, g);
+      point_terms<MODE>(prm, R, t, xi[u], xj[u], (long long)ind[u], qv[u], h, g);
   }
-  block_reduce_store(h, g, part + ((size_t)el * S + split) * kGnPartStride);
+  block_reduce_finish(a, h, g, el, e, split);
 }
 
 // ------------------------------------------------------------------------------------
 // Streaming form of the same pass (used whenever n % 16 == 0 and the streams are 16-B
-// aligned): the four per-edge streams of a 1024-point stage — Xj/Cj (16 B), idx (8 B),
-// Q (4 B), valid (1 B) = 29 B/point — are fetched by the bulk-copy engine
-// (cp.async.bulk global -> shared, completion on an mbarrier) three stages ahead, so HBM
+// aligned): the per-edge streams of a 1024-point stage are fetched by the bulk-copy engine
+// (cp.async.bulk global -> shared, completion on an mbarrier) several stages ahead, so HBM
 // stays busy independently of the register file; only the irregular Xi/Ci gather is a
-// register load, issued one stage ahead of its use.  Point -> thread mapping, arithmetic and
-// reduction order are identical to gn_accum_kernel, so both produce the same bits.
+// register load, issued one stage ahead of its use.
+//   reference layout: Xj/Cj 16 + idx 8 + Q 4 + valid 1 = 29 B/point streamed, 3 stages (87 KB)
+//   packed layout   : Xj/Cj 16 + record 8            = 24 B/point streamed, 4 stages (96 KB)
+// (+ 16 B gathered either way: 45 / 40 B per point).  Point -> thread mapping, arithmetic and
+// reduction order are identical to gn_accum_kernel and between the two layouts, so all four
+// produce the same bits.
 // ------------------------------------------------------------------------------------
 constexpr int kStagePts = kAccThreads * kAccUnroll;  // 1024
-constexpr int kStages = 3;
-constexpr int kOffIdx = kStagePts * 16, kOffQ = kOffIdx + kStagePts * 8, kOffVm = kOffQ + kStagePts * 4;
-constexpr int kStageBytes = kOffVm + kStagePts;      // 29 KB
-constexpr int kAccSmemBytes = kStages * kStageBytes;
+template <bool PK> struct StageCfg;
+template <> struct StageCfg<false> {
+  static constexpr int kStages = 3;
+  static constexpr int kOffIdx = kStagePts * 16, kOffQ = kOffIdx + kStagePts * 8, kOffVm = kOffQ + kStagePts * 4;
+  static constexpr int kStageBytes = kOffVm + kStagePts;  // 29 KB
+};
+template <> struct StageCfg<true> {
+  static constexpr int kStages = 4;
+  static constexpr int kOffIdx = kStagePts * 16, kOffQ = 0, kOffVm = 0;
+  static constexpr int kStageBytes = kOffIdx + kStagePts * 8;  // 24 KB
+};
+template <bool PK> constexpr int acc_smem_bytes() { return StageCfg<PK>::kStages * StageCfg<PK>::kStageBytes; }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
@@ -357,39 +525,41 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-template <int MODE>
+template <int MODE, bool PK>
 __global__ void __launch_bounds__(kAccThreads, 2)
-gn_accum_stream_kernel(const GnDev prm, const float* __restrict__ Twc, const float4* __restrict__ xc,
-                       const int* __restrict__ ie, const int* __restrict__ je,
-                       const int64_t* __restrict__ idx, const uint8_t* __restrict__ vmatch,
-                       const float* __restrict__ Q, int n, int edge_begin, int chunk, int S,
-                       float* __restrict__ part, const GnHeader* __restrict__ hdr) {
+gn_accum_stream_kernel(const AccArgs a) {
+  using SC = StageCfg<PK>;
+  constexpr int kStages = SC::kStages, kStageBytes = SC::kStageBytes;
+  constexpr int kOffIdx = SC::kOffIdx, kOffQ = SC::kOffQ, kOffVm = SC::kOffVm;
   extern __shared__ __align__(128) unsigned char stage_mem[];
   __shared__ uint64_t full[kStages];
-  if (hdr->done) return;
-  const int tid = threadIdx.x;
+  if (acc_stopped(a)) return;
+  GnDev prm = a.prm;
+  if (MODE == M3R_GN_CALIB) resolve_intrinsics(prm);
+  const int tid = threadIdx.x, n = a.n;
   const int el = blockIdx.y, split = blockIdx.x;
-  const int e = edge_begin + el;
-  const int ix = ie[e], jx = je[e];
-  const float4* xi_base = xc + (size_t)ix * n;
-  const float4* xj_base = xc + (size_t)jx * n;
-  const int64_t* idx_e = idx + (size_t)el * n;
-  const uint8_t* vm_e = vmatch + (size_t)el * n;
-  const float* q_e = Q + (size_t)el * n;
-  const int p_begin = split * chunk;
-  const int p_end = min(n, p_begin + chunk);
+  const int e = a.edge_begin + el;
+  const int ix = a.ie[e], jx = a.je[e];
+  const float4* xi_base = a.xc + (size_t)ix * n;
+  const float4* xj_base = a.xc + (size_t)jx * n;
+  const unsigned char* idx_raw; const uint8_t* vm_e; const float* q_e;
+  edge_rows<PK>(a, el, idx_raw, vm_e, q_e);
+  const int p_begin = split * a.chunk;
+  const int p_end = min(n, p_begin + a.chunk);
   const int T = (p_end - p_begin + kStagePts - 1) / kStagePts;
 
-  auto issue = [&](int st) {  // one thread: arm the barrier, start the four copies of stage st
+  auto issue = [&](int st) {  // one thread: arm the barrier, start the copies of stage st
     const int p0 = p_begin + st * kStagePts;
     const uint32_t cnt = (uint32_t)min(kStagePts, p_end - p0);
     unsigned char* buf = stage_mem + (st % kStages) * kStageBytes;
     uint64_t* bar = &full[st % kStages];
-    mbar_expect_tx(bar, cnt * 29u);
+    mbar_expect_tx(bar, cnt * (PK ? 24u : 29u));
     bulk_g2s(buf, xj_base + p0, cnt * 16u, bar);
-    bulk_g2s(buf + kOffIdx, idx_e + p0, cnt * 8u, bar);
-    bulk_g2s(buf + kOffQ, q_e + p0, cnt * 4u, bar);
-    bulk_g2s(buf + kOffVm, vm_e + p0, cnt, bar);
+    bulk_g2s(buf + kOffIdx, idx_raw + (size_t)p0 * 8, cnt * 8u, bar);
+    if (!PK) {
+      bulk_g2s(buf + kOffQ, q_e + p0, cnt * 4u, bar);
+      bulk_g2s(buf + kOffVm, vm_e + p0, cnt, bar);
+    }
   };
   if (tid == 0) {
     for (int s = 0; s < kStages; s++) mbar_init(&full[s], 1);
@@ -398,7 +568,7 @@ gn_accum_stream_kernel(const GnDev prm, const float* __restrict__ Twc, const flo
     for (int st = 0; st < kStages && st < T; st++) issue(st);
   }
   float R[9], t[3];
-  edge_transform(Twc, ix, jx, R, t);
+  edge_transform(a.Twc, ix, jx, R, t);
   float h[28], g[7];
 #pragma unroll
   for (int k = 0; k < 28; k++) h[k] = 0.f;
@@ -406,159 +576,108 @@ gn_accum_stream_kernel(const GnDev prm, const float* __restrict__ Twc, const flo
   for (int k = 0; k < 7; k++) g[k] = 0.f;
   __syncthreads();  // barriers initialised
 
-  // slot of this thread's u-th point inside a stage, -1 when past the end of the split.  Every
-  // stage but the last of the image is full (chunks are multiples of the stage size), and a
-  // full stage needs none of the range tests: `full` is CTA-uniform.
-  auto slot_of = [&](int st, int u, bool full) {
-    const int sl = u * kAccThreads + tid;
-    return (full || p_begin + st * kStagePts + sl < p_end) ? sl : -1;
-  };
+  // Every stage but the last of the image is full (chunks are multiples of the stage size), and a
+  // full stage needs none of the range tests: `stage_full` is CTA-uniform.
   auto stage_full = [&](int st) { return p_begin + (st + 1) * kStagePts <= p_end; };
-  float4 xi_nxt[kAccUnroll];
-  int ind_nxt[kAccUnroll];  // gathered pixel (0 for invalid matches, gn_kernels.cu:913-914)
-  auto gather = [&](int st) {
-    const unsigned char* buf = stage_mem + (st % kStages) * kStageBytes;
-    if (stage_full(st)) {
-#pragma unroll
-      for (int u = 0; u < kAccUnroll; u++) {
-        const int sl = u * kAccThreads + tid;
-        const bool vm = buf[kOffVm + sl] != 0;
-        ind_nxt[u] = vm ? (int)reinterpret_cast<const long long*>(buf + kOffIdx)[sl] : 0;
-        xi_nxt[u] = __ldg(xi_base + ind_nxt[u]);
-      }
+  // (gathered pixel, confidence or -3e38) of this thread's u-th point of a stage
+  auto match_of = [&](const unsigned char* buf, int sl, bool in, int& ind, float& qv) {
+    if (PK) {
+      unpack_match(reinterpret_cast<const int2*>(buf + kOffIdx)[sl], ind, qv);
+      if (!in) { ind = 0; qv = -3.0e38f; }
     } else {
-#pragma unroll
-      for (int u = 0; u < kAccUnroll; u++) {
-        const int sl = slot_of(st, u, false);
-        const bool vm = sl >= 0 && buf[kOffVm + (sl < 0 ? 0 : sl)] != 0;
-        ind_nxt[u] = vm ? (int)reinterpret_cast<const long long*>(buf + kOffIdx)[sl] : 0;
-        xi_nxt[u] = __ldg(xi_base + ind_nxt[u]);
-      }
+      const bool vm = in && buf[kOffVm + sl] != 0;
+      ind = vm ? (int)reinterpret_cast<const long long*>(buf + kOffIdx)[sl] : 0;
+      qv = vm ? reinterpret_cast<const float*>(buf + kOffQ)[sl] : -3.0e38f;
     }
+  };
+  float4 xi_nxt[kAccUnroll];
+  auto gather_impl = [&](int st, auto FULL) {
+    constexpr bool kFull = decltype(FULL)::value;
+    const unsigned char* buf = stage_mem + (st % kStages) * kStageBytes;
+#pragma unroll
+    for (int u = 0; u < kAccUnroll; u++) {
+      const int sl = u * kAccThreads + tid;
+      const bool in = kFull || (p_begin + st * kStagePts + sl < p_end);
+      int ind; float qv;
+      match_of(buf, in ? sl : 0, in, ind, qv);
+      xi_nxt[u] = __ldg(xi_base + ind);
+    }
+  };
+  auto gather = [&](int st) {
+    if (stage_full(st)) gather_impl(st, std::true_type{}); else gather_impl(st, std::false_type{});
   };
   mbar_wait(&full[0], 0);
   gather(0);
   for (int it = 0; it < T; it++) {
     float4 xi[kAccUnroll];
-    int ind[kAccUnroll];
 #pragma unroll
-    for (int u = 0; u < kAccUnroll; u++) { xi[u] = xi_nxt[u]; ind[u] = ind_nxt[u]; }
+    for (int u = 0; u < kAccUnroll; u++) xi[u] = xi_nxt[u];
     if (it + 1 < T) {
       mbar_wait(&full[(it + 1) % kStages], ((it + 1) / kStages) & 1);
       gather(it + 1);
     }
     const unsigned char* buf = stage_mem + (it % kStages) * kStageBytes;
-    if (stage_full(it)) {
+    auto compute = [&](auto FULL) {
+      constexpr bool kFull = decltype(FULL)::value;
 #pragma unroll
       for (int u = 0; u < kAccUnroll; u++) {
-        const int s0 = u * kAccThreads + tid;
-        const float qv = buf[kOffVm + s0] != 0 ? reinterpret_cast<const float*>(buf + kOffQ)[s0] : -3.0e38f;
+        const int sl = u * kAccThreads + tid;
+        const bool in = kFull || (p_begin + it * kStagePts + sl < p_end);
+        const int s0 = in ? sl : 0;  // past-the-end lanes re-read slot 0 with weight 0
+        int ind; float qv;           // the stage is still in shared memory: re-read, do not carry
+        match_of(buf, s0, in, ind, qv);
         // 32 consecutive points without a usable match (occluded / low-confidence regions are
         // spatially coherent in real maps) contribute exact zeros: skip their arithmetic.  Measured
         // on config 3: +1.3 % with 96 % usable matches, +7 % with half of them dropped in ~30-px
         // blobs (profiles/time_gn_sparse.py); the calib kernel lost 2.6 % to it and goes without.
-        if (MODE != M3R_GN_CALIB && __ballot_sync(0xffffffffu, qv > prm.Q_thresh) == 0u) continue;
+        if (kFull && MODE != M3R_GN_CALIB && __ballot_sync(0xffffffffu, qv > prm.Q_thresh) == 0u) continue;
         const float4 xj = reinterpret_cast<const float4*>(buf)[s0];
-        point_terms<MODE>(prm, R, t, xi[u], xj, (long long)ind[u], qv, h, g);
+        point_terms<MODE>(prm, R, t, xi[u], xj, (long long)ind, qv, h, g);
       }
-    } else {
-#pragma unroll
-      for (int u = 0; u < kAccUnroll; u++) {
-        const int sl = slot_of(it, u, false);
-        const int s0 = sl < 0 ? 0 : sl;  // past-the-end lanes re-read slot 0 with weight 0
-        const bool vm = sl >= 0 && buf[kOffVm + s0] != 0;
-        const float qv = vm ? reinterpret_cast<const float*>(buf + kOffQ)[s0] : -3.0e38f;
-        const float4 xj = reinterpret_cast<const float4*>(buf)[s0];
-        point_terms<MODE>(prm, R, t, xi[u], xj, (long long)ind[u], qv, h, g);
-      }
-    }
+    };
+    if (stage_full(it)) compute(std::true_type{}); else compute(std::false_type{});
     __syncthreads();  // every thread is done with stage `it`: its buffer may be refilled
     if (tid == 0 && it + kStages < T) issue(it + kStages);
   }
-  block_reduce_store(h, g, part + ((size_t)el * S + split) * kGnPartStride);
+  block_reduce_finish(a, h, g, el, e, split);
 }
 
-// Per edge: sum the S partials (fp64, fixed order), apply the adjoint of T_i once:
-//   Jj = J_local * A with A[k][:] = apply_Sim3_adj_inv(T_i, e_k)   (gn_kernels.cu:277-297)
-//   S = A^T H_local A,  v = A^T g_local.
-// With peers.world > 1 the block is stored into EVERY process's buffer through the NVLink peer
-// mappings (the exchange step of the sharded solve, fused into the producer).
-struct GnPeerDst { double* blocks[M3R_MAX_PEERS]; int world; };
-
-__global__ void __launch_bounds__(64)
-gn_edge_finish_kernel(const float* __restrict__ Twc, const int* __restrict__ ie,
-                      const float* __restrict__ part, int edge_begin, int S,
-                      double* __restrict__ blocks, const GnPeerDst dst,
-                      const GnHeader* __restrict__ hdr) {
-  if (hdr->done) return;
-  __shared__ double Hl[7][7], gl[7], A[7][7], HA[7][7];
-  const int el = blockIdx.x, e = edge_begin + el, t = threadIdx.x;
-  if (t < 35) {
-    double s = 0.0;
-    for (int sp = 0; sp < S; sp++) s += (double)part[((size_t)el * S + sp) * kGnPartStride + t];
-    if (t < 28) {
-      int a = 0;
-      while ((a + 1) * (a + 2) / 2 <= t) a++;
-      const int c = t - a * (a + 1) / 2;
-      Hl[a][c] = s; Hl[c][a] = s;
-    } else {
-      gl[t - 28] = s;
-    }
-  } else if (t >= 40 && t < 47) {
-    const int k = t - 40;
-    const int ix = ie[e];
-    double Ti[8], X[7], Y[7];
-    for (int m = 0; m < 8; m++) Ti[m] = (double)Twc[ix * 8 + m];
-    for (int m = 0; m < 7; m++) X[m] = (m == k) ? 1.0 : 0.0;
-    adj_inv_row<double>(Ti, Ti + 3, Ti[7], X, Y);
-    for (int m = 0; m < 7; m++) A[k][m] = Y[m];
-  }
-  __syncthreads();
-  if (t < 49) {
-    const int a = t / 7, b = t % 7;
-    double s = 0.0;
-    for (int l = 0; l < 7; l++) s += Hl[a][l] * A[l][b];
-    HA[a][b] = s;
-  }
-  __syncthreads();
-  if (t < 49) {
-    const int a = t / 7, b = t % 7;
-    double s = 0.0;
-    for (int k = 0; k < 7; k++) s += A[k][a] * HA[k][b];
-    if (dst.world <= 1) blocks[(size_t)e * kGnBlock + t] = s;
-    else for (int r = 0; r < dst.world; r++) dst.blocks[r][(size_t)e * kGnBlock + t] = s;
-  } else if (t < 56) {
-    const int m = t - 49;
-    double s = 0.0;
-    for (int k = 0; k < 7; k++) s += gl[k] * A[k][m];
-    if (dst.world <= 1) blocks[(size_t)e * kGnBlock + t] = s;
-    else for (int r = 0; r < dst.world; r++) dst.blocks[r][(size_t)e * kGnBlock + t] = s;
-  }
-  if (dst.world > 1) __threadfence_system();  // peer stores ordered before the flag that follows
-}
-
-// Raises flags[rank] = epoch in every process (one warp; launched behind the finish kernel).
-struct GnPeerFlags { int* flags[M3R_MAX_PEERS]; int world, rank, epoch; };
+// Raises flags[rank] = epoch in every process: a pass over zero edges still has to announce itself.
 __global__ void gn_peer_signal_kernel(const GnPeerFlags f, const GnHeader* __restrict__ hdr) {
-  if (hdr->done) return;
-  __threadfence_system();
-  const int r = threadIdx.x;
-  if (r < f.world)
-    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(f.flags[r] + f.rank), "r"(f.epoch) : "memory");
+  if (*reinterpret_cast<const volatile int*>(&hdr->peer_timeout)) return;
+  if (threadIdx.x == 0) peer_signal_all(f);
 }
 
-static GnDev make_dev_params(const m3r_gn_params* p) {
+static GnDev make_dev_params(const m3r_gn_params* p, bool packed) {
   GnDev d;
   d.inv_var_a = (float)(1.0 / ((double)p->sigma_a * (double)p->sigma_a));
   d.inv_var_b = p->sigma_b != 0.f ? (float)(1.0 / ((double)p->sigma_b * (double)p->sigma_b)) : 0.f;
-  d.C_thresh = p->C_thresh; d.Q_thresh = p->Q_thresh;
+  d.C_thresh = p->C_thresh;
+  // packed records carry valid_match in the sign of Q (Q >= 0: it is a square root), so an invalid
+  // match must fail `q > Q_thresh` through its sign: clamp the threshold at 0.  A valid match with
+  // Q == 0 has weight 0 on either side of the test, so the results do not change.
+  d.Q_thresh = (packed && p->Q_thresh < 0.f) ? 0.f : p->Q_thresh;
   d.fx = p->fx; d.fy = p->fy; d.cx = p->cx; d.cy = p->cy;
+  d.Kdev = p->mode == M3R_GN_CALIB ? p->K_dev : nullptr;
   d.u_lo = (float)p->pixel_border; d.u_hi = (float)(p->width - 1 - p->pixel_border);
   d.v_lo = (float)p->pixel_border; d.v_hi = (float)(p->height - 1 - p->pixel_border);
   d.z_eps = p->z_eps;
   d.width = p->width > 0 ? p->width : 1;
   d.width_magic = d.width > 1 ? (unsigned)((0x100000000ULL + (unsigned)d.width - 1) / (unsigned)d.width) : 0xFFFFFFFFu;
   return d;
+}
+
+template <int MODE, bool PK>
+static int launch_accum(const AccArgs& a, dim3 grid, bool stream_ok, cudaStream_t st) {
+  if (stream_ok) {  // > 48 KB of dynamic shared memory is an opt-in, per device: set it every time
+    M3R_TRY(check_cuda(cudaFuncSetAttribute(gn_accum_stream_kernel<MODE, PK>,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            acc_smem_bytes<PK>())));
+    gn_accum_stream_kernel<MODE, PK><<<grid, kAccThreads, acc_smem_bytes<PK>(), st>>>(a);
+  } else {
+    gn_accum_kernel<MODE, PK><<<grid, kAccThreads, 0, st>>>(a);
+  }
+  return after_launch();
 }
 
 }  // namespace m3r
@@ -574,27 +693,32 @@ extern "C" int* m3r_gn_done_flag(void* workspace) {
   return workspace ? &reinterpret_cast<GnHeader*>(workspace)->done : nullptr;
 }
 
+extern "C" int* m3r_gn_status(void* workspace) {
+  return workspace ? &reinterpret_cast<GnHeader*>(workspace)->done : nullptr;  // int32[4]: the GnHeader
+}
+
 extern "C" double* m3r_gn_blocks(void* workspace, int num_poses, int num_edges, int local_edges,
                                  int n) {
   if (!workspace) return nullptr;
   return ws_ptr<double>(workspace, gn_layout(num_poses, num_edges, local_edges, n).blocks);
 }
 
-extern "C" int m3r_gn_prepare(const float* Xs, const float* Cs, const int64_t* ii,
-                              const int64_t* jj, int num_poses, int n, int num_edges,
-                              int local_edges, void* workspace, size_t workspace_bytes,
-                              m3r_stream_t stream) {
+static int gn_prepare_impl(const float* Xs, const float* Cs, const int64_t* ii, const int64_t* jj,
+                           int two_way, int num_poses, int n, int num_edges, int local_edges,
+                           void* workspace, size_t workspace_bytes, m3r_stream_t stream) {
   if (num_poses < 1 || n <= 0 || num_edges <= 0 || local_edges < 0 || local_edges > num_edges)
     return M3R_EINVAL;
+  if (two_way && (num_edges & 1)) return M3R_EINVAL;
   if (!Xs || !Cs || !ii || !jj || !workspace) return M3R_EINVAL;
   const GnLayout L = gn_layout(num_poses, num_edges, local_edges, n);
   if (workspace_bytes < L.total) return M3R_EWORKSPACE;
   cudaStream_t st = as_stream(stream);
   gn_index_kernel<<<1, kIdxThreads, 0, st>>>(
-      ii, jj, num_edges, num_poses, L.P, ws_ptr<int64_t>(workspace, L.keys),
+      ii, jj, two_way, num_edges, num_poses, L.P, ws_ptr<int64_t>(workspace, L.keys),
       ws_ptr<int>(workspace, L.rank), ws_ptr<int>(workspace, L.ie), ws_ptr<int>(workspace, L.je),
       ws_ptr<int>(workspace, L.row_ptr), ws_ptr<int>(workspace, L.adj),
-      ws_ptr<int>(workspace, L.flags), L.nflags, ws_ptr<GnHeader>(workspace, L.hdr));
+      ws_ptr<int>(workspace, L.flags), L.nflags, ws_ptr<int>(workspace, L.tickets),
+      ws_ptr<GnHeader>(workspace, L.hdr));
   M3R_TRY(after_launch());
   const size_t count = (size_t)num_poses * n;
   const int grid = (int)((count + 255) / 256 < (size_t)(kNumSMs * 16) ? (count + 255) / 256
@@ -603,91 +727,107 @@ extern "C" int m3r_gn_prepare(const float* Xs, const float* Cs, const int64_t* i
   return after_launch();
 }
 
-static int gn_accumulate_impl(const m3r_gn_params* prm, const float* Twc,
-                              const int64_t* idx_ii2jj, const uint8_t* valid_match,
-                              const float* Q, int num_poses, int n, int num_edges,
-                              int edge_begin, int edge_count, double* blocks,
-                              const m3r_gn_peers* peers, void* workspace,
+extern "C" int m3r_gn_prepare(const float* Xs, const float* Cs, const int64_t* ii,
+                              const int64_t* jj, int num_poses, int n, int num_edges,
+                              int local_edges, void* workspace, size_t workspace_bytes,
+                              m3r_stream_t stream) {
+  return gn_prepare_impl(Xs, Cs, ii, jj, 0, num_poses, n, num_edges, local_edges, workspace,
+                         workspace_bytes, stream);
+}
+
+extern "C" int m3r_gn_prepare_two_way(const float* Xs, const float* Cs, const int64_t* ii,
+                                      const int64_t* jj, int num_poses, int n, int num_edges,
+                                      int local_edges, void* workspace, size_t workspace_bytes,
+                                      m3r_stream_t stream) {
+  return gn_prepare_impl(Xs, Cs, ii, jj, 1, num_poses, n, num_edges, local_edges, workspace,
+                         workspace_bytes, stream);
+}
+
+// One accumulation pass over local edges [0, edge_count) = global [edge_begin, +edge_count).
+// seg: the per-edge streams in up to two segments (AccArgs); packed selects the record layout.
+struct EdgeStreams {
+  const void* idx[2]; const uint8_t* vm[2]; const float* Q[2];
+  int split; bool packed;
+};
+
+static int gn_accumulate_impl(const m3r_gn_params* prm, const float* Twc, const EdgeStreams& es,
+                              int num_poses, int n, int num_edges, int edge_begin, int edge_count,
+                              double* blocks, const m3r_gn_peers* peers, void* workspace,
                               size_t workspace_bytes, m3r_stream_t stream) {
   if (!prm || num_poses < 1 || n <= 0 || num_edges <= 0 || edge_begin < 0 || edge_count < 0 ||
       edge_begin + edge_count > num_edges || edge_count > 65535)
     return M3R_EINVAL;
-  GnPeerDst dst;
-  dst.world = 0;
+  AccArgs a;
+  a.dst.world = 0; a.sig.world = 0; a.sig.rank = 0; a.sig.epoch = 0; a.pass_edges = 0;
   if (peers) {
     if (peers->world < 1 || peers->world > M3R_MAX_PEERS || peers->rank < 0 || peers->rank >= peers->world)
       return M3R_EINVAL;
-    dst.world = peers->world;
+    a.dst.world = peers->world;
+    a.sig.world = peers->world; a.sig.rank = peers->rank; a.sig.epoch = peers->epoch;
     for (int r = 0; r < peers->world; r++) {
       if (!peers->blocks[r] || !peers->flags[r]) return M3R_EINVAL;
-      dst.blocks[r] = peers->blocks[r];
+      a.dst.blocks[r] = peers->blocks[r];
+      a.sig.flags[r] = peers->flags[r];
     }
     blocks = peers->blocks[peers->rank];
+    if (peers->world > 1) a.pass_edges = edge_count;
   }
+  cudaStream_t st = as_stream(stream);
   if (edge_count == 0) {
     if (peers && peers->world > 1 && workspace) {  // nothing to add, but the peers still wait for this rank
-      GnPeerFlags f;
-      f.world = peers->world; f.rank = peers->rank; f.epoch = peers->epoch;
-      for (int r = 0; r < peers->world; r++) f.flags[r] = peers->flags[r];
       const GnLayout L0 = gn_layout(num_poses, num_edges, 0, n);
-      gn_peer_signal_kernel<<<1, 32, 0, as_stream(stream)>>>(f, ws_ptr<GnHeader>(workspace, L0.hdr));
+      gn_peer_signal_kernel<<<1, 32, 0, st>>>(a.sig, ws_ptr<GnHeader>(workspace, L0.hdr));
       return after_launch();
     }
     return M3R_OK;
   }
-  if (!Twc || !idx_ii2jj || !valid_match || !Q || !blocks || !workspace) return M3R_EINVAL;
+  if (!Twc || !es.idx[0] || !blocks || !workspace) return M3R_EINVAL;
+  if (!es.packed && (!es.vm[0] || !es.Q[0])) return M3R_EINVAL;
+  if (es.split < 0 || (es.split < edge_count && !es.idx[1])) return M3R_EINVAL;
   if (prm->sigma_a == 0.f) return M3R_EINVAL;
   // the partial buffer is sized for `local_edges`; accept any slice up to that size
   const GnLayout L = gn_layout(num_poses, num_edges, edge_count, n);  // offsets independent of edge_count
   if (workspace_bytes < L.part + sizeof(float) * (size_t)edge_count * L.S * kGnPartStride)
     return M3R_EWORKSPACE;
-  cudaStream_t st = as_stream(stream);
-  const GnDev d = make_dev_params(prm);
-  const GnHeader* hdr = ws_ptr<GnHeader>(workspace, L.hdr);
+  a.prm = make_dev_params(prm, es.packed);
+  a.Twc = Twc; a.xc = ws_ptr<float4>(workspace, L.xc);
+  a.ie = ws_ptr<int>(workspace, L.ie); a.je = ws_ptr<int>(workspace, L.je);
+  for (int s = 0; s < 2; s++) { a.idx[s] = es.idx[s]; a.vmatch[s] = es.vm[s]; a.Q[s] = es.Q[s]; }
+  a.split = es.split < edge_count ? es.split : edge_count;
+  a.n = n; a.edge_begin = edge_begin; a.chunk = L.chunk; a.S = L.S; a.M = num_edges;
+  a.part = ws_ptr<float>(workspace, L.part);
+  a.hdr = ws_ptr<GnHeader>(workspace, L.hdr);
+  a.tickets = ws_ptr<int>(workspace, L.tickets);
+  a.blocks = blocks;
   dim3 grid(L.S, edge_count);
   // streaming (bulk-copy) form when every stage of every stream is 16-B aligned
-  const bool stream_ok = (n % 16 == 0) && ((uintptr_t)idx_ii2jj % 16 == 0) &&
-                         ((uintptr_t)valid_match % 16 == 0) && ((uintptr_t)Q % 16 == 0);
-  if (stream_ok) {  // > 48 KB of dynamic shared memory is an opt-in, per device
-    const void* fn = prm->mode == M3R_GN_RAYS    ? (const void*)gn_accum_stream_kernel<M3R_GN_RAYS>
-                     : prm->mode == M3R_GN_CALIB ? (const void*)gn_accum_stream_kernel<M3R_GN_CALIB>
-                                                 : (const void*)gn_accum_stream_kernel<M3R_GN_POINTS>;
-    M3R_TRY(check_cuda(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            kAccSmemBytes)));
+  bool stream_ok = (n % 16 == 0);
+  for (int s = 0; s < 2; s++) {
+    stream_ok = stream_ok && ((uintptr_t)es.idx[s] % 16 == 0);
+    if (!es.packed) stream_ok = stream_ok && ((uintptr_t)es.vm[s] % 16 == 0) && ((uintptr_t)es.Q[s] % 16 == 0);
   }
-#define M3R_ACC(MODE)                                                                          \
-  do {                                                                                         \
-    if (stream_ok)                                                                             \
-      gn_accum_stream_kernel<MODE><<<grid, kAccThreads, kAccSmemBytes, st>>>(                  \
-          d, Twc, ws_ptr<float4>(workspace, L.xc), ws_ptr<int>(workspace, L.ie),               \
-          ws_ptr<int>(workspace, L.je), idx_ii2jj, valid_match, Q, n, edge_begin, L.chunk,     \
-          L.S, ws_ptr<float>(workspace, L.part), hdr);                                         \
-    else                                                                                       \
-      gn_accum_kernel<MODE><<<grid, kAccThreads, 0, st>>>(                                     \
-          d, Twc, ws_ptr<float4>(workspace, L.xc), ws_ptr<int>(workspace, L.ie),               \
-          ws_ptr<int>(workspace, L.je), idx_ii2jj, valid_match, Q, n, edge_begin, L.chunk,     \
-          L.S, ws_ptr<float>(workspace, L.part), hdr);                                         \
-  } while (0)
+#define M3R_ACC(MODE) \
+  (es.packed ? launch_accum<MODE, true>(a, grid, stream_ok, st) : launch_accum<MODE, false>(a, grid, stream_ok, st))
   switch (prm->mode) {
-    case M3R_GN_RAYS: M3R_ACC(M3R_GN_RAYS); break;
-    case M3R_GN_CALIB: M3R_ACC(M3R_GN_CALIB); break;
-    case M3R_GN_POINTS: M3R_ACC(M3R_GN_POINTS); break;
+    case M3R_GN_RAYS: return M3R_ACC(M3R_GN_RAYS);
+    case M3R_GN_CALIB: return M3R_ACC(M3R_GN_CALIB);
+    case M3R_GN_POINTS: return M3R_ACC(M3R_GN_POINTS);
     default: return M3R_EINVAL;
   }
 #undef M3R_ACC
-  M3R_TRY(after_launch());
-  gn_edge_finish_kernel<<<edge_count, 64, 0, st>>>(Twc, ws_ptr<int>(workspace, L.ie),
-                                                   ws_ptr<float>(workspace, L.part), edge_begin,
-                                                   L.S, blocks, dst, hdr);
-  M3R_TRY(after_launch());
-  if (peers && peers->world > 1) {
-    GnPeerFlags f;
-    f.world = peers->world; f.rank = peers->rank; f.epoch = peers->epoch;
-    for (int r = 0; r < peers->world; r++) f.flags[r] = peers->flags[r];
-    gn_peer_signal_kernel<<<1, 32, 0, st>>>(f, hdr);
-    M3R_TRY(after_launch());
-  }
-  return M3R_OK;
+}
+
+static EdgeStreams reference_streams(const int64_t* idx, const uint8_t* vm, const float* Q) {
+  EdgeStreams es;
+  es.idx[0] = idx; es.idx[1] = nullptr; es.vm[0] = vm; es.vm[1] = nullptr; es.Q[0] = Q; es.Q[1] = nullptr;
+  es.split = 0x7fffffff; es.packed = false;
+  return es;
+}
+static EdgeStreams packed_streams(const m3r_packed_match* pk0, const m3r_packed_match* pk1, int split) {
+  EdgeStreams es;
+  es.idx[0] = pk0; es.idx[1] = pk1; es.vm[0] = es.vm[1] = nullptr; es.Q[0] = es.Q[1] = nullptr;
+  es.split = split; es.packed = true;
+  return es;
 }
 
 extern "C" int m3r_gn_accumulate(const m3r_gn_params* prm, const float* Twc,
@@ -695,8 +835,19 @@ extern "C" int m3r_gn_accumulate(const m3r_gn_params* prm, const float* Twc,
                                  const float* Q, int num_poses, int n, int num_edges,
                                  int edge_begin, int edge_count, double* blocks, void* workspace,
                                  size_t workspace_bytes, m3r_stream_t stream) {
-  return gn_accumulate_impl(prm, Twc, idx_ii2jj, valid_match, Q, num_poses, n, num_edges, edge_begin,
-                            edge_count, blocks, nullptr, workspace, workspace_bytes, stream);
+  return gn_accumulate_impl(prm, Twc, reference_streams(idx_ii2jj, valid_match, Q), num_poses, n,
+                            num_edges, edge_begin, edge_count, blocks, nullptr, workspace,
+                            workspace_bytes, stream);
+}
+
+extern "C" int m3r_gn_accumulate_packed(const m3r_gn_params* prm, const float* Twc,
+                                        const m3r_packed_match* pk0, const m3r_packed_match* pk1,
+                                        int split, int num_poses, int n, int num_edges,
+                                        int edge_begin, int edge_count, double* blocks,
+                                        const m3r_gn_peers* peers, void* workspace,
+                                        size_t workspace_bytes, m3r_stream_t stream) {
+  return gn_accumulate_impl(prm, Twc, packed_streams(pk0, pk1, split), num_poses, n, num_edges,
+                            edge_begin, edge_count, blocks, peers, workspace, workspace_bytes, stream);
 }
 
 extern "C" int m3r_gn_accumulate_p2p(const m3r_gn_params* prm, const float* Twc,
@@ -705,8 +856,9 @@ extern "C" int m3r_gn_accumulate_p2p(const m3r_gn_params* prm, const float* Twc,
                                      int edge_begin, int edge_count, const m3r_gn_peers* peers,
                                      void* workspace, size_t workspace_bytes, m3r_stream_t stream) {
   if (!peers) return M3R_EINVAL;
-  return gn_accumulate_impl(prm, Twc, idx_ii2jj, valid_match, Q, num_poses, n, num_edges, edge_begin,
-                            edge_count, nullptr, peers, workspace, workspace_bytes, stream);
+  return gn_accumulate_impl(prm, Twc, reference_streams(idx_ii2jj, valid_match, Q), num_poses, n,
+                            num_edges, edge_begin, edge_count, nullptr, peers, workspace,
+                            workspace_bytes, stream);
 }
 
 extern "C" int m3r_gn_solve_step_p2p(float* Twc, const m3r_gn_peers* peers, int num_poses,
@@ -733,31 +885,67 @@ extern "C" int m3r_gn_solve_step(float* Twc, const double* blocks, int num_poses
                          as_stream(stream));
 }
 
-extern "C" int m3r_gauss_newton(const m3r_gn_params* prm, float* Twc, const float* Xs,
-                                const float* Cs, const int64_t* ii, const int64_t* jj,
-                                const int64_t* idx_ii2jj, const uint8_t* valid_match,
-                                const float* Q, int num_poses, int n, int num_edges, int max_iter,
-                                float delta_thresh, float* dx, void* workspace,
-                                size_t workspace_bytes, m3r_stream_t stream) {
+// the whole loop: prepare, then max_iter x (accumulate in grid.y-sized slices, solve step)
+static int gauss_newton_impl(const m3r_gn_params* prm, float* Twc, const float* Xs, const float* Cs,
+                             const int64_t* ii, const int64_t* jj, int two_way, const EdgeStreams& es,
+                             int num_poses, int n, int num_edges, int max_iter, float delta_thresh,
+                             float* dx, void* workspace, size_t workspace_bytes, m3r_stream_t stream) {
   if (!prm || num_poses < 2 || n <= 0 || num_edges <= 0 || max_iter < 0 || !dx) return M3R_EINVAL;
   if (workspace_bytes < m3r_gn_workspace_bytes(num_poses, num_edges, num_edges, n))
     return M3R_EWORKSPACE;
   M3R_TRY(check_cuda(cudaMemsetAsync(dx, 0, sizeof(float) * 7 * (size_t)(num_poses - 1),
                                      as_stream(stream))));
   if (max_iter == 0) return M3R_OK;
-  M3R_TRY(m3r_gn_prepare(Xs, Cs, ii, jj, num_poses, n, num_edges, num_edges, workspace,
-                         workspace_bytes, stream));
+  M3R_TRY(gn_prepare_impl(Xs, Cs, ii, jj, two_way, num_poses, n, num_edges, num_edges, workspace,
+                          workspace_bytes, stream));
   double* blocks = m3r_gn_blocks(workspace, num_poses, num_edges, num_edges, n);
+  const int kSlice = 32768;  // grid.y limit is 65535
   for (int it = 0; it < max_iter; it++) {
-    // edge slices of <= 65535 (grid.y limit)
-    for (int e0 = 0; e0 < num_edges; e0 += 32768) {
-      const int cnt = num_edges - e0 < 32768 ? num_edges - e0 : 32768;
-      M3R_TRY(m3r_gn_accumulate(prm, Twc, idx_ii2jj + (size_t)e0 * n, valid_match + (size_t)e0 * n,
-                                Q + (size_t)e0 * n, num_poses, n, num_edges, e0, cnt, blocks,
-                                workspace, workspace_bytes, stream));
+    for (int e0 = 0; e0 < num_edges; e0 += kSlice) {
+      const int cnt = num_edges - e0 < kSlice ? num_edges - e0 : kSlice;
+      EdgeStreams sl = es;  // the slice [e0, e0+cnt) of the local (= whole) edge list
+      const size_t esz = (size_t)n;
+      auto adv = [&](int seg, size_t rows) {
+        sl.idx[seg] = static_cast<const unsigned char*>(es.idx[seg]) + rows * esz * 8;
+        if (!es.packed) { sl.vm[seg] = es.vm[seg] + rows * esz; sl.Q[seg] = es.Q[seg] + rows * esz; }
+      };
+      if (e0 >= es.split) {  // wholly inside segment 1
+        adv(1, (size_t)(e0 - es.split));
+        sl.idx[0] = sl.idx[1]; sl.vm[0] = sl.vm[1]; sl.Q[0] = sl.Q[1];
+        sl.split = 0x7fffffff;
+      } else {
+        adv(0, (size_t)e0);
+        sl.split = es.split - e0;
+      }
+      M3R_TRY(gn_accumulate_impl(prm, Twc, sl, num_poses, n, num_edges, e0, cnt, blocks, nullptr,
+                                 workspace, workspace_bytes, stream));
     }
     M3R_TRY(m3r_gn_solve_step(Twc, blocks, num_poses, num_edges, delta_thresh, dx, workspace,
                               workspace_bytes, stream));
   }
   return M3R_OK;
+}
+
+extern "C" int m3r_gauss_newton(const m3r_gn_params* prm, float* Twc, const float* Xs,
+                                const float* Cs, const int64_t* ii, const int64_t* jj,
+                                const int64_t* idx_ii2jj, const uint8_t* valid_match,
+                                const float* Q, int num_poses, int n, int num_edges, int max_iter,
+                                float delta_thresh, float* dx, void* workspace,
+                                size_t workspace_bytes, m3r_stream_t stream) {
+  if (max_iter > 0 && (!idx_ii2jj || !valid_match || !Q)) return M3R_EINVAL;
+  return gauss_newton_impl(prm, Twc, Xs, Cs, ii, jj, 0, reference_streams(idx_ii2jj, valid_match, Q),
+                           num_poses, n, num_edges, max_iter, delta_thresh, dx, workspace,
+                           workspace_bytes, stream);
+}
+
+extern "C" int m3r_gauss_newton_packed(const m3r_gn_params* prm, float* Twc, const float* Xs,
+                                       const float* Cs, const int64_t* ii, const int64_t* jj,
+                                       int two_way, const m3r_packed_match* pk0,
+                                       const m3r_packed_match* pk1, int split, int num_poses, int n,
+                                       int num_edges, int max_iter, float delta_thresh, float* dx,
+                                       void* workspace, size_t workspace_bytes, m3r_stream_t stream) {
+  if (max_iter > 0 && (!pk0 || split < 0 || (split < num_edges && !pk1))) return M3R_EINVAL;
+  return gauss_newton_impl(prm, Twc, Xs, Cs, ii, jj, two_way, packed_streams(pk0, pk1, split),
+                           num_poses, n, num_edges, max_iter, delta_thresh, dx, workspace,
+                           workspace_bytes, stream);
 }

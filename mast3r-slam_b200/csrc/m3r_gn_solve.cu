@@ -42,10 +42,15 @@ gn_assemble_kernel(const double* __restrict__ blocks, const int* __restrict__ ie
                    const int* __restrict__ adj, int M, int N, int D, int Dp, double* __restrict__ A,
                    GnHeader* hdr, const int* wait_flags, int wait_world, int wait_epoch,
                    int smem_bytes) {
-  if (hdr->done) return;
   extern __shared__ __align__(16) double rowbuf[];  // [7][7r+7]: this pose's rows of the lower triangle
   __shared__ int s_e[kAsmChunk], s_other[kAsmChunk];
   __shared__ unsigned char s_role[kAsmChunk];
+  if (*reinterpret_cast<volatile int*>(&hdr->peer_timeout)) return;  // aborted solve: nothing runs any more
+  const bool done = *reinterpret_cast<volatile int*>(&hdr->done) != 0;
+  // A converged solve still WAITS for the peers' flags of this epoch (one CTA, no work after it):
+  // the exchange buffers alternate by epoch parity, and "epoch e+2 may overwrite the buffer of
+  // epoch e" holds only if every process has passed the wait of e+1, no-op iteration or not.
+  if (done && !(wait_flags && blockIdx.x == 0)) return;
   if (wait_flags) {  // peer-memory exchange: all ranks' blocks of this iteration must have landed
     if (threadIdx.x == 0) {
       unsigned long long t0;
@@ -57,13 +62,17 @@ gn_assemble_kernel(const double* __restrict__ blocks, const int* __restrict__ ie
           if (v - wait_epoch >= 0) break;
           unsigned long long t1;
           asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
-          if (t1 - t0 > 10000000000ull) { hdr->peer_timeout = 1; break; }  // 10 s: give up, zero step
+          if (t1 - t0 > 10000000000ull) {  // 10 s: give up — zero step, solve aborted (m3r_gn_status)
+            if (!done) hdr->peer_timeout = 1;
+            break;
+          }
           __nanosleep(64);
         }
       }
     }
     __syncthreads();
   }
+  if (done) return;
   const int t = threadIdx.x;
   const int r = blockIdx.x;  // free index; pose row r+1
   if (r == N - 1) {          // augmented row diagonal + identity padding
@@ -175,9 +184,11 @@ __device__ __forceinline__ void post_flag(int* f, int epoch) {
 
 // Optional timeline of the dataflow kernel (diagnostics; set by m3r_debug_chol_trace): per
 // task 4 x u64 = {kind<<32 | i<<16 | j, t_begin, t_inputs_ready, t_end} in globaltimer ns.
-static unsigned long long* g_chol_trace = nullptr;
-static int g_chol_trace_cap = 0;
-static int g_chol_delay_us = 0, g_chol_delay_which = 0;
+// Process-wide diagnostics switches; atomics so that concurrent solves (one host thread per
+// device) read a consistent value each — they are test hooks, not per-solve state.
+static std::atomic<unsigned long long*> g_chol_trace{nullptr};
+static std::atomic<int> g_chol_trace_cap{0};
+static std::atomic<int> g_chol_delay_us{0}, g_chol_delay_which{0};
 __device__ __forceinline__ unsigned long long gtimer() {
   unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t;
 }
@@ -704,8 +715,8 @@ __device__ __forceinline__ void gn_update_block(float* __restrict__ Twc, const d
                                                 int N, int D, float delta_thresh,
                                                 float* __restrict__ dx, GnHeader* hdr, float* red,
                                                 int nthr, int tid, Sync sync) {
-  const bool fail = *reinterpret_cast<volatile int*>(&hdr->chol_fail) != 0 ||
-                    *reinterpret_cast<volatile int*>(&hdr->peer_timeout) != 0;
+  const bool timed_out = *reinterpret_cast<volatile int*>(&hdr->peer_timeout) != 0;
+  const bool fail = *reinterpret_cast<volatile int*>(&hdr->chol_fail) != 0 || timed_out;
   float ss = 0.f;
   for (int i = tid; i < D; i += nthr) {
     const float v = fail ? 0.f : (float)(-__ldcg(x + i));
@@ -730,13 +741,19 @@ __device__ __forceinline__ void gn_update_block(float* __restrict__ Twc, const d
     float tot = 0.f;
     for (int w = 0; w < (nthr + 31) / 32; w++) tot += red[w];
     hdr->iters += 1;
-    if (sqrtf(tot) < delta_thresh) hdr->done = 1;
+    // a step zeroed by a peer timeout is not convergence: `done` stays 0, the abort is latched
+    // (peer_timeout = 2 turns every later launch of this solve into a no-op) and reported
+    if (timed_out) hdr->peer_timeout = 2;
+    else if (sqrtf(tot) < delta_thresh) hdr->done = 1;
   }
 }
 
 __global__ void __launch_bounds__(kCholThreads, 4)
 chol_dataflow_kernel(const CholArgs a) {
-  if (a.hdr->done) return;
+  if (*reinterpret_cast<volatile int*>(&a.hdr->done)) return;
+  // a peer timeout raised by THIS iteration's assembly still runs the step (as a zero step, so
+  // that dx is defined and the iteration counter — the flag epoch — advances); later ones do not
+  if (*reinterpret_cast<volatile int*>(&a.hdr->peer_timeout) > 1) return;
   __shared__ double sA[NB][NB + 1];
   __shared__ double sB[NB][NB + 1];
   __shared__ double sC[NB][NB + 1];
@@ -791,16 +808,17 @@ __global__ void pose_retr_kernel(float* __restrict__ poses, const float* __restr
 // Co-resident CTA capacity of the device for the dataflow kernel (its CTAs spin on each
 // other's flags, so the grid must never exceed it).
 static int chol_max_ctas() {
-  static int cached = 0;
-  if (cached) return cached;
+  static std::atomic<int> cache[kMaxDevices];  // per DEVICE: one process may drive several GPUs
   int dev = 0, sms = kNumSMs, per_sm = 1;
   cudaGetDevice(&dev);
+  std::atomic<int>* slot = (dev >= 0 && dev < kMaxDevices) ? &cache[dev] : nullptr;
+  if (slot && slot->load()) return slot->load();
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, chol_dataflow_kernel, kCholThreads, 0);
   if (per_sm < 1) per_sm = 1;
   if (per_sm > 4) per_sm = 4;
-  cached = sms * per_sm;
-  return cached;
+  if (slot) slot->store(sms * per_sm);
+  return sms * per_sm;
 }
 
 int gn_solve_launch(float* Twc, const double* blocks, int N, int M, float delta_thresh, float* dx,
@@ -811,12 +829,11 @@ int gn_solve_launch(float* Twc, const double* blocks, int N, int M, float delta_
   const int D = L.D, Dp = L.Dp, nb = Dp / NB;
   size_t asm_smem = (size_t)7 * (7 * (size_t)N) * sizeof(double);  // longest row: r = N-2
   if (asm_smem > (size_t)kAsmSmemMax) asm_smem = kAsmSmemMax;
-  static bool asm_configured = false;
-  if (!asm_configured) {
+  // the > 48 KB opt-in is a per-DEVICE attribute: set it on every launch (as the accumulate
+  // kernels do) rather than once per process, which broke the second GPU of a process at N > 125
+  if (asm_smem > 48 * 1024)
     M3R_TRY(check_cuda(cudaFuncSetAttribute(gn_assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             kAsmSmemMax)));
-    asm_configured = true;
-  }
   gn_assemble_kernel<<<N, kAsmThreads, asm_smem, st>>>(
       blocks, ws_ptr<int>(ws, L.ie), ws_ptr<int>(ws, L.je), ws_ptr<int>(ws, L.row_ptr), ws_ptr<int>(ws, L.adj),
       M, N, D, Dp, A, hdr, wait_flags, wait_world, wait_epoch, (int)asm_smem);
@@ -826,8 +843,8 @@ int gn_solve_launch(float* Twc, const double* blocks, int N, int M, float delta_
   a.flags = ws_ptr<int>(ws, L.flags);
   a.x = ws_ptr<double>(ws, L.x);
   a.Twc = Twc; a.dx = dx; a.N = N; a.delta_thresh = delta_thresh; a.hdr = hdr;
-  a.trace = g_chol_trace; a.trace_cap = g_chol_trace_cap;
-  a.delay_us = g_chol_delay_us; a.delay_which = g_chol_delay_which;
+  a.trace = g_chol_trace.load(); a.trace_cap = a.trace ? g_chol_trace_cap.load() : 0;
+  a.delay_us = g_chol_delay_us.load(); a.delay_which = g_chol_delay_which.load();
   const int tiles = nb * (nb + 1) / 2;
   int grid = chol_max_ctas();
   if (grid > tiles) grid = tiles;
@@ -843,13 +860,13 @@ int gn_solve_launch(float* Twc, const double* blocks, int N, int M, float delta_
 using namespace m3r;
 
 extern "C" void m3r_debug_chol_trace(unsigned long long* device_buf, int capacity_tasks) {
-  g_chol_trace = device_buf;
-  g_chol_trace_cap = device_buf ? capacity_tasks : 0;
+  g_chol_trace_cap.store(device_buf ? capacity_tasks : 0);
+  g_chol_trace.store(device_buf);
 }
 
 extern "C" void m3r_debug_chol_delay(int delay_us, int which) {
-  g_chol_delay_us = delay_us > 0 ? delay_us : 0;
-  g_chol_delay_which = which;
+  g_chol_delay_us.store(delay_us > 0 ? delay_us : 0);
+  g_chol_delay_which.store(which);
 }
 
 extern "C" int m3r_pose_retr(float* poses, const float* dx, int num_poses, int num_fix,

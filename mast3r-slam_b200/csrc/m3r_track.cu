@@ -34,7 +34,8 @@ struct TrackArgs {
   const float* Xf; const float* Xk; const float* Qk; const uint8_t* valid;
   // calib mode: Xk is meas_k (n,3) = [u, v, log z_k], valid_meas (n) its validity
   const uint8_t* valid_meas;
-  float fx, fy, cx, cy, u_lo, u_hi, v_lo, v_hi, z_eps;
+  const float* K;  // calib: (3,3) f32 row-major on the device (read once per CTA, no host copy)
+  float u_lo, u_hi, v_lo, v_hi, z_eps;
   int n;
   float inv_var_ray, inv_var_dist, huber_k;  // calib: 1/sigma_pixel^2, 1/sigma_depth^2
   int max_iters; float rel_error, delta_norm;
@@ -83,6 +84,8 @@ track_kernel(const TrackArgs a) {
   float T[8];
 #pragma unroll
   for (int k = 0; k < 8; k++) T[k] = Tsh[k];
+  float kfx = 0.f, kfy = 0.f, kcx = 0.f, kcy = 0.f;
+  if (MODE == kTrkCalib) { kfx = __ldg(a.K); kfy = __ldg(a.K + 4); kcx = __ldg(a.K + 2); kcy = __ldg(a.K + 5); }
   float old_cost = __int_as_float(0x7f800000);  // +inf (tracker.py:185)
   int iters = 0, converged = 0, failed = 0;
   const int nthreads = gridDim.x * kTrkThreads;
@@ -134,7 +137,7 @@ track_kernel(const TrackArgs a) {
       } else {
         // project_calib (geometry.py:63-104): pz = [u, v, log z], r = meas - pz  =>  e = pz - meas
         const bool valid_z = Pz > a.z_eps;
-        const float u = (a.fx * Px + a.cx * Pz) / Pz, v = (a.fy * Py + a.cy * Pz) / Pz;
+        const float u = (kfx * Px + kcx * Pz) / Pz, v = (kfy * Py + kcy * Pz) / Pz;
         const bool in_img = (u > a.u_lo) && (u < a.u_hi) && (v > a.v_lo) && (v < a.v_hi);
         const bool ok2 = ok && valid_z && in_img && (a.valid_meas[p] != 0);
         const float zinv = 1.0f / Pz;
@@ -146,11 +149,11 @@ track_kernel(const TrackArgs a) {
         if (ok2) {  // weight-0 rows are skipped (0 * inf would poison the sums when z == 0)
           const float w0 = huber_weight(wc_pix, e0, a.huber_k), w1 = huber_weight(wc_pix, e1, a.huber_k);
           const float w2 = huber_weight(wc_dep, e2, a.huber_k);
-          { const float J[7] = {a.fx * zinv, 0.f, -a.fx * xz * zinv, -a.fx * xz * yz,
-                                a.fx * (1.f + xz * xz), -a.fx * yz, 0.f};
+          { const float J[7] = {kfx * zinv, 0.f, -kfx * xz * zinv, -kfx * xz * yz,
+                                kfx * (1.f + xz * xz), -kfx * yz, 0.f};
             trk_row<0x3Du>(h, g, cost, w0, e0, J); }
-          { const float J[7] = {0.f, a.fy * zinv, -a.fy * yz * zinv, -a.fy * (1.f + yz * yz),
-                                a.fy * xz * yz, a.fy * xz, 0.f};
+          { const float J[7] = {0.f, kfy * zinv, -kfy * yz * zinv, -kfy * (1.f + yz * yz),
+                                kfy * xz * yz, kfy * xz, 0.f};
             trk_row<0x3Eu>(h, g, cost, w1, e1, J); }
           { const float J[7] = {0.f, 0.f, zinv, yz, -xz, 0.f, 1.f}; trk_row<0x5Cu>(h, g, cost, w2, e2, J); }
         }
@@ -258,11 +261,11 @@ track_kernel(const TrackArgs a) {
 }
 
 static int track_grid_size(int mode) {
-  static int cache[2] = {0, 0};
-  int& cached = cache[mode];
-  if (cached) return cached;
+  static std::atomic<int> cache[kMaxDevices];  // SM count per DEVICE (one process may drive several)
   int dev = 0, sms = kNumSMs, per_sm = 1;
   cudaGetDevice(&dev);
+  std::atomic<int>* slot = (dev >= 0 && dev < kMaxDevices) ? &cache[dev] : nullptr;
+  if (slot && slot->load()) return slot->load();
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   if (mode == kTrkRays)
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel<kTrkRays>, kTrkThreads, 0);
@@ -273,8 +276,8 @@ static int track_grid_size(int mode) {
   // iteration pays for is the grid barrier and the reduction of the partials, both of which grow
   // with the CTA count (measured 296 / 148 / 111 / 74 CTAs: 59.7 / 52.7 / 53.0 / 56.1 us per solve)
   per_sm = 1;
-  cached = sms * per_sm;
-  return cached;
+  if (slot) slot->store(sms * per_sm);
+  return sms * per_sm;
 }
 
 static int track_launch(int mode, TrackArgs& a, size_t workspace_bytes, cudaStream_t st) {
@@ -312,24 +315,23 @@ extern "C" int m3r_track_ray_dist(const float* Xf, const float* Xk, const float*
   a.inv_var_dist = (float)(1.0 / ((double)sigma_dist * sigma_dist));
   a.huber_k = huber_k; a.max_iters = max_iters; a.rel_error = rel_error; a.delta_norm = delta_norm;
   a.T = T_CkCf; a.status = status; a.cost = cost; a.part = static_cast<float*>(workspace);
-  a.valid_meas = nullptr;
+  a.valid_meas = nullptr; a.K = nullptr;
   return track_launch(kTrkRays, a, workspace_bytes, as_stream(stream));
 }
 
 extern "C" int m3r_track_calib(const float* Xf, const float* meas_k, const float* Qk,
-                               const uint8_t* valid, const uint8_t* valid_meas_k, int n, float fx,
-                               float fy, float cx, float cy, int height, int width,
-                               int pixel_border, float z_eps, float sigma_pixel, float sigma_depth,
+                               const uint8_t* valid, const uint8_t* valid_meas_k, int n,
+                               const float* K_dev, int height, int width, int pixel_border, float z_eps, float sigma_pixel, float sigma_depth,
                                float huber_k, int max_iters, float rel_error, float delta_norm,
                                float* T_CkCf, int* status, float* cost, void* workspace,
                                size_t workspace_bytes, m3r_stream_t stream) {
-  if (n <= 0 || max_iters < 0 || !Xf || !meas_k || !Qk || !valid || !valid_meas_k || !T_CkCf ||
+  if (n <= 0 || max_iters < 0 || !Xf || !meas_k || !Qk || !valid || !valid_meas_k || !K_dev || !T_CkCf ||
       !status || !workspace)
     return M3R_EINVAL;
   if (sigma_pixel == 0.f || sigma_depth == 0.f) return M3R_EINVAL;
   TrackArgs a;
   a.Xf = Xf; a.Xk = meas_k; a.Qk = Qk; a.valid = valid; a.valid_meas = valid_meas_k; a.n = n;
-  a.fx = fx; a.fy = fy; a.cx = cx; a.cy = cy;
+  a.K = K_dev;
   a.u_lo = (float)pixel_border; a.u_hi = (float)(width - 1 - pixel_border);
   a.v_lo = (float)pixel_border; a.v_hi = (float)(height - 1 - pixel_border);
   a.z_eps = z_eps;

@@ -29,7 +29,7 @@ class _GNParams(C.Structure):
                 ("C_thresh", C.c_float), ("Q_thresh", C.c_float),
                 ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
                 ("height", C.c_int), ("width", C.c_int), ("pixel_border", C.c_int),
-                ("z_eps", C.c_float)]
+                ("z_eps", C.c_float), ("K_dev", C.c_void_p)]
 
 
 MAX_PEERS = 16
@@ -64,6 +64,8 @@ EXPORTS = [
     "m3r_match_prep_packed", "m3r_match_iter_proj_packed", "m3r_img_gradient",
     "m3r_render_default_opts", "m3r_render_clear", "m3r_render_surfels", "m3r_render_triangles",
     "m3r_render_resolve",
+    "m3r_gn_status", "m3r_gn_prepare_two_way", "m3r_gn_accumulate_packed", "m3r_gauss_newton_packed",
+    "m3r_edge_build_packed", "m3r_edge_pack", "m3r_edge_unpack",
 ]
 
 
@@ -109,12 +111,21 @@ def _load():
     lib.m3r_track_workspace_bytes.argtypes = [i32]
     lib.m3r_track_ray_dist.argtypes = [vp, vp, vp, vp, i32, f32, f32, f32, i32, f32, f32, vp, vp,
                                        vp, vp, sz, vp]
-    lib.m3r_track_calib.argtypes = [vp, vp, vp, vp, vp, i32, f32, f32, f32, f32, i32, i32, i32, f32,
+    lib.m3r_track_calib.argtypes = [vp, vp, vp, vp, vp, i32, vp, i32, i32, i32, f32,
                                     f32, f32, f32, i32, f32, f32, vp, vp, vp, vp, sz, vp]
     pp = C.POINTER(_GNPeers)
     lib.m3r_gn_accumulate_p2p.argtypes = [gp, vp, vp, vp, vp, i32, i32, i32, i32, i32, pp, vp, sz, vp]
     lib.m3r_gn_solve_step_p2p.argtypes = [vp, pp, i32, i32, f32, vp, vp, sz, vp]
     lib.m3r_edge_build.argtypes = [vp, vp, vp, vp, i32, i32, f32, vp, vp, vp]
+    lib.m3r_edge_build_packed.argtypes = [vp, vp, vp, vp, i32, i32, f32, vp, vp, vp, vp]
+    lib.m3r_edge_pack.argtypes = [vp, vp, vp, sz, vp, vp]
+    lib.m3r_edge_unpack.argtypes = [vp, sz, vp, vp, vp, vp]
+    lib.m3r_gn_status.restype = vp
+    lib.m3r_gn_status.argtypes = [vp]
+    lib.m3r_gn_prepare_two_way.argtypes = lib.m3r_gn_prepare.argtypes
+    lib.m3r_gn_accumulate_packed.argtypes = [gp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, pp, vp, sz, vp]
+    lib.m3r_gauss_newton_packed.argtypes = [gp, vp, vp, vp, vp, vp, i32, vp, vp, i32, i32, i32, i32, i32, f32,
+                                            vp, vp, sz, vp]
     lib.m3r_pointmap_update.argtypes = [vp, vp, vp, vp, vp, i32, i32, vp]
     rv, ro = C.POINTER(_RenderView), C.POINTER(_RenderOpts)
     lib.m3r_render_default_opts.restype = None
@@ -284,14 +295,23 @@ def pose_retr(poses, dx, num_fix=1):
 
 
 def _params(mode, sigma_a, sigma_b, C_thresh, Q_thresh, K=None, height=0, width=0,
-            pixel_border=0, z_eps=0.0):
+            pixel_border=0, z_eps=0.0, device=None):
     p = _GNParams()
     p.mode = mode
     p.sigma_a, p.sigma_b = float(sigma_a), float(sigma_b)
     p.C_thresh, p.Q_thresh = float(C_thresh), float(Q_thresh)
     if K is not None:
-        Kc = K.detach().to("cpu", torch.float32)  # 4 scalars; the reference reads them on device
-        p.fx, p.fy, p.cx, p.cy = float(Kc[0, 0]), float(Kc[1, 1]), float(Kc[0, 2]), float(Kc[1, 2])
+        # the kernels read fx, fy, cx, cy from the DEVICE matrix, like the reference
+        # (gn_kernels.cu:1274-1279): no .to("cpu"), hence no hidden host synchronisation
+        Kd = K.detach()
+        if not (Kd.is_cuda and Kd.dtype == torch.float32 and Kd.is_contiguous() and Kd.shape == (3, 3)):
+            if not Kd.is_cuda and device is None:
+                raise RuntimeError("K must be a CUDA tensor (or pass the target device)")
+            Kd = Kd.to(device=device if not Kd.is_cuda else Kd.device, dtype=torch.float32).contiguous()
+            if Kd.shape != (3, 3):
+                raise RuntimeError("K must be (3,3)")
+        p._K_keepalive = Kd  # the struct holds a raw pointer
+        p.K_dev = Kd.data_ptr()
     p.height, p.width, p.pixel_border, p.z_eps = int(height), int(width), int(pixel_border), float(z_eps)
     return p
 
@@ -336,9 +356,8 @@ def gauss_newton_calib(Twc, Xs, Cs, K, ii, jj, idx_ii2jj, valid_match, Q, height
                        pixel_border, z_eps, sigma_pixel, sigma_depth, C_thresh, Q_thresh, max_iter,
                        delta_thresh):
     """-> [dx (N-1,7)]; Twc updated in place   (gn.h:74-87)"""
-    _req(K, "K", torch.float32, 2)
     prm = _params(GN_CALIB, sigma_pixel, sigma_depth, C_thresh, Q_thresh, K, height, width,
-                  pixel_border, z_eps)
+                  pixel_border, z_eps, device=Twc.device)
     return _gauss_newton(prm, Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, max_iter, delta_thresh)
 
 
@@ -349,19 +368,108 @@ def gauss_newton_points(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, sigma_po
     return _gauss_newton(prm, Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, max_iter, delta_thresh)
 
 
+def _req_packed(t, name, n=None):
+    """Packed edge records (include/m3r_b200.h m3r_packed_match): (E,n) int64, one 8-byte record
+    per correspondence (low word idx i32, high word the sign-folded Q f32)."""
+    t = _req(t, name, torch.int64, 2)
+    if n is not None and t.shape[1] != n:
+        raise RuntimeError(f"{name} must have {n} records per edge, got {t.shape[1]}")
+    if t.data_ptr() % 8:
+        raise RuntimeError(f"{name} must be 8-byte aligned")
+    return t
+
+
+def gauss_newton_packed(prm, Twc, Xs, Cs, ii, jj, pk0, pk1, max_iter, delta_thresh, two_way=False):
+    """The gauss_newton_* loop over PACKED edges in up to two row blocks (m3r_gauss_newton_packed).
+    two_way=True: ii/jj are the E undirected edges, pk0 their forward and pk1 their reverse
+    records — FactorGraph.solve_GN_* without prep_two_way_edges' concatenations.
+    two_way=False: ii/jj are the M directed edges, rows [0,len(pk0)) in pk0, the rest in pk1 (may be None)."""
+    Twc = _req(Twc, "Twc", torch.float32, 2)
+    Xs = _req(Xs, "Xs", torch.float32, 3)
+    Cs = _req(Cs, "Cs", torch.float32)
+    ii = _req(ii, "ii", torch.int64, 1)
+    jj = _req(jj, "jj", torch.int64, 1)
+    N, n = Xs.shape[0], Xs.shape[1]
+    if Twc.shape[0] != N or Twc.shape[1] != 8:
+        raise RuntimeError("Twc must be (num_poses, 8)")
+    pk0 = _req_packed(pk0, "pk0", n)
+    pk1 = _req_packed(pk1, "pk1", n) if pk1 is not None else None
+    M = ii.shape[0] * (2 if two_way else 1)
+    split = pk0.shape[0]
+    if split + (pk1.shape[0] if pk1 is not None else 0) != M:
+        raise RuntimeError(f"packed edge blocks hold {split + (pk1.shape[0] if pk1 is not None else 0)} "
+                           f"edges, the edge list has {M}")
+    with torch.cuda.device(Twc.device):
+        dx = torch.empty((N - 1, 7), dtype=torch.float32, device=Twc.device)
+        nbytes = _lib.m3r_gn_workspace_bytes(N, M, M, n)
+        ws = torch.empty((nbytes,), dtype=torch.uint8, device=Twc.device)
+        _check(_lib.m3r_gauss_newton_packed(C.byref(prm), _ptr(Twc), _ptr(Xs), _ptr(Cs), _ptr(ii), _ptr(jj),
+                                            1 if two_way else 0, _ptr(pk0), _ptr(pk1), split, N, n, M,
+                                            int(max_iter), float(delta_thresh), _ptr(dx), _ptr(ws), nbytes,
+                                            _stream(Twc)), "gauss_newton_packed")
+    return [dx]
+
+
+def edge_pack(idx, valid_match, Q, out=None):
+    """Reference layout (idx (E,n) i64, valid_match (E,n,1) bool, Q (E,n,1) f32) -> packed (E,n) int64."""
+    idx = _req(idx, "idx", torch.int64, 2)
+    vm = _req(valid_match, "valid_match", torch.bool)
+    Q = _req(Q, "Q", torch.float32)
+    if vm.numel() != idx.numel() or Q.numel() != idx.numel():
+        raise RuntimeError("edge_pack: idx, valid_match and Q must have the same number of points")
+    with torch.cuda.device(idx.device):
+        if out is None:
+            out = torch.empty(idx.shape, dtype=torch.int64, device=idx.device)
+        else:
+            out = _req_packed(out, "out", idx.shape[1])
+            if out.shape != idx.shape:
+                raise RuntimeError("edge_pack: out has the wrong shape")
+        _check(_lib.m3r_edge_pack(_ptr(idx), _ptr(vm), _ptr(Q), idx.numel(), _ptr(out), _stream(idx)), "edge_pack")
+    return out
+
+
+def edge_unpack(pk):
+    """packed (E,n) int64 -> (idx (E,n) i64, valid_match (E,n,1) bool, Q (E,n,1) f32), lossless."""
+    pk = _req_packed(pk, "pk")
+    E, n = pk.shape
+    with torch.cuda.device(pk.device):
+        idx = torch.empty((E, n), dtype=torch.int64, device=pk.device)
+        vm = torch.empty((E, n, 1), dtype=torch.bool, device=pk.device)
+        Q = torch.empty((E, n, 1), dtype=torch.float32, device=pk.device)
+        _check(_lib.m3r_edge_unpack(_ptr(pk), pk.numel(), _ptr(idx), _ptr(vm), _ptr(Q), _stream(pk)), "edge_unpack")
+    return idx, vm, Q
+
+
 class GNSolver:
     """Stepwise Gauss-Newton over a slice [edge_begin, edge_begin+edge_count) of the directed edge
     list: prepare once, then per iteration accumulate() -> (exchange blocks) -> solve_step().
-    `ii`/`jj` are the FULL edge lists; idx/valid/Q are the LOCAL slice."""
+    `ii`/`jj` are the FULL edge lists; the per-edge streams are the LOCAL slice, either in the
+    reference layout (idx_local, valid_local, Q_local) or — idx_local an (Ml,n) int64 tensor of
+    packed records and valid_local = Q_local = None — in the packed layout (edge_pack /
+    edge_build_packed), optionally continued in a second row block `packed_tail`."""
 
     def __init__(self, prm, Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_local, edge_begin=0,
-                 peers=None):
-        (self.Twc, self.Xs, self.Cs, self.ii, self.jj, self.idx, self.vm, self.Q, self.N,
-         self.n) = _gn_inputs(Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_local)
+                 peers=None, packed_tail=None):
+        self.packed = valid_local is None and Q_local is None
+        if self.packed:
+            self.Twc = _req(Twc, "Twc", torch.float32, 2)
+            self.Xs = _req(Xs, "Xs", torch.float32, 3)
+            self.Cs = _req(Cs, "Cs", torch.float32)
+            self.ii = _req(ii, "ii", torch.int64, 1)
+            self.jj = _req(jj, "jj", torch.int64, 1)
+            self.N, self.n = self.Xs.shape[0], self.Xs.shape[1]
+            self.idx = _req_packed(idx_local, "packed", self.n)
+            self.tail = _req_packed(packed_tail, "packed_tail", self.n) if packed_tail is not None else None
+            self.vm = self.Q = None
+            self.Ml = self.idx.shape[0] + (self.tail.shape[0] if self.tail is not None else 0)
+        else:
+            (self.Twc, self.Xs, self.Cs, self.ii, self.jj, self.idx, self.vm, self.Q, self.N,
+             self.n) = _gn_inputs(Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_local)
+            self.tail = None
+            self.Ml = self.idx.shape[0]
         self.prm = prm
         self.M = self.ii.shape[0]
         self.edge_begin = int(edge_begin)
-        self.Ml = self.idx.shape[0]
         dev = Twc.device
         with torch.cuda.device(dev):
             self.nbytes = _lib.m3r_gn_workspace_bytes(self.N, self.M, self.Ml, self.n)
@@ -375,20 +483,28 @@ class GNSolver:
                                        _stream(Twc)), "gn_prepare")
 
     def accumulate(self):
-        if self.peers is not None:
-            with torch.cuda.device(self.Twc.device):
+        peers = C.byref(self.peers.next_epoch()) if self.peers is not None else None
+        with torch.cuda.device(self.Twc.device):
+            if self.packed:
+                _check(_lib.m3r_gn_accumulate_packed(C.byref(self.prm), _ptr(self.Twc), _ptr(self.idx),
+                                                     _ptr(self.tail), self.idx.shape[0], self.N, self.n, self.M,
+                                                     self.edge_begin, self.Ml,
+                                                     None if self.peers is not None else _ptr(self.blocks), peers,
+                                                     _ptr(self.ws), self.nbytes, _stream(self.Twc)),
+                       "gn_accumulate_packed")
+            elif self.peers is not None:
                 _check(_lib.m3r_gn_accumulate_p2p(C.byref(self.prm), _ptr(self.Twc), _ptr(self.idx),
                                                   _ptr(self.vm), _ptr(self.Q), self.N, self.n, self.M,
-                                                  self.edge_begin, self.Ml, C.byref(self.peers.next_epoch()),
+                                                  self.edge_begin, self.Ml, peers,
                                                   _ptr(self.ws), self.nbytes, _stream(self.Twc)),
                        "gn_accumulate_p2p")
+            else:
+                _check(_lib.m3r_gn_accumulate(C.byref(self.prm), _ptr(self.Twc), _ptr(self.idx),
+                                              _ptr(self.vm), _ptr(self.Q), self.N, self.n, self.M,
+                                              self.edge_begin, self.Ml, _ptr(self.blocks), _ptr(self.ws),
+                                              self.nbytes, _stream(self.Twc)), "gn_accumulate")
+        if self.peers is not None:
             self.blocks = self.peers.blocks
-            return self.blocks
-        with torch.cuda.device(self.Twc.device):
-            _check(_lib.m3r_gn_accumulate(C.byref(self.prm), _ptr(self.Twc), _ptr(self.idx),
-                                          _ptr(self.vm), _ptr(self.Q), self.N, self.n, self.M,
-                                          self.edge_begin, self.Ml, _ptr(self.blocks), _ptr(self.ws),
-                                          self.nbytes, _stream(self.Twc)), "gn_accumulate")
         return self.blocks
 
     def solve_step(self, delta_thresh):
@@ -406,6 +522,13 @@ class GNSolver:
 
     def local_blocks(self):
         return self.blocks[self.edge_begin:self.edge_begin + self.Ml]
+
+    def status(self):
+        """Host copy (one synchronising 16-byte read) of the solve's status words (m3r_gn_status):
+        dict(done, chol_failed, iterations, peer_timeout)."""
+        off = _lib.m3r_gn_status(_ptr(self.ws)) - self.ws.data_ptr()
+        w = self.ws[off:off + 16].view(torch.int32).tolist()
+        return dict(done=bool(w[0]), chol_failed=bool(w[1]), iterations=w[2], peer_timeout=bool(w[3]))
 
 
 def gn_blocks_reference_layout(blocks):
@@ -460,7 +583,8 @@ class PeerBlocks:
     the consuming kernel waits for the flags on the device (include/m3r_b200.h, m3r_gn_peers).
     Construction is collective (every rank of `group`, same num_edges); reuse the object across solves."""
 
-    _cache = {}
+    _cache = {}          # (num_edges, device, group) -> PeerBlocks, insertion-ordered
+    _cache_max = 4       # distinct graph sizes kept mapped; the oldest mapping is dropped beyond that
 
     def __init__(self, num_edges, device, group=None):
         import torch.distributed as dist
@@ -502,22 +626,32 @@ class PeerBlocks:
     def get(cls, num_edges, device, group=None):
         key = (int(num_edges), str(device), id(group))
         if key not in cls._cache:
+            # every rank sees the same sequence of requests, so every rank evicts the same entry
+            while len(cls._cache) >= cls._cache_max:
+                cls._cache.pop(next(iter(cls._cache)))
             cls._cache[key] = cls(num_edges, device, group)
         return cls._cache[key]
 
 
 def gauss_newton_sharded(prm, Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_local, edge_begin,
-                         max_iter, delta_thresh, group=None, edge_counts=None, p2p=False):
+                         max_iter, delta_thresh, group=None, edge_counts=None, p2p=False, check=True,
+                         packed_tail=None):
     """Edge-sharded solve: each rank accumulates its contiguous slice of the directed edges
-    (`shard_edges`), the 56-double per-edge blocks are exchanged with ONE all-gather per iteration
-    (`exchange_blocks`), then every rank runs the identical replicated assembly + Cholesky +
-    retraction, so poses stay bit-identical on all ranks — and identical to the single-GPU solve,
-    because an edge's block does not depend on which rank computed it."""
+    (`shard_edges`), the 56-double per-edge blocks are exchanged — with ONE all-gather per iteration
+    (`exchange_blocks`) or, p2p=True, inside the kernels over NVLink peer memory — then every rank
+    runs the identical replicated assembly + Cholesky + retraction, so poses stay bit-identical on
+    all ranks — and identical to the single-GPU solve, because an edge's block does not depend on
+    which rank computed it.  The local slice is in the reference layout, or packed records when
+    valid_local and Q_local are None (see GNSolver).
+    check=True (default): after the loop the status words are read back (one 16-byte synchronising
+    read) and a peer-memory timeout raises RuntimeError on EVERY rank — a rank that stopped hearing
+    from a peer stops signalling, so its peers time out as well; nobody keeps diverged poses silently."""
     import torch.distributed as dist
 
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     peers = PeerBlocks.get(ii.shape[0], Twc.device, group) if (p2p and world > 1) else None
-    solver = GNSolver(prm, Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_local, edge_begin, peers=peers)
+    solver = GNSolver(prm, Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_local, edge_begin, peers=peers,
+                      packed_tail=packed_tail)
     if world > 1 and edge_counts is None and peers is None:
         raise RuntimeError("gauss_newton_sharded: edge_counts (from shard_edges) is required")
     for _ in range(int(max_iter)):
@@ -525,6 +659,12 @@ def gauss_newton_sharded(prm, Twc, Xs, Cs, ii, jj, idx_local, valid_local, Q_loc
         if world > 1 and peers is None:
             exchange_blocks(solver.blocks, solver.edge_begin, solver.Ml, list(edge_counts), group)
         solver.solve_step(delta_thresh)
+    if check and peers is not None and int(max_iter) > 0:
+        st = solver.status()
+        if st["peer_timeout"]:
+            raise RuntimeError("gauss_newton_sharded: a peer's blocks did not arrive within the device-side "
+                               f"timeout after {st['iterations']} iteration(s); the poses of this solve are not "
+                               "valid (all ranks raise)")
     return [solver.dx]
 
 
@@ -563,7 +703,9 @@ def track_calib(Xf, meas_k, Qk, valid, valid_meas_k, K, img_size, T_CkCf, sigma_
     valid = _req(valid, "valid", torch.bool)
     valid_meas_k = _req(valid_meas_k, "valid_meas_k", torch.bool)
     T = _req(T_CkCf, "T_CkCf", torch.float32)
-    Kc = K.detach().to("cpu", torch.float32)
+    Kd = K.detach().to(device=Xf.device, dtype=torch.float32).contiguous()  # no-op when already there
+    if Kd.shape != (3, 3):
+        raise RuntimeError("K must be (3,3)")
     n = Xf.shape[0]
     with torch.cuda.device(Xf.device):
         status = torch.zeros((4,), dtype=torch.int32, device=Xf.device)
@@ -571,8 +713,7 @@ def track_calib(Xf, meas_k, Qk, valid, valid_meas_k, K, img_size, T_CkCf, sigma_
         nbytes = _lib.m3r_track_workspace_bytes(n)
         ws = torch.empty((nbytes,), dtype=torch.uint8, device=Xf.device)
         _check(_lib.m3r_track_calib(_ptr(Xf), _ptr(meas_k), _ptr(Qk), _ptr(valid), _ptr(valid_meas_k), n,
-                                    float(Kc[0, 0]), float(Kc[1, 1]), float(Kc[0, 2]), float(Kc[1, 2]),
-                                    int(img_size[0]), int(img_size[1]), int(pixel_border), float(z_eps),
+                                    _ptr(Kd), int(img_size[0]), int(img_size[1]), int(pixel_border), float(z_eps),
                                     float(sigma_pixel), float(sigma_depth), float(huber_k), int(max_iters),
                                     float(rel_error), float(delta_norm), _ptr(T), _ptr(status), _ptr(cost),
                                     _ptr(ws), nbytes, _stream(Xf)), "track_calib")
@@ -595,6 +736,28 @@ def edge_build(idx_src2dst, valid_match, Q_src, Q_dst, Q_conf):
         _check(_lib.m3r_edge_build(_ptr(idx), _ptr(vm), _ptr(Qs), _ptr(Qd), E, n, float(Q_conf), _ptr(Q),
                                    _ptr(cnt), _stream(idx)), "edge_build")
     return Q, cnt
+
+
+def edge_build_packed(idx_src2dst, valid_match, Q_src, Q_dst, Q_conf, out=None, want_Q=False):
+    """edge_build writing PACKED records (m3r_edge_build_packed): -> (pk (E,n) int64, valid_count (E,) i32
+    [, Q (E,n,1) f32]).  `out`: an (E,n) int64 destination (e.g. the tail rows of FactorGraph's store)."""
+    idx = _req(idx_src2dst, "idx", torch.int64, 2)
+    vm = _req(valid_match, "valid_match", torch.bool)
+    Qs = _req(Q_src, "Q_src", torch.float32)
+    Qd = _req(Q_dst, "Q_dst", torch.float32)
+    E, n = idx.shape
+    with torch.cuda.device(idx.device):
+        if out is None:
+            out = torch.empty((E, n), dtype=torch.int64, device=idx.device)
+        else:
+            out = _req_packed(out, "out", n)
+            if out.shape[0] != E:
+                raise RuntimeError("edge_build_packed: out has the wrong number of rows")
+        Q = torch.empty((E, n, 1), dtype=torch.float32, device=idx.device) if want_Q else None
+        cnt = torch.empty((E,), dtype=torch.int32, device=idx.device)
+        _check(_lib.m3r_edge_build_packed(_ptr(idx), _ptr(vm), _ptr(Qs), _ptr(Qd), E, n, float(Q_conf), _ptr(out),
+                                          _ptr(Q), _ptr(cnt), _stream(idx)), "edge_build_packed")
+    return (out, cnt, Q) if want_Q else (out, cnt)
 
 
 POINTMAP_MODES = {"weighted_pointmap": 0, "weighted_spherical": 1, "indep_conf": 2}

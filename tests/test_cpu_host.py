@@ -84,20 +84,35 @@ def test_index_helpers_and_graph_bookkeeping(backends):
     p = matching.lin_to_pixel(idx, 512)
     assert p.tolist() == [[[0, 0], [5, 0], [1, 1], [511, 383]]]
     assert torch.equal(matching.pixel_to_lin(p, 512), idx)
+    # the capacity-doubling edge store (pure torch bookkeeping; packing itself is a CUDA kernel,
+    # tests/test_gpu_frontend.py): records built in the tail rows, rejected rows squeezed out,
+    # growth keeps the live rows, no per-append re-cat of the whole graph
+    from mast3r_slam.global_opt import _EdgeStore
+
+    st, n = _EdgeStore("cpu"), 6
+    st.reserve(3, n)
+    assert st.cap >= 3 and st.pk.shape == (2, st.cap, n) and st.E == 0
+    for b in range(2):
+        st.tail(b, 3).copy_(torch.arange(3 * n).reshape(3, n) + 1000 * b)
+    assert st.commit(torch.tensor([4, 9, 7]), torch.tensor([9, 2, 8]), keep=torch.tensor([True, False, True])) == 2
+    assert st.E == 2 and st.ij[:, :2].tolist() == [[4, 7], [9, 8]]
+    assert st.pk[1, 1].tolist() == list(range(1000 + 2 * n, 1000 + 3 * n))  # row 2 moved up
+    base, grew = st.pk.data_ptr(), st.reallocations
+    st.reserve(1, n)                                    # fits: the store does not move
+    assert st.pk.data_ptr() == base and st.reallocations == grew
+    st.reserve(st.cap, n)                               # does not fit: one move, at least doubled
+    assert st.reallocations == grew + 1 and st.cap >= 2 * 8 and st.E == 2
+    assert st.pk[0, 0].tolist() == list(range(n)) and st.ij[0, :2].tolist() == [4, 7]
+    with pytest.raises(RuntimeError):
+        st.reserve(1, n + 1)                            # all edges of a graph have the same n
     g = FactorGraph(frames=None, device="cpu")
-    n = 6
-    mk = lambda m, dt: torch.arange(m * n).reshape(m, n).to(dt)
-    g.add_edges(torch.tensor([4, 9]), torch.tensor([9, 2]), mk(2, torch.long), mk(2, torch.long) + 100,
-                torch.ones(2, n, 1, dtype=torch.bool), torch.zeros(2, n, 1, dtype=torch.bool),
-                torch.full((2, n, 1), 2.0), torch.full((2, n, 1), 3.0))
-    g.add_edges(torch.tensor([2]), torch.tensor([4]), mk(1, torch.long), mk(1, torch.long) + 100,
-                torch.ones(1, n, 1, dtype=torch.bool), torch.zeros(1, n, 1, dtype=torch.bool),
-                torch.full((1, n, 1), 2.0), torch.full((1, n, 1), 3.0))
-    assert g.get_unique_kf_idx().tolist() == [2, 4, 9]
-    ii, jj, idx2, valid, Q = g.prep_two_way_edges()  # global_opt.py:104-110
-    assert ii.tolist() == [4, 9, 2, 9, 2, 4] and jj.tolist() == [9, 2, 4, 4, 9, 2]
-    assert idx2.shape == (6, n) and int(idx2[3, 0]) == 100
-    assert valid[:3].all() and not valid[3:].any() and float(Q[4, 0, 0]) == 3.0
+    assert g.ii.numel() == 0 and g.idx_ii2jj.numel() == 0 and g.get_unique_kf_idx().numel() == 0
+    with pytest.raises(RuntimeError, match="CUDA"):     # building edges is CUDA work: no CPU path
+        g.add_edges(torch.tensor([4]), torch.tensor([9]), torch.zeros(1, n, dtype=torch.long),
+                    torch.zeros(1, n, dtype=torch.long), torch.ones(1, n, 1, dtype=torch.bool),
+                    torch.ones(1, n, 1, dtype=torch.bool), torch.ones(1, n, 1), torch.ones(1, n, 1))
+    with pytest.raises(RuntimeError, match="matcher"):  # no matcher and no reference front end
+        g.add_factors([0], [1], 0.1)
     # fewer keyframes than `pin` => solve is a no-op (global_opt.py:125-127)
     assert FactorGraph(frames=None, device="cpu")._solve(calib=False) is None
 

@@ -1,0 +1,306 @@
+"""BASELINE-size parity of the Gauss-Newton path (configs 3 and 4 of BASELINE.json / SURVEY 8(d)) in the
+driver-run suite: against the UNMODIFIED reference extension (oracle/_ref) at north_star's bars —
+per-iteration dx and final poses within 1e-5, per-edge Hessian blocks within 1e-4 relative of the
+fp64 restatement at 512x384 — plus the packed edge layout and the mirror classes
+north_star names (FactorGraph.solve_GN_rays / solve_GN_calib, FrameTracker.opt_pose_ray_dist_sim3)."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from tests import synth
+from tests.kfstore import KeyframeStore
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+H, W = synth.H0, synth.W0
+DX_ATOL = 1e-5      # BASELINE.json north_star: pose updates within 1e-5 in fp32
+POSE_ATOL = 1e-5    # final poses within 1e-5
+BLOCK_RTOL = 1e-4   # Hessian blocks within 1e-4 relative (Frobenius, per 7x7 block)
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+def _record(name, obj):
+    """Measured parity numbers are kept (gpurun_out/parity_*.json -> copied under profiles/)."""
+    try:
+        os.makedirs(OUT, exist_ok=True)
+        with open(os.path.join(OUT, f"parity_{name}.json"), "w") as f:
+            json.dump(obj, f, indent=1)
+    except OSError:
+        pass
+
+
+def _graph(config):
+    if config == 3:   # 32 keyframes, 100 edges = 200 directed
+        return synth.make_graph(N=32, seed=1236, device=DEV), False
+    g = synth.make_graph(N=64, counts={1: None, 2: 62, 5: 59, "random": 16}, seed=1237, device=DEV)  # config 4
+    g["Xs"] = synth.constrain_points_to_ray(g["Xs"], H, W, g["K"])
+    return g, True
+
+
+def _run(mod, g, calib, iters, T=None):
+    T = g["Twc"].clone() if T is None else T
+    if calib:
+        out = mod.gauss_newton_calib(T, g["Xs"], g["Cs"], g["K"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
+                                     H, W, -10, 1e-6, 1.0, 10.0, 0.0, 1.5, iters, 0.0)
+    else:
+        out = mod.gauss_newton_rays(T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
+                                    0.003, 10.0, 0.0, 1.5, iters, 0.0)
+    torch.cuda.synchronize()
+    return T, out[0]
+
+
+@pytest.mark.parametrize("config", [3, 4])
+def test_baseline_config_vs_reference_every_iteration(backends, ref_ext, config):
+    """N = 32 / 200 directed edges rays and N = 64 / 400 calib at 512x384, 10 iterations, against the
+    reference extension (gn_kernels.cu:1140-1228, 1546-1638): dx of EVERY iteration (a k-iteration
+    call returns dx_k) and the final poses within 1e-5; and the packed-layout call is bit-identical."""
+    if ref_ext is None:
+        pytest.skip("oracle/_ref not built")
+    g, calib = _graph(config)
+    assert g["M"] == (200 if config == 3 else 400) and g["Xs"].shape[1] == H * W
+    worst_dx, worst_T, dxs = 0.0, 0.0, []
+    for k in range(1, 11):
+        T_r, dx_r = _run(ref_ext, g, calib, k)
+        T_n, dx_n = _run(backends, g, calib, k)
+        d = float((dx_r - dx_n).abs().max())
+        dT = float((T_r - T_n).abs().max())
+        dxs.append(dict(iteration=k, dx_max_abs_diff=d, dx_max_abs=float(dx_r.abs().max()), pose_max_abs_diff=dT))
+        worst_dx, worst_T = max(worst_dx, d), max(worst_T, dT)
+    moved = float((T_n - g["Twc"]).abs().max())
+    _record(f"gn_config{config}_vs_reference", dict(config=config, N=g["N"], directed_edges=g["M"], per_iteration=dxs,
+                                                     pose_max_abs_update=moved, bars=dict(dx=DX_ATOL, pose=POSE_ATOL)))
+    print(f"config {config}: worst |dx_k - reference| {worst_dx:.2e}, worst pose diff {worst_T:.2e}, moved {moved:.2e}")
+    assert moved > 1e-3                      # the solve did something
+    assert worst_dx < DX_ATOL
+    assert worst_T < POSE_ATOL
+    # packed layout (FactorGraph's storage): same arithmetic, same reduction order => same bits
+    pk = backends.edge_pack(g["idx"], g["valid"], g["Q"])
+    prm = (backends._params(backends.GN_CALIB, 1.0, 10.0, 0.0, 1.5, g["K"], H, W, -10, 1e-6) if calib
+           else backends._params(backends.GN_RAYS, 0.003, 10.0, 0.0, 1.5))
+    T_p = g["Twc"].clone()
+    (dx_p,) = backends.gauss_newton_packed(prm, T_p, g["Xs"], g["Cs"], g["ii"], g["jj"], pk, None, 10, 0.0)
+    torch.cuda.synchronize()
+    assert torch.equal(T_p, T_n) and torch.equal(dx_p, dx_n)
+    # ... also split over two row blocks with the UNDIRECTED edge list (what solve_GN_* passes)
+    E = g["M"] // 2
+    T_q = g["Twc"].clone()
+    (dx_q,) = backends.gauss_newton_packed(prm, T_q, g["Xs"], g["Cs"], g["ii"][:E].contiguous(),
+                                           g["jj"][:E].contiguous(), pk[:E], pk[E:], 10, 0.0, two_way=True)
+    torch.cuda.synchronize()
+    assert torch.equal(T_q, T_n) and torch.equal(dx_q, dx_n)
+
+
+@pytest.mark.parametrize("mode", ["rays", "calib"])
+def test_blocks_vs_fp64_oracle_full_size(backends, orc, mode):
+    """Per-edge blocks at 196 608 points per edge (64x the 48x64 case of test_gpu_gn.py): fp32
+    accumulation error grows with the point count, the bar does not (1e-4 relative)."""
+    g = synth.make_graph(N=4, counts={1: None, 2: 2}, seed=1236, device=DEV)
+    if mode == "calib":
+        g["Xs"] = synth.constrain_points_to_ray(g["Xs"], H, W, g["K"])
+        prm = backends._params(backends.GN_CALIB, 1.0, 10.0, 0.0, 1.5, g["K"], H, W, -10, 1e-6)
+        oprm = orc.make_params(orc.MODE_CALIB, 1.0, 10.0, 0.0, 1.5, _np(g["K"]), H, W, -10, 1e-6)
+    else:
+        prm = backends._params(backends.GN_RAYS, 0.003, 10.0, 0.0, 1.5)
+        oprm = orc.make_params(orc.MODE_RAYS, 0.003, 10.0, 0.0, 1.5)
+    solver = backends.GNSolver(prm, g["Twc"].clone(), g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"])
+    blocks = solver.accumulate().clone()
+    # the packed layout produces the same blocks, bit for bit
+    sp = backends.GNSolver(prm, g["Twc"].clone(), g["Xs"], g["Cs"], g["ii"], g["jj"],
+                           backends.edge_pack(g["idx"], g["valid"], g["Q"]), None, None)
+    blocks_p = sp.accumulate().clone()
+    torch.cuda.synchronize()
+    assert torch.equal(blocks, blocks_p)
+    Hs, gs = backends.gn_blocks_reference_layout(blocks)
+    _, ie, je, _, _ = orc.edge_rows(_np(g["ii"]), _np(g["jj"]))
+    _, _, Hs64, gs64 = orc.gn_blocks(oprm, _np(g["Twc"]), _np(g["Xs"]), _np(g["Cs"]), ie, je, _np(g["idx"]),
+                                     _np(g["valid"]), _np(g["Q"]), want64=True)
+    a, b = _np(Hs), Hs64
+    num = np.sqrt(((a - b) ** 2).reshape(a.shape[0], a.shape[1], -1).sum(-1))
+    den = np.sqrt((b ** 2).reshape(b.shape[0], b.shape[1], -1).sum(-1))
+    rel = num / np.maximum(den, 1e-30)
+    gnum = np.sqrt(((_np(gs) - gs64) ** 2).sum(-1))
+    # gradient error measured against what it is solved against: |dg| / (|H|_F |dx|-scale 1)
+    _record(f"gn_blocks_full_size_{mode}", dict(mode=mode, points_per_edge=H * W, edges=int(a.shape[1]),
+                                                 H_block_rel_err_max=float(rel.max()),
+                                                 g_abs_err_over_H_norm_max=float((gnum / den[:2]).max())))
+    print(f"{mode} 512x384: H block rel err max {rel.max():.2e}")
+    assert den.min() > 0 and rel.max() < BLOCK_RTOL
+    assert (gnum / den[:2]).max() < BLOCK_RTOL  # g error is below 1e-4 of the block it multiplies
+
+
+def test_packed_records_roundtrip_and_edge_build(backends):
+    """m3r_edge_pack / m3r_edge_unpack are lossless (incl. Q == 0 on invalid matches: -0.0 keeps the
+    sign) and m3r_edge_build_packed writes exactly pack(idx, valid, Q) of m3r_edge_build's Q."""
+    E, n = 5, 37 * 53
+    g = torch.Generator(device=DEV).manual_seed(5)
+    idx = torch.randint(0, n, (E, n), generator=g, device=DEV)
+    vm = torch.rand((E, n, 1), generator=g, device=DEV) > 0.3
+    Q = 1.0 + torch.rand((E, n, 1), generator=g, device=DEV)
+    Q[0, :5] = 0.0
+    vm[0, :3] = False; vm[0, 3:5] = True
+    pk = backends.edge_pack(idx, vm, Q)
+    i2, v2, q2 = backends.edge_unpack(pk)
+    assert torch.equal(i2, idx) and torch.equal(v2, vm) and torch.equal(q2, Q)
+    w = pk.view(torch.int32).view(E, n, 2)
+    assert torch.equal(w[..., 0].long(), idx)
+    assert torch.equal(w[..., 1] >= 0, vm[..., 0])
+    Qs = 1.0 + torch.rand((E, n, 1), generator=g, device=DEV)
+    Qd = 1.0 + torch.rand((E, n, 1), generator=g, device=DEV)
+    Qref, cnt = backends.edge_build(idx, vm, Qs, Qd, 1.5)
+    pk2, cnt2, Q2 = backends.edge_build_packed(idx, vm, Qs, Qd, 1.5, want_Q=True)
+    assert torch.equal(cnt, cnt2) and torch.equal(Q2, Qref)
+    assert torch.equal(pk2, backends.edge_pack(idx, vm, Qref))
+    # 16-byte aligned rows take the vectorised kernel: same records
+    n4 = 64 * 48
+    idx4 = torch.randint(0, n4, (3, n4), generator=g, device=DEV)
+    vm4 = torch.rand((3, n4, 1), generator=g, device=DEV) > 0.3
+    Qs4 = 1.0 + torch.rand((3, n4, 1), generator=g, device=DEV)
+    Qd4 = 1.0 + torch.rand((3, n4, 1), generator=g, device=DEV)
+    Qr4, c4 = backends.edge_build(idx4, vm4, Qs4, Qd4, 1.5)
+    pk4, c4b = backends.edge_build_packed(idx4, vm4, Qs4, Qd4, 1.5)
+    assert torch.equal(c4, c4b) and torch.equal(pk4, backends.edge_pack(idx4, vm4, Qr4))
+
+
+def _graph_store(g):
+    """Keyframes with ids = graph ids; C is the SUM over N = 2 updates so that get_average_conf()
+    (frame.py:107-108) has something to divide."""
+    ids = torch.unique(torch.cat((g["ii"], g["jj"]))).tolist()
+    K = max(ids) + 1
+    n = g["Xs"].shape[1]
+    X = torch.zeros((K, n, 3), device=DEV); C = torch.ones((K, n, 1), device=DEV)
+    T = torch.zeros((K, 8), device=DEV); T[:, 6:8] = 1.0
+    Nupd = torch.ones(K, dtype=torch.int64)
+    for row, i in enumerate(ids):
+        X[i] = g["Xs"][row]; C[i] = 2.0 * g["Cs"][row]; T[i] = g["Twc"][row]; Nupd[i] = 2
+    return KeyframeStore(X, C, T, (g["H"], g["W"]), Nupd), ids
+
+
+@pytest.mark.parametrize("calib", [False, True])
+def test_factor_graph_solves_through_the_mirror_class(backends, ref_ext, calib):
+    """FactorGraph.solve_GN_rays / solve_GN_calib (global_opt.py:112-213) end to end on the GPU:
+    add_edges in two batches (the store grows), get_poses_points, the in-place pose view, pin,
+    frames.update_T_WCs — against a direct call of the reference extension on the tensors the
+    reference's own class would have built (prep_two_way_edges order)."""
+    from mast3r_slam import config as cfgmod
+    from mast3r_slam.global_opt import FactorGraph
+
+    cfgmod.reset_config()
+    cfg = cfgmod.config["local_opt"]
+    Hs, Ws = 96, 128
+    g = synth.make_graph(N=7, counts={1: None, 2: 4, "random": 1}, H=Hs, W=Ws, seed=1260, device=DEV,
+                         kf_ids=[0, 2, 3, 5, 8, 9, 12])
+    if calib:
+        g["Xs"] = synth.constrain_points_to_ray(g["Xs"], Hs, Ws, g["K"])
+    store, ids = _graph_store(g)
+    E = g["M"] // 2
+    fg = FactorGraph(model=None, frames=store, K=g["K"], device=DEV)
+    for sl in (slice(0, 4), slice(4, E)):   # forward rows [0,E), reverse rows [E,2E) of the directed list
+        fg.add_edges(g["ii"][sl], g["jj"][sl], g["idx"][sl], g["idx"][E:][sl], g["valid"][sl], g["valid"][E:][sl],
+                     g["Q"][sl], g["Q"][E:][sl])
+    assert fg.ii.tolist() == g["ii"][:E].tolist() and fg.jj.tolist() == g["jj"][:E].tolist()
+    ii2, jj2, idx2, vm2, Q2 = fg.prep_two_way_edges()   # the reference's layout, rebuilt on request
+    assert torch.equal(ii2, g["ii"]) and torch.equal(jj2, g["jj"]) and torch.equal(idx2, g["idx"])
+    assert torch.equal(vm2, g["valid"]) and torch.equal(Q2, g["Q"])
+    assert fg.get_unique_kf_idx().tolist() == ids
+    T_before = store.T_WC.clone()
+    (fg.solve_GN_calib if calib else fg.solve_GN_rays)()
+    torch.cuda.synchronize()
+    assert store.updates == 1
+    T_after = store.T_WC[ids, 0]
+    # expected: the same call sequence on the reference extension (or, without it, on our entry point)
+    mod = ref_ext if ref_ext is not None else backends
+    T_exp = g["Twc"].clone()
+    Cs = (2.0 * g["Cs"]) / 2
+    if calib:
+        mod.gauss_newton_calib(T_exp, g["Xs"], Cs, g["K"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"], Hs, Ws,
+                               cfg["pixel_border"], cfg["depth_eps"], cfg["sigma_pixel"], cfg["sigma_depth"],
+                               cfg["C_conf"], cfg["Q_conf"], cfg["max_iters"], cfg["delta_norm"])
+    else:
+        mod.gauss_newton_rays(T_exp, g["Xs"], Cs, g["ii"], g["jj"], g["idx"], g["valid"], g["Q"], cfg["sigma_ray"],
+                              cfg["sigma_dist"], cfg["C_conf"], cfg["Q_conf"], cfg["max_iters"], cfg["delta_norm"])
+    torch.cuda.synchronize()
+    d = float((T_after - T_exp).abs().max())
+    print(f"FactorGraph.solve_GN_{'calib' if calib else 'rays'} vs {'reference' if ref_ext is not None else 'entry point'}: {d:.2e}")
+    assert d < 5e-5   # 96x128 images: 16x fewer points than full size, conditioning as in test_solve_vs_reference
+    assert float((T_after - g["Twc"]).abs().max()) > 1e-3            # poses moved and were written back
+    pin = cfg["pin"]
+    assert torch.equal(store.T_WC[ids[:pin], 0], T_before[ids[:pin], 0])  # pinned keyframes untouched
+    unused = [i for i in range(len(store)) if i not in ids]
+    assert torch.equal(store.T_WC[unused], T_before[unused])
+
+
+def test_factor_graph_add_factors_gates_and_packs_in_place(backends):
+    """add_factors (global_opt.py:30-99) with a stub matcher: match-fraction gate, consecutive edges
+    always kept, relocalisation all-or-nothing, records built in the store without re-concatenation."""
+    from mast3r_slam import config as cfgmod
+    from mast3r_slam.global_opt import FactorGraph
+    from oracle import frontend as ofe
+
+    cfgmod.reset_config()
+    Hs, Ws, E = 24, 32, 6
+    m = synth.make_symmetric_match_outputs(E, H=Hs, W=Ws, seed=91, device=DEV, weak=(1, 4))
+    matcher = lambda model, frames, ii, jj: (m["idx_i2j"], m["idx_j2i"], m["valid_i2j"], m["valid_j2i"], m["Qii"],
+                                             m["Qjj"], m["Qji"], m["Qij"])
+    ii, jj = [0, 0, 1, 2, 0, 3], [1, 2, 2, 3, 3, 4]   # edge 1 (0,2) and 4 (0,3) are weak; (0,1),(1,2),(2,3),(3,4) consecutive
+    fg = FactorGraph(model=None, frames=None, device=DEV)
+    assert fg.add_factors(ii, jj, 0.3, matcher=matcher) is True
+    mc = {k: v.cpu() for k, v in m.items()}
+    Qj, cj = ofe.edge_build(mc["idx_i2j"], mc["valid_i2j"], mc["Qii"], mc["Qji"], 1.5)
+    Qi, ci = ofe.edge_build(mc["idx_j2i"], mc["valid_j2i"], mc["Qjj"], mc["Qij"], 1.5)
+    keep = ofe.add_factors_gate(ii, jj, cj, ci, Hs * Ws, 0.3)
+    assert keep.tolist() == [True, False, True, True, False, True]
+    exp = dict(ii=torch.tensor(ii)[keep], jj=torch.tensor(jj)[keep], idx_ii2jj=mc["idx_i2j"][keep],
+               idx_jj2ii=mc["idx_j2i"][keep], valid_match_i=mc["valid_j2i"][keep], Q_ii2jj=Qj[keep], Q_jj2ii=Qi[keep])
+    assert fg.ii.tolist() == exp["ii"].tolist() and fg.jj.tolist() == exp["jj"].tolist()
+    assert torch.equal(fg.idx_ii2jj.cpu(), exp["idx_ii2jj"]) and torch.equal(fg.valid_match_i.cpu(), exp["valid_match_i"])
+    assert torch.equal(fg.Q_ii2jj.cpu(), exp["Q_ii2jj"]) and torch.equal(fg.Q_jj2ii.cpu(), exp["Q_jj2ii"])
+    # relocalisation: any weak edge rejects the whole batch and leaves the graph as it was
+    before = fg.ii.clone()
+    assert fg.add_factors(ii, jj, 0.3, is_reloc=True, matcher=matcher) is False
+    assert torch.equal(fg.ii, before)
+    # appending again grows the store in place: live rows keep their values, capacity doubles at most once
+    moves = fg._store.reallocations
+    fg.add_factors(ii, jj, 0.3, matcher=matcher)
+    assert fg.ii.tolist() == exp["ii"].tolist() * 2 and fg._store.reallocations <= moves + 1
+    assert torch.equal(fg.idx_jj2ii.cpu(), torch.cat((exp["idx_jj2ii"], exp["idx_jj2ii"])))
+
+
+def test_frame_tracker_mirror_method_ray_dist(backends):
+    """FrameTracker.opt_pose_ray_dist_sim3 (tracker.py:173-214) through the mirror class: the
+    reference's own iterates (tests/golden/tracker_ref.npz) and T_WCf = T_WCk * T_CkCf."""
+    from mast3r_slam import config as cfgmod
+    from mast3r_slam.sim3 import Sim3
+    from mast3r_slam.tracker import FrameTracker
+
+    cfgmod.reset_config()
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "tracker_ref.npz"))
+    trk = FrameTracker(None, None, DEV)
+    for name in ("a", "b"):
+        Hh, Ww, seed = (int(v) for v in z[f"{name}_HW"])
+        d = synth.make_tracker_inputs(Hh, Ww, seed=seed, device="cpu")
+        q = torch.tensor([0.05, 0.02, -0.03, 1.0]); q = q / q.norm()
+        T_WCk = Sim3(torch.cat([torch.tensor([0.3, -0.1, 0.2]), q, torch.tensor([1.1])])[None].to(DEV))
+        # T_WCf = T_WCk so that the relative pose starts at the identity, as in the golden run
+        T_WCf, T_CkCf = trk.opt_pose_ray_dist_sim3(d["Xf"].to(DEV), d["Xk"].to(DEV), Sim3(T_WCk.data.clone()), T_WCk,
+                                                   d["Qk"].to(DEV), d["valid"].to(DEV))
+        torch.cuda.synchronize()
+        assert trk.last_status["converged"] and trk.last_status["iterations"] == len(z[f"{name}_costs"])
+        # the composition T_WCk^-1 * T_WCk is the identity up to rounding, so the start differs by ~1e-7
+        assert np.abs(_np(T_CkCf.data[0]) - z[f"{name}_T_CkCf_out"][0]).max() < 2e-5
+        assert float((T_WCf.data - (T_WCk * T_CkCf).data).abs().max()) == 0.0
+    # full size, against the kernel called directly
+    d = synth.make_tracker_inputs(seed=1234, device=DEV)
+    T = torch.tensor([0, 0, 0, 0, 0, 0, 1, 1], dtype=torch.float32, device=DEV)
+    backends.track_ray_dist(d["Xf"], d["Xk"], d["Qk"], d["valid"], T, 0.003, 10.0, 1.345, 50, 1e-3, 1e-3)
+    I = Sim3.Identity(1, device=DEV)
+    T_WCf, T_CkCf = trk.opt_pose_ray_dist_sim3(d["Xf"], d["Xk"], I, Sim3(I.data.clone()), d["Qk"], d["valid"])
+    assert torch.equal(T_CkCf.data[0], T)
+    assert np.abs(_np(T_WCf.data[0]) - _np(d["T_gt"])).max() < 1e-3
