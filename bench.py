@@ -39,13 +39,22 @@ B_GN_POINT, B_TRACK_POINT = 45, 29
 
 
 def ncu_traffic(kernel, scale=1.0):
-    """DRAM bytes per launch of `kernel` from the committed ncu capture (profiles/traffic.json),
+    """DRAM bytes per launch of `kernel` from the committed ncu capture (profiles/traffic.json, written
+    by the capture script of the round named in its "source" key — NOT a measurement of this run),
     scaled when the bench batch differs from the captured one; None if not captured."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     try:
         with open(p) as f:
             v = json.load(f).get(kernel)
         return None if v is None else float(v) * scale
+    except OSError:
+        return None
+
+
+def ncu_traffic_source():
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get("source", "profiles/traffic.json (capture round not recorded)")
     except OSError:
         return None
 
@@ -125,26 +134,106 @@ def cpu_match_sample(b, threads):
     return time.perf_counter() - t0
 
 
+WORKLOAD = ("match_iterative_proj 512x384, iter_proj max_iter 10 + refine_matches radius 3 dilation 5, "
+            "24-d desc (BASELINE configs[1])")
+
+
+def pin_rank_affinity(local, world):
+    """Give each rank its own host cores, on the GPU's NUMA node when sysfs tells us which cores
+    those are (pinned buffers allocated afterwards are first-touched there).  Returns a description."""
+    try:
+        cur = sorted(os.sched_getaffinity(0))
+    except (AttributeError, OSError):
+        return "affinity: unavailable"
+    cpus, src = cur, "all cores"
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(local).pci_bus_id
+        dom = getattr(torch.cuda.get_device_properties(local), "pci_domain_id", 0)
+        dev_id = torch.cuda.get_device_properties(local).pci_device_id
+        path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev_id:02x}.0/local_cpulist"
+        txt = open(path).read().strip()
+        near = set()
+        for part in txt.split(","):
+            lo, _, hi = part.partition("-")
+            near.update(range(int(lo), int(hi or lo) + 1))
+        near = sorted(near & set(cur))
+        if near and len(near) < len(cur):
+            cpus, src = near, f"NUMA-local cores of GPU {local} ({txt})"
+    except Exception:
+        pass
+    if world > 1:
+        # ranks sharing a core set take disjoint chunks of it (same rule on every rank)
+        share = max(1, world // max(1, len(cur) // max(1, len(cpus))))
+        chunk = max(1, len(cpus) // share)
+        k = local % share
+        mine = cpus[k * chunk:(k + 1) * chunk] or cpus
+    else:
+        mine = cpus
+    try:
+        os.sched_setaffinity(0, mine)
+    except OSError:
+        return "affinity: not permitted"
+    return f"{len(mine)} cores ({src})"
+
+
+def h2d_probe(torch, dev, mb=256, reps=5):
+    """Pinned host -> device copy bandwidth of THIS rank, GB/s (all ranks run it at the same time)."""
+    h = torch.empty((mb << 20,), dtype=torch.uint8).pin_memory()
+    d = torch.empty((mb << 20,), dtype=torch.uint8, device=dev)
+    d.copy_(h, non_blocking=True)
+    torch.cuda.synchronize()
+    a = torch.cuda.Event(enable_timing=True); z = torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        d.copy_(h, non_blocking=True)
+    z.record()
+    torch.cuda.synchronize()
+    return reps * (mb << 20) / (a.elapsed_time(z) * 1e-3) / 1e9
+
+
+def load_reference_cuda():
+    """oracle/_ref/mast3r_slam_backends_ref.so — the UNMODIFIED reference extension compiled for sm_100
+    (oracle/build_ref.py) — as the incumbent timed BESIDE the repo arm (never inside its timed region,
+    never on the product path).  None when the prebuilt file is absent."""
+    try:
+        from oracle import build_ref
+        return build_ref.load_ref()
+    except Exception as e:  # pragma: no cover
+        sys.stderr.write(f"[bench] reference CUDA extension not loadable: {e}\n")
+        return None
+
+
+def make_config(batch, world):
+    """The `config` object of the JSON line — built by ONE function so that both arms state the same."""
+    in_bytes = batch * N_PIX * (12 + 12 + 4 * FDIM + 4 * FDIM)
+    return {"workload": WORKLOAD, "batch_pairs_per_gpu": batch,
+            "l2": f"inputs {in_bytes / 1e6:.0f} MB per step exceed the 126 MB L2",
+            "parallelism": f"independent frame pairs x{world}"}
+
+
 def run_reference(args):
-    """CPU arm: rank 0 only."""
+    """CPU arm (rank 0 only): the same config as the B200 arm, `--steps` timed steps after `--warmup`
+    (>= 3) untimed ones.  A step is a BOUNDED SAMPLE of the workload — one of the batch's frame pairs,
+    ~1.7 s on 16 host cores — because a whole 8-pair step (~14 s) x 25 steps would not end within
+    minutes; per-pixel CPU throughput does not depend on the batch size."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
     threads = os.cpu_count() or 1
-    b = 1
-    for _ in range(min(args.warmup, 1)):
-        cpu_match_sample(b, threads)
-    steps = max(1, min(args.steps, 3))
-    ts = [cpu_match_sample(b, threads) for _ in range(steps)]
+    warm, steps, sample_pairs = max(3, args.warmup), max(1, args.steps), 1
+    for _ in range(warm):
+        cpu_match_sample(sample_pairs, threads)
+    ts = [cpu_match_sample(sample_pairs, threads) for _ in range(steps)]
     t = sum(ts) / len(ts)
-    v = b * N_PIX / t / 1e9
-    sample = f"{b} frame pair(s) of {W}x{H} per step, {steps} step(s), oracle C port + torch-CPU glue"
+    v = sample_pairs * N_PIX / t / 1e9
+    sample = (f"each step = {sample_pairs} of the {args.batch} frame pairs of {W}x{H} (bounded sample), {steps} steps "
+              f"after {warm} warm-up: oracle C port of iter_proj + refine_matches (OpenMP) + torch-CPU glue")
     print(json.dumps({
         "impl": "reference", "metric": "dense matching throughput (match_iterative_proj)",
-        "value": v, "unit": "Gpix/s", "n_gpus": args.gpus, "steps": steps, "warmup": min(args.warmup, 1),
+        "value": v, "unit": "Gpix/s", "n_gpus": args.gpus, "steps": steps, "warmup": warm,
         "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "match_iterative_proj 512x384, iter_proj max_iter 10 + refine_matches "
-                               "radius 3 dilation 5, 24-d desc (BASELINE configs[1])", "batch_pairs": b},
+        "config": make_config(args.batch, args.gpus),
         "cpu_baseline": {"value": v, "unit": "Gpix/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "Gpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
@@ -160,6 +249,7 @@ def main():
     ap.add_argument("--no-extra", action="store_true", help="skip the GN / tracker extras")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-large", action="store_true", help="skip BASELINE configs[4] (N=512, 8192 directed edges)")
+    ap.add_argument("--no-ref-cuda", action="store_true", help="skip the reference_cuda leg (oracle/_ref timed beside)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -175,6 +265,7 @@ def main():
                          "(use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    affinity = pin_rank_affinity(local, world)  # before any pinned allocation
     json_fd = None
     if world > 1:
         # NCCL prints its version banner on STDOUT at communicator creation: keep fd 1 for the ONE
@@ -244,19 +335,36 @@ def main():
     dom = max(range(3), key=lambda i: k_ms[i])
     alg = {0: None, 1: B_ITER_PROJ, 2: B_REFINE}[dom]
     achieved = (alg * b * N_PIX / (k_ms[dom] * 1e-3) / 1e9) if alg else None
+    # refine_matches' real bound: the candidate gathers through the L1 data pipe (241 candidates x 48 B per
+    # query; an L1 hit moves 127 B/clk/SM, profiles/micro/l1_width.cu) and the fp16x2 rounding chain on the
+    # half-rate fma pipe (241 x 24 dims x 2 ops / 2 lanes).  Both are stated at the SM clock sampled in this run.
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
+    l1_peak = 127.0 * n_sm * sm_mhz * 1e6 / 1e9                       # GB/s
+    l1_bytes = 241 * 48 * b * N_PIX                                   # candidate bytes through L1 per launch
+    l1_ach = l1_bytes / (k_ms[2] * 1e-3) / 1e9
+    fp16_floor_ms = 241 * 24 * 2 / 2 * b * N_PIX / 32 / (n_sm * 4 * 0.5 * sm_mhz * 1e6) * 1e3  # warp instr / (4 SMSP x 1/2 per clk)
     roofline = {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": (achieved / peak) if achieved else None, "traffic": ncu_traffic(names[dom], b / 8.0),
+                "traffic_source": ncu_traffic_source(),
                 "peak_kind": peak_kind, "algorithmic_bytes_per_pixel": alg,
                 "algorithmic_bytes_per_launch": (alg * b * N_PIX) if alg else None,
-                "note": "refine_matches is bound by on-chip pipes, not HBM: ncu shows the L1 data pipe 74 % and the "
-                        "fp16x2 (fma-heavy) pipe 62 % busy (profiles/r1v_ncu_digest.md; floors 0.67 / 0.49 ms at "
-                        "b=8); its exact fp16 rounding chain admits no tensor-core form (DESIGN.md 4.2)",
+                "bound_actual": {"bound": "l1 data pipe + fp16x2 (fma-heavy) pipe, not HBM", "kernel": "refine_fused",
+                                 "l1_achieved": l1_ach, "l1_peak": l1_peak, "l1_unit": "GB/s", "l1_frac": l1_ach / l1_peak,
+                                 "l1_peak_source": "127 B/clk/SM measured (profiles/micro/l1_width.cu) x SMs x sampled SM clock",
+                                 "l1_bytes_per_pixel": 241 * 48,
+                                 "fp16_pipe_floor_ms": fp16_floor_ms, "fp16_pipe_frac": fp16_floor_ms / k_ms[2],
+                                 "sm_mhz": sm_mhz},
+                "note": "refine_matches cannot reach '>= 60 % of HBM': it moves 128 compulsory bytes per pixel but 11.6 KB "
+                        "through L1 and 5 784 fp16x2 ops; its exact fp16 rounding chain admits no tensor-core form "
+                        "(DESIGN.md 4.2, BASELINE.md 3)",
                 "on_chip": {"l1_data_pipe_pct": 74.3, "fp16x2_pipe_pct": 62.2, "issue_pct": 63.8,
-                            "source": "profiles/r1v_ncu_digest.md"},
+                            "source": "profiles/r2o_ncu_digest.md (ncu --set full, round 1)"},
                 "kernel_ms": {n: round(t, 4) for n, t in zip(names, k_ms)},
                 "kernels": {
                     "iter_proj_fused": {"achieved": B_ITER_PROJ * b * N_PIX / (k_ms[1] * 1e-3) / 1e9,
-                                        "frac": B_ITER_PROJ * b * N_PIX / (k_ms[1] * 1e-3) / 1e9 / peak},
+                                        "frac": B_ITER_PROJ * b * N_PIX / (k_ms[1] * 1e-3) / 1e9 / peak,
+                                        "bound_actual": "instruction issue of 10 dependent LM steps (DESIGN.md 4.3)"},
                     "refine_fused": {"achieved": B_REFINE * b * N_PIX / (k_ms[2] * 1e-3) / 1e9,
                                      "frac": B_REFINE * b * N_PIX / (k_ms[2] * 1e-3) / 1e9 / peak},
                     "whole_call_225B": {"achieved": B_MATCH_CALL * b * N_PIX / (ms_step * 1e-3) / 1e9,
@@ -266,6 +374,13 @@ def main():
     # Two in-flight steps on two streams (each with its own device buffers): the H2D copy of step
     # k+1 overlaps the kernels of step k.  Every step still moves all of its inputs from pinned host
     # memory and its result back to the host inside the timed region.
+    h2d_gbs = h2d_probe(torch, dev)  # every rank at the same time: what the host side can feed
+    if world > 1:
+        allv = [torch.zeros(1, device=dev, dtype=torch.float64) for _ in range(world)]
+        dist.all_gather(allv, torch.tensor([h2d_gbs], device=dev, dtype=torch.float64))
+        h2d_all = [round(float(v.item()), 2) for v in allv]
+    else:
+        h2d_all = [round(h2d_gbs, 2)]
     host = [t.cpu().pin_memory() for t in (X11, X21, D11, D21)]
     NBUF = 2
     streams = [torch.cuda.Stream(device=dev) for _ in range(NBUF)]
@@ -304,24 +419,73 @@ def main():
     e2e = {"value": world * b * N_PIX / (ms_e2e * 1e-3) / 1e9, "unit": "Gpix/s",
            "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": idx_h[0].numel() * 8 + val_h[0].numel(),
            "ms_per_step": ms_e2e, "call": "mast3r_slam.matching.match_iterative_proj",
-           "pipelining": f"{NBUF} steps in flight on {NBUF} streams (copy of step k+1 overlaps kernels of step k)"}
+           "pipelining": f"{NBUF} steps in flight on {NBUF} streams (copy of step k+1 overlaps kernels of step k)",
+           "h2d_gbs_per_rank": h2d_all, "host_affinity": affinity}
+    floor_ms = in_bytes / (min(h2d_all) * 1e9) * 1e3  # the slowest rank's input copy alone
+    e2e["h2d_copy_floor_ms_per_step"] = floor_ms
+    e2e["bound"] = (f"host memory / PCIe: {in_bytes / 1e6:.0f} MB of inputs per step at {min(h2d_all):.1f}-{max(h2d_all):.1f} "
+                    f"GB/s per rank with {world} rank(s) copying at once = {floor_ms:.2f} ms of the {ms_e2e:.2f} ms step "
+                    f"(kernels: {ms_step:.2f} ms, overlapped)")
     dbuf = dbufs
     del host, dbuf
 
     # ---------------------------------------------------------------- extras: GN rays, tracker
     extra = {}
+    ref = load_reference_cuda() if (world == 1 and not args.no_ref_cuda and not args.no_extra) else None
     if not args.no_extra:
         try:
-            extra.update(bench_gn(be, synth, dev, rank, world, peak, barrier, max_over_ranks))
+            extra.update(bench_gn(be, synth, dev, rank, world, peak, barrier, max_over_ranks, ref=ref))
             if world == 1:
-                extra.update(bench_gn_calib(be, synth, dev))
+                extra.update(bench_gn_calib(be, synth, dev, ref=ref))
                 extra.update(bench_tracker(be, synth, dev, peak))
                 extra.update(bench_frontend(be, synth, dev, peak))
                 extra.update(bench_viewer(be, synth, dev, peak, cpu=not args.no_cpu))
             if not args.no_large:
                 extra.update(bench_gn_large(be, synth, dev, rank, world, peak, barrier, max_over_ranks))
         except Exception as e:  # keep the headline line even if an extra fails
-            extra["error"] = repr(e)
+            import traceback
+            extra["error"] = repr(e) + " | " + traceback.format_exc(limit=3).replace("\n", " / ")
+
+    # ---------------------------------------------------------------- the incumbent, timed beside (N=1)
+    # The UNMODIFIED reference CUDA extension (oracle/_ref, sm_100 build) through the reference's own call
+    # sequence (matching.py:53-90: torch glue around its two kernels) on the same inputs, outside the repo
+    # arm's timed region.  Raw timings of both; the driver's reference arm stays the CPU port (tier rule).
+    reference_cuda = None
+    if ref is not None:
+        try:
+            reference_cuda = bench_reference_cuda_matching(torch, ref, X11, X21, D11, D21, matching, ms_step)
+            for k in ("reference_cuda_gn_rays", "reference_cuda_gn_calib"):
+                if k in extra:
+                    reference_cuda[k[len("reference_cuda_"):]] = extra.pop(k)
+        except Exception as e:
+            reference_cuda = {"error": repr(e)}
+
+    # ---------------------------------------------------------------- GN scaling, where it is parsed
+    scaling_detail = None
+    if "gn_rays" in extra:
+        gr = extra["gn_rays"]
+        scaling_detail = {"n_gpus": world, "gn_rays_iters_per_s": gr["iters_per_s"],
+                          "gn_rays_exchange": "peer-memory (fused into the kernels)" if world > 1 else "none (1 GPU)"}
+        if world > 1:
+            ind = extra["gn_rays_independent_graphs"]
+            one = ind["iters_per_s_aggregate"] / world  # one GPU solving the whole graph, measured in this run
+            nc = extra["gn_rays_nccl_allgather_exchange"]["iters_per_s"]
+            scaling_detail.update({
+                "gn_rays_single_gpu_iters_per_s": one,
+                "gn_rays_sharded_efficiency": gr["iters_per_s"] / (world * one),
+                "gn_rays_nccl_allgather_iters_per_s": nc,
+                "gn_rays_nccl_allgather_efficiency": nc / (world * one),
+                "gn_rays_independent_graphs_iters_per_s": ind["iters_per_s_aggregate"],
+                "gn_rays_sharded_equals_single_gpu": extra.get("gn_rays_sharded_equals_single_gpu")})
+        if "gn_large" in extra:
+            gl = extra["gn_large"]
+            scaling_detail.update({"gn_large_ms_per_iteration": gl["ms_per_iteration"],
+                                   "gn_large_replicated_solve_step_ms": gl["replicated_solve_step_ms"],
+                                   "gn_large_pose_sha256": gl["pose_sha256"],
+                                   "gn_large_sharded_equals_single_gpu":
+                                       gl.get("sharded_equals_single_gpu", {}).get("value")})
+        scaling_detail["matching_e2e_gpix_s"] = e2e["value"]
+        scaling_detail["h2d_gbs_per_rank"] = h2d_all
 
     # ---------------------------------------------------------------- CPU baseline (rank 0, N=1)
     cpu = None
@@ -345,20 +509,72 @@ def main():
             "metric": "dense matching throughput (match_iterative_proj)", "value": value, "unit": "Gpix/s",
             "n_gpus": world, "steps": K, "warmup": W_, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "match_iterative_proj 512x384, iter_proj max_iter 10 + refine_matches "
-                                   "radius 3 dilation 5, 24-d desc (BASELINE configs[1])",
-                       "batch_pairs_per_gpu": b, "l2": f"inputs {in_bytes / 1e6:.0f} MB per step exceed the 126 MB L2",
-                       "parallelism": f"independent frame pairs x{world}"},
+            "config": make_config(b, world),
             "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
-            "cpu_baseline": cpu, "extra": extra}))
+            "cpu_baseline": cpu, "scaling_detail": scaling_detail, "reference_cuda": reference_cuda,
+            "extra": extra}))
     if world > 1:
         dist.destroy_process_group()
 
 
-def bench_gn(be, synth, dev, rank, world, peak, barrier, max_over_ranks):
+def bench_reference_cuda_matching(torch, ref, X11, X21, D11, D21, matching, ours_ms):
+    """The reference's match_iterative_proj (matching.py:53-90, image.py:5-38) over ITS extension."""
+    import torch.nn.functional as F
+
+    b, h, w, _ = X11.shape
+    k = torch.tensor([[-3.0, 0, 3], [-10, 0, 10], [-3, 0, 3]], device=X11.device) / 32.0
+
+    def ref_call():
+        rays = F.normalize(X11, dim=-1).permute(0, 3, 1, 2)
+        c = rays.shape[1]
+        p = F.pad(rays, (1, 1, 1, 1), mode="reflect")
+        gx = F.conv2d(p, k.view(1, 1, 3, 3).repeat(c, 1, 1, 1), groups=c)
+        gy = F.conv2d(p, k.t().contiguous().view(1, 1, 3, 3).repeat(c, 1, 1, 1), groups=c)
+        img = torch.cat((rays, gx, gy), dim=1).permute(0, 2, 3, 1).contiguous()
+        pts = F.normalize(X21.view(b, -1, 3), dim=-1)
+        idx0 = torch.arange(h * w, device=X11.device)[None].repeat(b, 1)
+        p_init = torch.stack((idx0 % w, idx0 // w), -1).float()
+        p1, conv = ref.iter_proj(img, pts, p_init, MATCH["max_iter"], MATCH["lambda_init"], MATCH["convergence_thresh"])
+        p1 = p1.long()
+        bi = torch.arange(b, device=X11.device)[:, None]
+        dist_ = torch.linalg.norm(X11[bi, p1[..., 1], p1[..., 0]] - X21.view(b, -1, 3), dim=-1)
+        valid = conv & (dist_ < MATCH["dist_thresh"])
+        (p1,) = ref.refine_matches(D11.half(), D21.view(b, h * w, -1).half(), p1, MATCH["radius"], MATCH["dilation_max"])
+        return p1[..., 0] + w * p1[..., 1], valid.unsqueeze(-1)
+    ms_ref = _time_gpu(torch, ref_call, 2, 5)
+    ms_ours = _time_gpu(torch, lambda: matching.match_iterative_proj(X11, X21, D11, D21), 2, 5)
+    i_r, v_r = ref_call()
+    i_n, v_n = matching.match_iterative_proj(X11, X21, D11, D21)
+    return {"what": "oracle/_ref/mast3r_slam_backends_ref.so = the unmodified reference extension built for sm_100, "
+                    "timed on the same GPU and inputs through the reference's own call sequence (CUDA events, median of 5)",
+            "matching": {"gpix_s": b * h * w / (ms_ref * 1e-3) / 1e9, "ms_per_call": ms_ref,
+                         "ours_gpix_s": b * h * w / (ms_ours * 1e-3) / 1e9, "ours_ms_per_call": ms_ours,
+                         "ours_ms_per_step_timed_region": ours_ms, "batch_pairs": b,
+                         "idx_agree": float((i_r == i_n).float().mean()), "valid_agree": float((v_r == v_n).float().mean())}}
+
+
+def _time_gpu(torch, fn, warm, reps, setup=None):
+    """CUDA events around `reps` calls (setup outside the timed region, e.g. the pose clone) -> median ms."""
+    ts = []
+    for i in range(warm + reps):
+        args = setup() if setup else ()
+        a = torch.cuda.Event(enable_timing=True); z = torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        a.record()
+        fn(*args)
+        z.record()
+        torch.cuda.synchronize()
+        if i >= warm:
+            ts.append(a.elapsed_time(z))
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
+def bench_gn(be, synth, dev, rank, world, peak, barrier, max_over_ranks, ref=None):
     """BASELINE configs[2]: gauss_newton_rays, 32 keyframes, 100 edges (200 directed), 512x384,
-    10 iterations (delta_thresh 0 so all run).  Single GPU: the drop-in call.  N GPUs: directed
-    edges sharded contiguously, per-edge blocks all-gathered each iteration."""
+    10 iterations (delta_thresh 0 so all run).  Single GPU: the drop-in call, and the same solve over
+    FactorGraph's packed edge store.  N GPUs: directed edges sharded contiguously, per-edge blocks
+    exchanged inside the kernels over NVLink peer memory (and, as the baseline, by an NCCL all-gather)."""
     import torch
     import torch.distributed as dist
 
@@ -366,171 +582,242 @@ def bench_gn(be, synth, dev, rank, world, peak, barrier, max_over_ranks):
     M, n, N = g["M"], H * W, g["N"]
     iters, reps = 10, 5
     out = {}
+    prm = be._params(be.GN_RAYS, 0.003, 10.0, 0.0, 1.5)
+
+    def run_single():
+        T = g["Twc"].clone()
+        be.gauss_newton_rays(T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
+                             0.003, 10.0, 0.0, 1.5, iters, 0.0)
+        return T
     if world == 1:
-        def run():
-            T = g["Twc"].clone()
-            be.gauss_newton_rays(T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
-                                 0.003, 10.0, 0.0, 1.5, iters, 0.0)
-            return T
+        run = run_single
     else:
         e0, cnt, counts = be.shard_edges(M, world, rank)
         e1 = e0 + cnt
-        prm = be._params(be.GN_RAYS, 0.003, 10.0, 0.0, 1.5)
         sl = slice(e0, e1)
         idx_l, val_l, Q_l = g["idx"][sl].contiguous(), g["valid"][sl].contiguous(), g["Q"][sl].contiguous()
+        pk_l = be.edge_pack(idx_l, val_l, Q_l)
 
-        def run(p2p=True):
+        def run(p2p=True, packed=True):
             T = g["Twc"].clone()
-            be.gauss_newton_sharded(prm, T, g["Xs"], g["Cs"], g["ii"], g["jj"], idx_l, val_l, Q_l, e0,
-                                    iters, 0.0, edge_counts=counts, p2p=p2p)
+            if packed:
+                be.gauss_newton_sharded(prm, T, g["Xs"], g["Cs"], g["ii"], g["jj"], pk_l, None, None, e0,
+                                        iters, 0.0, edge_counts=counts, p2p=p2p)
+            else:
+                be.gauss_newton_sharded(prm, T, g["Xs"], g["Cs"], g["ii"], g["jj"], idx_l, val_l, Q_l, e0,
+                                        iters, 0.0, edge_counts=counts, p2p=p2p)
             return T
-    for _ in range(3):
-        run()
-    barrier()
-    a = torch.cuda.Event(enable_timing=True); z = torch.cuda.Event(enable_timing=True)
-    a.record()
-    for _ in range(reps):
-        run()
-    z.record()
-    barrier()
-    ms = max_over_ranks(a.elapsed_time(z)) / reps
-    if world > 1:  # the sharded solve must reproduce the single-GPU poses bit for bit
-        for _ in range(2):
-            run(p2p=False)
+
+    def timed(fn, warm=3):
+        for _ in range(warm):
+            fn()
         barrier()
+        a = torch.cuda.Event(enable_timing=True); z = torch.cuda.Event(enable_timing=True)
         a.record()
         for _ in range(reps):
-            run(p2p=False)
+            fn()
         z.record()
         barrier()
-        ms_nccl = max_over_ranks(a.elapsed_time(z)) / reps
+        return max_over_ranks(a.elapsed_time(z)) / reps
+
+    ms = timed(run)
+    if world > 1:  # the sharded solve must reproduce the single-GPU poses bit for bit
+        ms_nccl = timed(lambda: run(p2p=False), warm=2)
+        ms_ref_layout = timed(lambda: run(packed=False), warm=2)
         out["gn_rays_nccl_allgather_exchange"] = {"iters_per_s": iters / (ms_nccl * 1e-3), "ms_per_solve": ms_nccl}
-        T_nc = run(p2p=False)
-        T_sh = run()
-        T_one = g["Twc"].clone()
-        be.gauss_newton_rays(T_one, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
-                             0.003, 10.0, 0.0, 1.5, iters, 0.0)
-        same = torch.tensor([1 if (torch.equal(T_sh, T_one) and torch.equal(T_nc, T_one)) else 0], device=dev)
+        out["gn_rays_sharded_reference_layout"] = {"iters_per_s": iters / (ms_ref_layout * 1e-3),
+                                                   "ms_per_solve": ms_ref_layout}
+        T_nc, T_sh, T_rl, T_one = run(p2p=False), run(), run(packed=False), run_single()
+        same = torch.tensor([1 if (torch.equal(T_sh, T_one) and torch.equal(T_nc, T_one) and torch.equal(T_rl, T_one))
+                             else 0], device=dev)
         dist.all_reduce(same, op=dist.ReduceOp.MIN)
         out["gn_rays_sharded_equals_single_gpu"] = bool(same.item())
-
         # BASELINE configs[4], second half: independent graphs, one per GPU (no exchange at all)
-        def run_one():
-            T = g["Twc"].clone()
-            be.gauss_newton_rays(T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
-                                 0.003, 10.0, 0.0, 1.5, iters, 0.0)
-        for _ in range(2):
-            run_one()
-        barrier()
-        a.record()
-        for _ in range(reps):
-            run_one()
-        z.record()
-        barrier()
-        ms_ind = max_over_ranks(a.elapsed_time(z)) / reps
+        ms_ind = timed(run_single, warm=2)
         out["gn_rays_independent_graphs"] = {"graphs": world, "iters_per_s_aggregate": world * iters / (ms_ind * 1e-3),
                                              "ms_per_solve": ms_ind}
     out["gn_rays"] = {"workload": "gauss_newton_rays N=32, 200 directed edges, 512x384, 10 iterations "
-                                  "(BASELINE configs[2])" + (f", edge-sharded x{world}, block exchange fused into the "
-                                                             "kernels over NVLink peer memory" if world > 1 else ""),
+                                  "(BASELINE configs[2])" + (f", edge-sharded x{world}, packed edge records, block exchange "
+                                                             "fused into the kernels over NVLink peer memory" if world > 1 else ""),
                       "iters_per_s": iters / (ms * 1e-3), "ms_per_solve": ms}
     if world == 1:
-        # accumulation kernel alone (the HBM-bound part): 45 B per (directed edge, point)
-        prm = be._params(be.GN_RAYS, 0.003, 10.0, 0.0, 1.5)
-        s = be.GNSolver(prm, g["Twc"].clone(), g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"])
-        for _ in range(3):
-            s.accumulate()
-        torch.cuda.synchronize()
-        a.record()
-        for _ in range(10):
-            s.accumulate()
-        z.record()
-        torch.cuda.synchronize()
-        ms_acc = a.elapsed_time(z) / 10
+        # the same solve over FactorGraph's packed two-block store (no prep_two_way_edges copies)
+        E = M // 2
+        pk = be.edge_pack(g["idx"], g["valid"], g["Q"])
+        ii_u, jj_u = g["ii"][:E].contiguous(), g["jj"][:E].contiguous()
+
+        def run_packed():
+            T = g["Twc"].clone()
+            be.gauss_newton_packed(prm, T, g["Xs"], g["Cs"], ii_u, jj_u, pk[:E], pk[E:], iters, 0.0, two_way=True)
+            return T
+        ms_pk = timed(run_packed)
+        out["gn_rays_packed"] = {"workload": "the same solve as FactorGraph.solve_GN_rays runs it: packed 8-byte edge records "
+                                             "in two row blocks, undirected edge list (m3r_gauss_newton_packed)",
+                                 "iters_per_s": iters / (ms_pk * 1e-3), "ms_per_solve": ms_pk,
+                                 "equals_reference_layout_bits": bool(torch.equal(run_packed(), run_single()))}
+        # accumulation kernel alone: 45 B per (directed edge, point) by contract; the packed layout moves 40
+        a = torch.cuda.Event(enable_timing=True); z = torch.cuda.Event(enable_timing=True)
+        res = {}
+        for tag, solver in (("reference_layout", be.GNSolver(prm, g["Twc"].clone(), g["Xs"], g["Cs"], g["ii"], g["jj"],
+                                                             g["idx"], g["valid"], g["Q"])),
+                            ("packed", be.GNSolver(prm, g["Twc"].clone(), g["Xs"], g["Cs"], g["ii"], g["jj"], pk, None, None))):
+            for _ in range(3):
+                solver.accumulate()
+            torch.cuda.synchronize()
+            a.record()
+            for _ in range(10):
+                solver.accumulate()
+            z.record()
+            torch.cuda.synchronize()
+            res[tag] = a.elapsed_time(z) / 10
+            if tag == "packed":
+                a.record()
+                for _ in range(10):
+                    solver.solve_step(0.0)
+                z.record()
+                torch.cuda.synchronize()
+                res["solve_step"] = a.elapsed_time(z) / 10
+        ms_acc = res["packed"]
         ach = B_GN_POINT * M * n / (ms_acc * 1e-3) / 1e9
-        a.record()
-        for _ in range(10):
-            s.solve_step(0.0)
-        z.record()
-        torch.cuda.synchronize()
-        out["gn_rays"].update({"accumulate_ms": ms_acc, "solve_step_ms": a.elapsed_time(z) / 10,
-                               "roofline": {"bound": "hbm", "kernel": "gn_accum_stream_kernel<rays> (+edge finish)",
-                                            "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                                            "algorithmic_bytes_per_edge_point": B_GN_POINT,
-                                            "traffic": ncu_traffic("gn_accum_stream_kernel<rays>")}})
+        out["gn_rays"].update({"accumulate_ms": res["reference_layout"], "accumulate_packed_ms": ms_acc,
+                               "solve_step_ms": res["solve_step"]})
+        out["gn_rays_packed"]["roofline"] = {
+            "bound": "hbm", "kernel": "gn_accum_stream_kernel<rays, packed> (edge epilogue fused)",
+            "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+            "algorithmic_bytes_per_edge_point": B_GN_POINT,
+            "achieved_by_moved_bytes_40B": 40 * M * n / (ms_acc * 1e-3) / 1e9,
+            "frac_by_moved_bytes_40B": 40 * M * n / (ms_acc * 1e-3) / 1e9 / peak,
+            "traffic": ncu_traffic("gn_accum_stream_kernel<rays,packed>"), "traffic_source": ncu_traffic_source(),
+            "note": "frac is ALGORITHMIC bytes (the 45 B contract figure) over time; ncu DRAM traffic is below it because "
+                    "the 100 MB of packed pointmaps are re-hit in the 126 MB L2, and the kernel is issue-bound (BASELINE.md 3)"}
+        ach_r = B_GN_POINT * M * n / (res["reference_layout"] * 1e-3) / 1e9
+        out["gn_rays"]["roofline"] = {"bound": "hbm", "kernel": "gn_accum_stream_kernel<rays> (edge epilogue fused)",
+                                      "achieved": ach_r, "peak": peak, "unit": "GB/s", "frac": ach_r / peak,
+                                      "algorithmic_bytes_per_edge_point": B_GN_POINT,
+                                      "traffic": ncu_traffic("gn_accum_stream_kernel<rays>"),
+                                      "traffic_source": ncu_traffic_source()}
+        if ref is not None:  # the incumbent: the unmodified reference extension on the same inputs, same box
+            def run_ref(T):
+                ref.gauss_newton_rays(T, g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
+                                      0.003, 10.0, 0.0, 1.5, iters, 0.0)
+            ms_ref = _time_gpu(torch, run_ref, 1, 3, setup=lambda: (g["Twc"].clone(),))
+            out["reference_cuda_gn_rays"] = {"iters_per_s": iters / (ms_ref * 1e-3), "ms_per_solve": ms_ref,
+                                             "ours_iters_per_s": iters / (ms * 1e-3), "ours_ms_per_solve": ms}
     return out
 
 
-def bench_gn_calib(be, synth, dev):
+def bench_gn_calib(be, synth, dev, ref=None):
     """BASELINE configs[3]: gauss_newton_calib, 64 keyframes, 200 edges (400 directed), TUM fr1
     intrinsics scaled to 512x384, pixel + log-depth residuals, 10 iterations."""
     import torch
 
     g = synth.make_graph(N=64, counts={1: None, 2: 62, 5: 59, "random": 16}, seed=1237, device=dev)
     Xs = synth.constrain_points_to_ray(g["Xs"], H, W, g["K"])
-    iters, reps = 10, 5
+    iters = 10
 
-    def run():
-        T = g["Twc"].clone()
-        be.gauss_newton_calib(T, Xs, g["Cs"], g["K"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
-                              H, W, -10, 1e-6, 1.0, 10.0, 0.0, 1.5, iters, 0.0)
-    for _ in range(2):
-        run()
-    torch.cuda.synchronize()
-    a = torch.cuda.Event(enable_timing=True); z = torch.cuda.Event(enable_timing=True)
-    a.record()
-    for _ in range(reps):
-        run()
-    z.record()
-    torch.cuda.synchronize()
-    ms = a.elapsed_time(z) / reps
-    return {"gn_calib": {"workload": f"gauss_newton_calib N=64, {g['M']} directed edges, 512x384, 10 iterations "
-                                     "(BASELINE configs[3])", "iters_per_s": iters / (ms * 1e-3),
-                         "ms_per_solve": ms}}
+    def run(mod, T):
+        mod.gauss_newton_calib(T, Xs, g["Cs"], g["K"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"],
+                               H, W, -10, 1e-6, 1.0, 10.0, 0.0, 1.5, iters, 0.0)
+    ms = _time_gpu(torch, lambda T: run(be, T), 2, 5, setup=lambda: (g["Twc"].clone(),))
+    out = {"gn_calib": {"workload": f"gauss_newton_calib N=64, {g['M']} directed edges, 512x384, 10 iterations "
+                                    "(BASELINE configs[3])", "iters_per_s": iters / (ms * 1e-3),
+                        "ms_per_solve": ms}}
+    if ref is not None:
+        ms_ref = _time_gpu(torch, lambda T: run(ref, T), 1, 3, setup=lambda: (g["Twc"].clone(),))
+        out["reference_cuda_gn_calib"] = {"iters_per_s": iters / (ms_ref * 1e-3), "ms_per_solve": ms_ref,
+                                          "ours_iters_per_s": iters / (ms * 1e-3), "ours_ms_per_solve": ms}
+    return out
 
 
 def bench_gn_large(be, synth, dev, rank, world, peak, barrier, max_over_ranks):
     """BASELINE configs[4]: 512 keyframes, 4096 edges (8192 directed), edge-sharded over the ranks;
-    each rank generates only its own edge streams on the device (20.9 GB in total)."""
+    each rank generates only its own edge streams on the device (20.9 GB in total in the reference
+    layout, 12.9 GB as packed records).  Every edge's streams are seeded by its GLOBAL id, so the
+    k-GPU problem is the 1-GPU problem: `pose_sha256` of the final poses is the same string at every
+    N (compare the lines of a scaling run), and `sharded_equals_single_gpu` checks it inside one run
+    at reduced image size (48x64), where a rank can hold the whole problem."""
+    import hashlib
+
     import torch
+    import torch.distributed as dist
 
     N, iters = 512, 3
-    K = synth.intrinsics(H, W, dev)
-    T_gt = synth.make_poses(N, 1238, dev)
-    Xs = synth.render_pointmaps(T_gt, H, W, K)
-    gen = synth._gen(1238 + 7, dev)
-    Cs = (1.0 + torch.exp(0.5 + 0.5 * synth.smooth_noise((N, 1, H, W), 4.0, gen, dev).view(N, H * W, 1))).contiguous()
-    counts = {1: None, 2: None, 3: None, 4: None, 5: None, 6: None, 7: None}
+    counts = {k: None for k in range(1, 8)}
     counts["random"] = 4096 - sum(N - k for k in range(1, 8))
     ii_u, jj_u = synth.make_edges(N, counts, 1238)
     ii_d = torch.cat([ii_u, jj_u]); jj_d = torch.cat([jj_u, ii_u])
     M = ii_d.shape[0]
+    ids = torch.arange(M)
     e0, cnt, ecounts = be.shard_edges(M, world, rank)
-    idx, valid, Q = synth.edge_streams(T_gt, Xs, ii_d[e0:e0 + cnt], jj_d[e0:e0 + cnt], H, W, K, 1238 + 13 + rank)
-    T0 = synth.perturb_poses(T_gt, 1238 + 29)
     prm = be._params(be.GN_RAYS, 0.003, 10.0, 0.0, 1.5)
     ii_g, jj_g = ii_d.to(dev), jj_d.to(dev)
 
+    def problem(h, w):
+        K = synth.intrinsics(h, w, dev)
+        T_gt = synth.make_poses(N, 1238, dev)
+        Xs = synth.render_pointmaps(T_gt, h, w, K)
+        Cs = (1.0 + torch.exp(0.5 + 0.5 * synth.smooth_noise((N, 1, h, w), 4.0 * w / synth.W0, synth._gen(1245, dev), dev)
+                              .view(N, h * w, 1))).contiguous()
+        return K, T_gt, Xs, Cs, synth.perturb_poses(T_gt, 1238 + 29)
+
+    out = {}
+    # correctness at reduced size: sharded (both exchanges) == the single-GPU solve of ALL edges
+    if world > 1:
+        K, T_gt, Xs, Cs, T0 = problem(48, 64)
+        loc = synth.edge_streams(T_gt, Xs, ii_d[e0:e0 + cnt], jj_d[e0:e0 + cnt], 48, 64, K, 1251, edge_ids=ids[e0:e0 + cnt])
+        full = synth.edge_streams(T_gt, Xs, ii_d, jj_d, 48, 64, K, 1251, edge_ids=ids)
+        T_one = T0.clone()
+        be._gauss_newton(prm, T_one, Xs, Cs, ii_g, jj_g, full[0], full[1], full[2], iters, 0.0)
+        ok = True
+        for p2p in (True, False):
+            T = T0.clone()
+            be.gauss_newton_sharded(prm, T, Xs, Cs, ii_g, jj_g, be.edge_pack(*loc), None, None, e0, iters, 0.0,
+                                    edge_counts=ecounts, p2p=p2p)
+            ok = ok and torch.equal(T, T_one) and not torch.equal(T, T0)
+        same = torch.tensor([1 if ok else 0], device=dev)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        out["sharded_equals_single_gpu"] = {"value": bool(same.item()), "size": "N=512, 8192 directed edges, 48x64 images, "
+                                            "3 iterations, peer-memory and NCCL exchange"}
+        del loc, full, Xs, Cs
+    K, T_gt, Xs, Cs, T0 = problem(H, W)
+    idx, valid, Q = synth.edge_streams(T_gt, Xs, ii_d[e0:e0 + cnt], jj_d[e0:e0 + cnt], H, W, K, 1251,
+                                       edge_ids=ids[e0:e0 + cnt])
+    pk = be.edge_pack(idx, valid, Q)
+    del idx, valid, Q
+
     def run():
         T = T0.clone()
-        be.gauss_newton_sharded(prm, T, Xs, Cs, ii_g, jj_g, idx, valid, Q, e0, iters, 0.0, edge_counts=ecounts,
-                                p2p=True)
+        be.gauss_newton_sharded(prm, T, Xs, Cs, ii_g, jj_g, pk, None, None, e0, iters, 0.0, edge_counts=ecounts, p2p=True)
         return T
     run()
     barrier()
     a = torch.cuda.Event(enable_timing=True); z = torch.cuda.Event(enable_timing=True)
     a.record()
-    run()
+    T_fin = run()
     z.record()
     barrier()
     ms = max_over_ranks(a.elapsed_time(z))
     per_iter = ms / iters
-    return {"gn_large": {"workload": f"gauss_newton_rays N=512, {M} directed edges, 512x384, {iters} iterations, "
-                                     f"edge-sharded x{world} (BASELINE configs[4])",
-                         "iters_per_s": iters / (ms * 1e-3), "ms_per_iteration": per_iter,
-                         "edges_per_rank": ecounts,
-                         "algorithmic_GB_per_iteration": B_GN_POINT * M * N_PIX / 1e9,
-                         "achieved_GBps_aggregate_incl_solve": B_GN_POINT * M * N_PIX / (per_iter * 1e-3) / 1e9}}
+    # the replicated part alone: assembly + factorisation + back substitution + retraction
+    peers = be.PeerBlocks.get(M, dev) if world > 1 else None
+    s = be.GNSolver(prm, T0.clone(), Xs, Cs, ii_g, jj_g, pk, None, None, e0, peers=peers)
+    s.accumulate(); s.solve_step(0.0)
+    barrier()
+    a.record()
+    for _ in range(3):
+        s.solve_step(0.0)
+    z.record()
+    barrier()
+    solve_ms = max_over_ranks(a.elapsed_time(z)) / 3
+    out.update({"workload": f"gauss_newton_rays N=512, {M} directed edges, 512x384, {iters} iterations, "
+                            f"edge-sharded x{world}, packed edge records (BASELINE configs[4])",
+                "iters_per_s": iters / (ms * 1e-3), "ms_per_iteration": per_iter,
+                "replicated_solve_step_ms": solve_ms, "accumulate_ms_per_iteration": per_iter - solve_ms,
+                "edges_per_rank": ecounts,
+                "pose_sha256": hashlib.sha256(T_fin.cpu().numpy().tobytes()).hexdigest()[:16],
+                "algorithmic_GB_per_iteration": B_GN_POINT * M * N_PIX / 1e9,
+                "achieved_GBps_aggregate_incl_solve": B_GN_POINT * M * N_PIX / (per_iter * 1e-3) / 1e9})
+    return {"gn_large": out}
 
 
 def bench_tracker(be, synth, dev, peak):

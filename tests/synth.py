@@ -189,9 +189,14 @@ def perturb_poses(T, seed, sig_t=0.01, sig_r=math.radians(1.0), sig_s=0.01):
     return out.float().contiguous()
 
 
-def edge_streams(T_gt, Xs, ii_d, jj_d, H, W, K, seed, chunk=64):
+def edge_streams(T_gt, Xs, ii_d, jj_d, H, W, K, seed, chunk=64, edge_ids=None):
     """Per directed edge (i <- j): idx (M,n) i64 nearest-pixel projection of T_ij Xj into camera i,
-    valid (M,n,1) bool (inside image and depth-consistent within 5 %), Q (M,n,1) f32."""
+    valid (M,n,1) bool (inside image and depth-consistent within 5 %), Q (M,n,1) f32.
+    edge_ids: GLOBAL ids of these directed edges.  With them every edge draws its confidence noise
+    from its own generator (seed, id) and is normalised on its own, so an edge's streams do not
+    depend on which other edges — i.e. which rank's slice — it is generated with: the k-GPU problem
+    IS the 1-GPU problem.  Without (default) the noise comes from one
+    generator in chunks, as the committed golden fixtures were made."""
     device = Xs.device
     gen = _gen(seed, device)
     M, n = ii_d.shape[0], Xs.shape[1]
@@ -212,7 +217,13 @@ def edge_streams(T_gt, Xs, ii_d, jj_d, H, W, K, seed, chunk=64):
         idx[s:s + chunk] = torch.where(ok, lin, torch.zeros_like(lin))
         valid[s:s + chunk, :, 0] = ok
         B = i.shape[0]
-        qn = smooth_noise((B, 1, H, W), 4.0 * W / W0, gen, device).view(B, n)
+        if edge_ids is None:
+            qn = smooth_noise((B, 1, H, W), 4.0 * W / W0, gen, device).view(B, n)
+        else:
+            x = torch.stack([torch.randn((1, H, W), generator=_gen(int(seed) * 1000003 + int(e), device), device=device)
+                             for e in edge_ids[s:s + chunk]])
+            x = _blur(x, 4.0 * W / W0).view(B, n)
+            qn = x / x.std(dim=1, keepdim=True).clamp_min(1e-6)
         Q[s:s + chunk, :, 0] = 1.0 + torch.exp(0.7 + 0.5 * qn)
     return idx, valid, Q
 
