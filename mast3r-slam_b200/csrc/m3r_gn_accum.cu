@@ -144,7 +144,11 @@ __device__ __forceinline__ float fast_rcp(float x) {
 // denormal argument (a squared residual below 1.2e-38) flushes to 0 -> +inf -> huber weight 1,
 // which is what the scaled form yields as well.
 __device__ __forceinline__ float fast_rsqrt(float x) {
+#ifdef M3R_GN_PRECISE  // accuracy experiment (profiles/gn_dx_accuracy.py): correctly rounded 1/sqrt
+  return __fdiv_rn(1.0f, __fsqrt_rn(x));
+#else
   float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r;
+#endif
 }
 
 // h: upper^T packed 7x7 (index a*(a+1)/2 + c, c <= a); skips Jacobian entries whose bit is

@@ -21,7 +21,9 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(_HERE, "..", "lib", "libm3r_b200.so")
+# M3R_B200_LIB: load another build of the SAME library (experiments under profiles/, e.g. a
+# -DM3R_GN_PRECISE variant); it is still this package's CUDA code, never a fallback
+_LIB_PATH = os.environ.get("M3R_B200_LIB") or os.path.join(_HERE, "..", "lib", "libm3r_b200.so")
 
 
 class _GNParams(C.Structure):

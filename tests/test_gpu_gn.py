@@ -103,7 +103,7 @@ def test_solve_vs_oracle(backends, orc, mode):
     assert dx.shape == (g["N"] - 1, 7) and dx.dtype == torch.float32
     dT = np.abs(_np(Twc) - T_o).max()
     print(f"{mode}: final pose diff vs oracle {dT:.2e}, last |dx| {np.abs(_np(dx)).max():.2e}")
-    assert dT < 5e-5
+    assert dT < DX_ATOL  # measured 1e-7 .. 5e-7 (48x64 images)
     assert np.array_equal(_np(Twc)[0], _np(g["Twc"])[0])  # gauge pose untouched
     # the solve moved towards the ground truth (nearest-pixel correspondences bound how close)
     e0 = np.abs(_np(g["Twc"]) - _np(g["T_gt"])).max()
@@ -142,7 +142,7 @@ def test_solve_vs_reference(backends, ref_ext, mode):
     T_n, dx_n = run(backends, 10)
     dT = float((T_r - T_n).abs().max())
     print(f"{mode}: final pose diff vs reference after 10 iterations {dT:.2e}")
-    assert dT < 5e-5
+    assert dT < DX_ATOL  # north_star: within 1e-5; measured 1e-7 .. 4e-7 at 96x128 (full size: test_gpu_gn_full.py)
 
 
 def test_rays_full_size_vs_reference_and_properties(backends, ref_ext):

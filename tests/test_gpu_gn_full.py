@@ -57,30 +57,84 @@ def _run(mod, g, calib, iters, T=None):
     return T, out[0]
 
 
+def _exact_sum_dx(orc, g, calib, T_start):
+    """dx of ONE iteration as the reference would return it if its sums did not round: the oracle's
+    restatement of the reference's per-point fp32 arithmetic (oracle/m3r_oracle.c, gn_kernels.cu:880-1138 /
+    1300-1543) accumulated in fp64, assembled and solved in fp64 (SparseBlock semantics, :71-153)."""
+    if calib:
+        oprm = orc.make_params(orc.MODE_CALIB, 1.0, 10.0, 0.0, 1.5, _np(g["K"]), H, W, -10, 1e-6)
+    else:
+        oprm = orc.make_params(orc.MODE_RAYS, 0.003, 10.0, 0.0, 1.5)
+    _, ie, je, io, jo = orc.edge_rows(_np(g["ii"]), _np(g["jj"]))
+    _, _, Hs64, gs64 = orc.gn_blocks(oprm, _np(T_start), _np(g["Xs"]), _np(g["Cs"]), ie, je, _np(g["idx"]),
+                                     _np(g["valid"]), _np(g["Q"]), want64=True)
+    nfree = g["N"] - 1
+    A, b = np.zeros((7 * nfree, 7 * nfree)), np.zeros(7 * nfree)
+    for e in range(g["M"]):
+        i, j = int(io[e]), int(jo[e])
+        si, sj = slice(7 * i, 7 * i + 7), slice(7 * j, 7 * j + 7)
+        if i >= 0:
+            A[si, si] += Hs64[0, e]; b[si] += gs64[0, e]
+        if j >= 0:
+            A[sj, sj] += Hs64[3, e]; b[sj] += gs64[1, e]
+        if i >= 0 and j >= 0:
+            A[si, sj] += Hs64[1, e]; A[sj, si] += Hs64[2, e]
+    return (-np.linalg.solve(A, b)).reshape(nfree, 7), float(np.linalg.cond(A))
+
+
 @pytest.mark.parametrize("config", [3, 4])
-def test_baseline_config_vs_reference_every_iteration(backends, ref_ext, config):
+def test_baseline_config_vs_reference_every_iteration(backends, ref_ext, orc, config):
     """N = 32 / 200 directed edges rays and N = 64 / 400 calib at 512x384, 10 iterations, against the
-    reference extension (gn_kernels.cu:1140-1228, 1546-1638): dx of EVERY iteration (a k-iteration
-    call returns dx_k) and the final poses within 1e-5; and the packed-layout call is bit-identical."""
+    reference extension (gn_kernels.cu:1140-1228, 1546-1638).
+
+    Every iteration is compared FROM THE SAME POSES (the reference's own trajectory), so that what is
+    measured is one iteration's arithmetic and not the divergence of two trajectories.  Bars:
+      * final poses of the two independent 10-iteration solves within 1e-5 (north_star)  [measured 1-4e-7];
+      * dx_k within 1e-5 of the reference for every k — EXCEPT where the reference itself is further than
+        that from its own exactly-summed result.  The normal equations here have condition numbers of
+        1e5..1e6, and the reference's fp32 block reductions (119 of them per edge over 196 608 points,
+        gn_kernels.cu:1096-1112) move its first dx by 1.9e-5 (rays) / 5.5e-5 (calib) away from the dx of the
+        SAME per-point arithmetic summed in fp64; this library lands within 5e-7 of that exact-sum dx
+        (profiles/r3/r3b_gn_dx_accuracy.json; IEEE instead of MUFU rsqrt changes nothing, ..._ieee_rsqrt.json).
+        For the first three iterations (where |dx| is above the 1e-5 bar at all) the test therefore asserts
+        |dx_ours - dx_exact| < 1e-5 and |dx_ours - dx_ref| < 1e-5 + 1.5 |dx_ref - dx_exact|.
+    The packed-layout call must be bit-identical to the reference-layout call."""
     if ref_ext is None:
         pytest.skip("oracle/_ref not built")
     g, calib = _graph(config)
     assert g["M"] == (200 if config == 3 else 400) and g["Xs"].shape[1] == H * W
-    worst_dx, worst_T, dxs = 0.0, 0.0, []
+    rows, T_start = [], g["Twc"].clone()
     for k in range(1, 11):
-        T_r, dx_r = _run(ref_ext, g, calib, k)
-        T_n, dx_n = _run(backends, g, calib, k)
-        d = float((dx_r - dx_n).abs().max())
-        dT = float((T_r - T_n).abs().max())
-        dxs.append(dict(iteration=k, dx_max_abs_diff=d, dx_max_abs=float(dx_r.abs().max()), pose_max_abs_diff=dT))
-        worst_dx, worst_T = max(worst_dx, d), max(worst_T, dT)
+        T_r, dx_r = _run(ref_ext, g, calib, 1, T_start.clone())
+        T_n, dx_n = _run(backends, g, calib, 1, T_start.clone())
+        row = dict(iteration=k, dx_max_abs=float(dx_r.abs().max()), ours_vs_ref=float((dx_r - dx_n).abs().max()),
+                   pose_after_step_diff=float((T_r - T_n).abs().max()))
+        if k <= 3:
+            dx_x, cond = _exact_sum_dx(orc, g, calib, T_start)
+            row.update(cond=cond, ours_vs_exact_sum=float(np.abs(_np(dx_n) - dx_x).max()),
+                       ref_vs_exact_sum=float(np.abs(_np(dx_r) - dx_x).max()))
+        rows.append(row)
+        T_start = T_r   # follow the reference
+    T_r, _ = _run(ref_ext, g, calib, 10)
+    T_n, dx_n = _run(backends, g, calib, 10)
+    final = float((T_r - T_n).abs().max())
     moved = float((T_n - g["Twc"]).abs().max())
-    _record(f"gn_config{config}_vs_reference", dict(config=config, N=g["N"], directed_edges=g["M"], per_iteration=dxs,
-                                                     pose_max_abs_update=moved, bars=dict(dx=DX_ATOL, pose=POSE_ATOL)))
-    print(f"config {config}: worst |dx_k - reference| {worst_dx:.2e}, worst pose diff {worst_T:.2e}, moved {moved:.2e}")
+    _record(f"gn_config{config}_vs_reference", dict(config=config, N=g["N"], directed_edges=g["M"], per_iteration=rows,
+                                                     final_pose_max_abs_diff=final, pose_max_abs_update=moved,
+                                                     bars=dict(dx=DX_ATOL, pose=POSE_ATOL)))
+    for r in rows:
+        print(f"config {config} it {r['iteration']}: |dx| {r['dx_max_abs']:.2e} ours-ref {r['ours_vs_ref']:.2e}"
+              + (f" ours-exact {r['ours_vs_exact_sum']:.2e} ref-exact {r['ref_vs_exact_sum']:.2e} cond {r['cond']:.1e}"
+                 if "cond" in r else ""))
+    print(f"config {config}: final pose diff {final:.2e}, moved {moved:.2e}")
     assert moved > 1e-3                      # the solve did something
-    assert worst_dx < DX_ATOL
-    assert worst_T < POSE_ATOL
+    assert final < POSE_ATOL
+    for r in rows:
+        if "ours_vs_exact_sum" in r:
+            assert r["ours_vs_exact_sum"] < DX_ATOL, r
+            assert r["ours_vs_ref"] < DX_ATOL + 1.5 * r["ref_vs_exact_sum"], r
+        else:
+            assert r["ours_vs_ref"] < DX_ATOL, r
     # packed layout (FactorGraph's storage): same arithmetic, same reduction order => same bits
     pk = backends.edge_pack(g["idx"], g["valid"], g["Q"])
     prm = (backends._params(backends.GN_CALIB, 1.0, 10.0, 0.0, 1.5, g["K"], H, W, -10, 1e-6) if calib
@@ -229,7 +283,7 @@ def test_factor_graph_solves_through_the_mirror_class(backends, ref_ext, calib):
     torch.cuda.synchronize()
     d = float((T_after - T_exp).abs().max())
     print(f"FactorGraph.solve_GN_{'calib' if calib else 'rays'} vs {'reference' if ref_ext is not None else 'entry point'}: {d:.2e}")
-    assert d < 5e-5   # 96x128 images: 16x fewer points than full size, conditioning as in test_solve_vs_reference
+    assert d < POSE_ATOL   # measured 1.2e-7
     assert float((T_after - g["Twc"]).abs().max()) > 1e-3            # poses moved and were written back
     pin = cfg["pin"]
     assert torch.equal(store.T_WC[ids[:pin], 0], T_before[ids[:pin], 0])  # pinned keyframes untouched
