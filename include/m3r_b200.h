@@ -37,7 +37,8 @@ enum {
   M3R_OK = 0,
   M3R_EINVAL = -1,    /* bad shape / null pointer / unsupported parameter */
   M3R_ELAUNCH = -2,   /* CUDA launch or runtime error (see m3r_last_cuda_error) */
-  M3R_EWORKSPACE = -3 /* workspace too small */
+  M3R_EWORKSPACE = -3, /* workspace too small */
+  M3R_ETOOLARGE = -4   /* size beyond the fixed maximum of a *_noalloc entry point */
 };
 
 /* Residual family of a Gauss-Newton accumulation pass. */
@@ -323,6 +324,22 @@ int m3r_track_ray_dist(const float* Xf, const float* Xk, const float* Qk,
                        float huber_k, int max_iters, float rel_error, float delta_norm,
                        float* T_CkCf, int* status, float* cost, void* workspace,
                        size_t workspace_bytes, m3r_stream_t stream);
+
+/* m3r_track_ray_dist for callers that cannot allocate device memory (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  It has NO counterpart in the
+ * reference.  Same arguments, arithmetic and
+ * results as m3r_track_ray_dist, minus the workspace: the per-CTA partial sums live in a static
+ * device array inside the library (85 248 bytes, held by every GPU that loads the library until
+ * the process exits), and the call performs no cudaMalloc / cudaFree / allocating library call.
+ * Limits: n <= M3R_TRACK_NOALLOC_MAX_N points and a device of at most 296 SMs, otherwise
+ * M3R_ETOOLARGE and nothing is launched.  All calls on one device share the array: calls that
+ * overlap on the GPU (two streams) race — serialise them on one stream or with events.  Nothing
+ * in the array needs to start at zero and it keeps the last call's partials. */
+#define M3R_TRACK_NOALLOC_MAX_N (1 << 22) /* 4 194 304 points = a 2048 x 2048 pointmap */
+int m3r_track_ray_dist_noalloc(const float* Xf, const float* Xk, const float* Qk,
+                               const uint8_t* valid, int n, float sigma_ray, float sigma_dist,
+                               float huber_k, int max_iters, float rel_error, float delta_norm,
+                               float* T_CkCf, int* status, float* cost, m3r_stream_t stream);
 
 /* Calibrated twin: FrameTracker.opt_pose_calib_sim3 (tracker.py:216-266 with
  * geometry.project_calib, geometry.py:63-104): residuals [u - u_k, v - v_k, log z - log z_k]

@@ -14,6 +14,7 @@ extern "C" const char* m3r_error_string(int code) {
     case M3R_EINVAL: return "invalid argument (shape, null pointer or unsupported parameter)";
     case M3R_ELAUNCH: return "CUDA launch/runtime error";
     case M3R_EWORKSPACE: return "workspace too small";
+    case M3R_ETOOLARGE: return "size beyond the fixed maximum of a no-allocation entry point (see include/m3r_b200.h)";
     default: return "unknown error";
   }
 }

@@ -341,3 +341,57 @@ extern "C" int m3r_track_calib(const float* Xf, const float* meas_k, const float
   a.T = T_CkCf; a.status = status; a.cost = cost; a.part = static_cast<float*>(workspace);
   return track_launch(kTrkCalib, a, workspace_bytes, as_stream(stream));
 }
+
+// ---------------------------------------------------------------------------------
+// m3r_track_ray_dist_noalloc — the same solve for callers that cannot allocate (CUDA graph
+// capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The per-CTA partial sums, the only scratch of
+// the tracker kernel, live in a file-scope device array instead of a caller workspace:
+// 2 x kTrkStaticCtas x 36 floats = 85 248 bytes, held by every GPU that loads the library until
+// the process exits.  Nothing in it has to start at zero (every partial an iteration reads was
+// written by that iteration, before the grid barrier), so the array is never cleared.  All calls
+// on a device share it: two calls that overlap on the GPU (different streams) race.
+// ---------------------------------------------------------------------------------
+namespace m3r {
+constexpr int kTrkStaticCtas = 2 * kNumSMs;  // one CTA per SM is launched; room for a 296-SM part
+static __device__ __align__(256) float g_trk_static_part[2 * kTrkStaticCtas * kTrkVals];
+
+// Device address of the array on the CURRENT device.  In host code `g_trk_static_part` is only a
+// handle for the runtime, not a device address: it must go through cudaGetSymbolAddress, once
+// per device, with that device current.
+static int trk_static_scratch(float** out) {
+  static std::atomic<float*> cache[kMaxDevices];
+  int dev = 0;
+  M3R_TRY(check_cuda(cudaGetDevice(&dev)));
+  std::atomic<float*>* slot = (dev >= 0 && dev < kMaxDevices) ? &cache[dev] : nullptr;
+  float* p = slot ? slot->load() : nullptr;
+  if (!p) {
+    M3R_TRY(check_cuda(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_trk_static_part)));
+    if (!p) return M3R_ELAUNCH;
+    if (slot) slot->store(p);
+  }
+  *out = p;
+  return M3R_OK;
+}
+}  // namespace m3r
+
+extern "C" int m3r_track_ray_dist_noalloc(const float* Xf, const float* Xk, const float* Qk,
+                                          const uint8_t* valid, int n, float sigma_ray,
+                                          float sigma_dist, float huber_k, int max_iters,
+                                          float rel_error, float delta_norm, float* T_CkCf,
+                                          int* status, float* cost, m3r_stream_t stream) {
+  if (n <= 0 || max_iters < 0 || !Xf || !Xk || !Qk || !valid || !T_CkCf || !status) return M3R_EINVAL;
+  if (sigma_ray == 0.f || sigma_dist == 0.f) return M3R_EINVAL;
+  if (n > M3R_TRACK_NOALLOC_MAX_N) return M3R_ETOOLARGE;
+  if (track_grid_size(kTrkRays) > kTrkStaticCtas) return M3R_ETOOLARGE;  // a GPU with > 296 SMs
+  float* part = nullptr;
+  M3R_TRY(trk_static_scratch(&part));
+  TrackArgs a;
+  a.Xf = Xf; a.Xk = Xk; a.Qk = Qk; a.valid = valid; a.n = n;
+  a.inv_var_ray = (float)(1.0 / ((double)sigma_ray * sigma_ray));
+  a.inv_var_dist = (float)(1.0 / ((double)sigma_dist * sigma_dist));
+  a.huber_k = huber_k; a.max_iters = max_iters; a.rel_error = rel_error; a.delta_norm = delta_norm;
+  a.T = T_CkCf; a.status = status; a.cost = cost; a.part = part;
+  a.valid_meas = nullptr; a.K = nullptr;
+  return track_launch(kTrkRays, a, sizeof(g_trk_static_part), as_stream(stream));
+}

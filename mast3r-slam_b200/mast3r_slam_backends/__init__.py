@@ -68,6 +68,7 @@ EXPORTS = [
     "m3r_render_resolve",
     "m3r_gn_status", "m3r_gn_prepare_two_way", "m3r_gn_accumulate_packed", "m3r_gauss_newton_packed",
     "m3r_edge_build_packed", "m3r_edge_pack", "m3r_edge_unpack",
+    "m3r_track_ray_dist_noalloc",
 ]
 
 
@@ -113,6 +114,7 @@ def _load():
     lib.m3r_track_workspace_bytes.argtypes = [i32]
     lib.m3r_track_ray_dist.argtypes = [vp, vp, vp, vp, i32, f32, f32, f32, i32, f32, f32, vp, vp,
                                        vp, vp, sz, vp]
+    lib.m3r_track_ray_dist_noalloc.argtypes = [vp, vp, vp, vp, i32, f32, f32, f32, i32, f32, f32, vp, vp, vp, vp]
     lib.m3r_track_calib.argtypes = [vp, vp, vp, vp, vp, i32, vp, i32, i32, i32, f32,
                                     f32, f32, f32, i32, f32, f32, vp, vp, vp, vp, sz, vp]
     pp = C.POINTER(_GNPeers)
@@ -693,6 +695,27 @@ def track_ray_dist(Xf, Xk, Qk, valid, T_CkCf, sigma_ray, sigma_dist, huber_k, ma
                                        float(rel_error), float(delta_norm), _ptr(T), _ptr(status),
                                        _ptr(cost), _ptr(ws), nbytes, _stream(Xf)), "track_ray_dist")
     return (status, cost) if want_cost else status
+
+
+TRACK_NOALLOC_MAX_N = 1 << 22
+ETOOLARGE = -4
+
+
+def track_ray_dist_noalloc(Xf, Xk, Qk, valid, T_CkCf, status, sigma_ray, sigma_dist, huber_k, max_iters,
+                           rel_error, delta_norm, cost=None, n=None):
+    """m3r_track_ray_dist_noalloc: track_ray_dist for callers that cannot allocate.  The caller
+    passes every output (`status` (4,) i32, optionally `cost` (max_iters,) f32); the scratch is a
+    static device array inside the library, so neither this wrapper nor the call allocates device
+    memory.  No counterpart in the reference.
+    -> the C return code (0 ok, ETOOLARGE beyond TRACK_NOALLOC_MAX_N points); other errors raise.
+    Calls that overlap on one GPU share the scratch and race."""
+    n = int(Xf.shape[0]) if n is None else int(n)
+    rc = _lib.m3r_track_ray_dist_noalloc(_ptr(Xf), _ptr(Xk), _ptr(Qk), _ptr(valid), n, float(sigma_ray),
+                                         float(sigma_dist), float(huber_k), int(max_iters), float(rel_error),
+                                         float(delta_norm), _ptr(T_CkCf), _ptr(status), _ptr(cost), _stream(Xf))
+    if rc not in (0, ETOOLARGE):
+        _check(rc, "track_ray_dist_noalloc")
+    return rc
 
 
 def track_calib(Xf, meas_k, Qk, valid, valid_meas_k, K, img_size, T_CkCf, sigma_pixel, sigma_depth,
