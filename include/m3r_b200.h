@@ -307,6 +307,14 @@ void m3r_debug_chol_trace(unsigned long long* device_buf, int capacity_tasks);
  * delay_us <= 0 switches it off (default). */
 void m3r_debug_chol_delay(int delay_us, int which);
 
+/* Diagnostics / tests: systems of more than 16 panels of 32 (more than ~74 keyframes) are
+ * factorised in 64x64 macro tiles by a kernel whose work is a statically ordered task list
+ * (csrc/m3r_gn_chol64.cu).  This returns that list for `nbm` 64-wide block columns, built on the
+ * host by the same enumeration the device runs: 4 ints per task {I | J << 16, k0 | k1 << 16,
+ * kind (0 chunk update, 1 final = last chunk + TRSM), chunk index}.  Returns the task count
+ * (-1 if the enumeration and the workspace formula disagree); writes at most `capacity` tasks. */
+int m3r_debug_chol64_tasklist(int nbm, int* out, int capacity);
+
 /* ------------------------------------------------------------------------- *
  * Two-frame tracker solve
  * ------------------------------------------------------------------------- */

@@ -728,7 +728,9 @@ static int gn_prepare_impl(const float* Xs, const float* Cs, const int64_t* ii, 
   const int grid = (int)((count + 255) / 256 < (size_t)(kNumSMs * 16) ? (count + 255) / 256
                                                                        : (size_t)(kNumSMs * 16));
   gn_pack_kernel<<<grid, 256, 0, st>>>(Xs, Cs, count, ws_ptr<float4>(workspace, L.xc));
-  return after_launch();
+  M3R_TRY(after_launch());
+  if (L.nbm) return gn_chol64_prepare(workspace, L, st);  // task list of the macro-tile Cholesky
+  return M3R_OK;
 }
 
 extern "C" int m3r_gn_prepare(const float* Xs, const float* Cs, const int64_t* ii,

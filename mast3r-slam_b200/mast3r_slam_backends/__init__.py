@@ -68,7 +68,7 @@ EXPORTS = [
     "m3r_render_resolve",
     "m3r_gn_status", "m3r_gn_prepare_two_way", "m3r_gn_accumulate_packed", "m3r_gauss_newton_packed",
     "m3r_edge_build_packed", "m3r_edge_pack", "m3r_edge_unpack",
-    "m3r_track_ray_dist_noalloc",
+    "m3r_track_ray_dist_noalloc", "m3r_debug_chol64_tasklist",
 ]
 
 
@@ -114,6 +114,7 @@ def _load():
     lib.m3r_track_workspace_bytes.argtypes = [i32]
     lib.m3r_track_ray_dist.argtypes = [vp, vp, vp, vp, i32, f32, f32, f32, i32, f32, f32, vp, vp,
                                        vp, vp, sz, vp]
+    lib.m3r_debug_chol64_tasklist.argtypes = [i32, vp, i32]
     lib.m3r_track_ray_dist_noalloc.argtypes = [vp, vp, vp, vp, i32, f32, f32, f32, i32, f32, f32, vp, vp, vp, vp]
     lib.m3r_track_calib.argtypes = [vp, vp, vp, vp, vp, i32, vp, i32, i32, i32, f32,
                                     f32, f32, f32, i32, f32, f32, vp, vp, vp, vp, sz, vp]

@@ -22,7 +22,13 @@ for _ in range(3):
     s.accumulate(); s.solve_step(0.0)
 torch.cuda.synchronize()
 nb = (7 * (N - 1) + 1 + 31) // 32
-cap = nb * (nb + 1) // 2 + nb
+big = nb > 16  # macro-tile kernel (m3r_gn_chol64.cu): slots = chain steps, then list tasks, then back tasks
+if big:
+    nbm = (7 * (N - 1) + 1 + 63) // 64
+    nb = 2 * nbm
+    cap = nbm + be._lib.m3r_debug_chol64_tasklist(nbm, None, 0) + nb
+else:
+    cap = nb * (nb + 1) // 2 + nb
 buf = torch.zeros((cap, 4), dtype=torch.int64, device=dev)
 be._lib.m3r_debug_chol_trace(buf.data_ptr(), cap)
 s.accumulate()
@@ -35,13 +41,26 @@ t = buf.cpu().numpy()
 t0 = t[t[:, 1] > 0, 1].min()
 lines = [f"N={N} nb={nb} solve_step {a.elapsed_time(z) * 1e3:.1f} us (event); kernel span "
          f"{(t[:, 3].max() - t0) / 1e3:.1f} us"]
-kinds = {0: "potrf", 1: "trsm ", 2: "back "}
+kinds = {0: "potrf", 1: "trsm ", 2: "back ", 3: "chunk"}
+if big:  # summary by kind: busy time between inputs-ready and end, and waiting before it
+    tt = t[t[:, 3] > 0]
+    for k, name in kinds.items():
+        sel = tt[(tt[:, 0] >> 32) == k]
+        if len(sel):
+            lines.append(f"{name}: {len(sel)} tasks, work {((sel[:, 3] - sel[:, 2]).sum()) / 1e3:.0f} us total "
+                         f"(mean {((sel[:, 3] - sel[:, 2]).mean()) / 1e3:.2f}), wait for inputs "
+                         f"{((sel[:, 2] - sel[:, 1]).sum()) / 1e3:.0f} us total (mean {((sel[:, 2] - sel[:, 1]).mean()) / 1e3:.2f})")
+    pot = tt[(tt[:, 0] >> 32) == 0]
+    lines.append(f"factorisation span {(pot[:, 3].max() - t0) / 1e3:.1f} us; back substitution "
+                 f"{(tt[:, 3].max() - pot[:, 3].max()) / 1e3:.1f} us")
 order = sorted(range(cap), key=lambda r: t[r, 3])
 for r in order:
     if t[r, 3] == 0:
         continue
     k, i, j = int(t[r, 0] >> 32), int((t[r, 0] >> 16) & 0xFFFF), int(t[r, 0] & 0xFFFF)
-    if nb > 16 and not (k != 1 or i == j + 1):
+    if big and (k == 3 or (k == 1 and i > j + 2) or (k == 2 and i % 8)):
+        continue
+    if (not big) and nb > 16 and not (k != 1 or i == j + 1):
         continue
     lines.append(f"{kinds[k]} ({i:3d},{j:3d}) begin {(t[r, 1] - t0) / 1e3:8.2f}  ready {(t[r, 2] - t0) / 1e3:8.2f}  "
                  f"end {(t[r, 3] - t0) / 1e3:8.2f}  work {(t[r, 3] - t[r, 2]) / 1e3:6.2f} us")
