@@ -43,19 +43,62 @@ __device__ __forceinline__ bool gn_stopped(const GnHeader* hdr) {
 // ---- large systems: 64x64 macro tiles (m3r_gn_chol64.cu) ----------------------------------
 // A system of more than kGnSmallMaxNb 32-wide panels is padded to a multiple of 64 and
 // factorised by the macro-tile kernel.  The left-looking sum of tile (I,J) over block columns
-// k is cut into chunks of kGnKC block columns; every chunk is one task.  Chunk counts per tile,
-// shared by the host (workspace size) and the device (task list, progress counters):
+// k is cut into chunks; every chunk is one task.  A tile's list tasks cover k in [0, R) and the
+// chunks are laid out FROM THE END: a tail of `t` block columns (the chunk released last, one
+// or two chain steps before the tile is needed, is short), then chunks of kGnKC going down;
+// the partial chunk is the first.  Because R depends on the tile column, the chunk boundaries of
+// neighbouring columns are staggered and the chain releases work evenly (with boundaries at
+// multiples of 4 everywhere, every fourth chain step released ~400 tasks ahead of the urgent ones).
+//   diagonal tile (J,J):       R = J-2, t = 2; the chain CTA adds k = J-2 and k = J-1 itself
+//   sub-diagonal tile (J+1,J): R = J-1, t = 2; the chain CTA adds k = J-1 itself
+//   any other tile (I >= J+2): R = J-1, t = 4; k = J-1 is alone in the tile's final (TRSM) task
+// Shared by the host (workspace size) and the device (task list, progress counters).
 constexpr int kGnSmallMaxNb = 16;
 constexpr int kGnMB = 64;
 constexpr int kGnKC = 4;
+constexpr int kGnTailChain = 2;
 __host__ __device__ inline int gn_cdiv(int a, int b) { return (a + b - 1) / b; }
-// diagonal tile (J,J): bulk tasks sum k in [0, J-1); the chain adds k = J-1 privately
-__host__ __device__ inline int gn_nch_diag(int J) { return J >= 2 ? gn_cdiv(J - 1, kGnKC) : 0; }
-// sub-diagonal tile (J+1,J): chunks of [0, J-1) and the single k = J-1 on its own (the chain
-// waits for that one, so it must not drag three other products with it)
-__host__ __device__ inline int gn_nch_sub(int J) { return (J >= 1 ? 1 : 0) + gn_nch_diag(J); }
-// any other tile (I >= J+2): chunks of [0, J); the last one is merged into the tile's TRSM task
-__host__ __device__ inline int gn_ntask_other(int J) { return J >= 1 ? gn_cdiv(J, kGnKC) : 1; }
+// Chunk ends of [0, R), walking down from R: the tail t, then kGnRecent / kGnKC chunks of kGnKC,
+// then chunks of kGnKCOld.  The recent chunks are released one at a time as the chain advances;
+// the old ones are all available when the tile's column enters the task list's window and are
+// released TOGETHER — their subtractions from the tile are serialised by the progress counter, so
+// they are few and long (with chunks of 4 everywhere a column's tiles spent 30 % of their CTA time
+// waiting for their turn).
+constexpr int kGnRecent = 8;
+constexpr int kGnKCOld = 16;
+__host__ __device__ inline int gn_chunk_step(int d) { return d < kGnRecent ? kGnKC : kGnKCOld; }  // d = R - t - end
+__host__ __device__ inline int gn_nch(int R, int t) {
+  if (R <= 0) return 0;
+  int n = 1;
+  for (int e = R - t, d = 0; e > 0; n++) { const int st = gn_chunk_step(d); e -= st; d += st; }
+  return n;
+}
+// is e the end of a chunk of a tile with range [0, R) and tail t; its start and index if so
+__host__ __device__ inline bool gn_chunk_end(int R, int t, int e) {
+  if (R <= 0 || e <= 0 || e > R) return false;
+  if (e == R) return true;
+  for (int c = R - t, d = 0; c > 0;) {
+    if (c == e) return true;
+    if (c < e) return false;
+    const int st = gn_chunk_step(d); c -= st; d += st;
+  }
+  return false;
+}
+__host__ __device__ inline int gn_chunk_k0(int R, int t, int e) {
+  const int k0 = e == R ? R - t : e - gn_chunk_step(R - t - e);
+  return k0 > 0 ? k0 : 0;
+}
+__host__ __device__ inline int gn_chunk_index(int R, int t, int e) {
+  int above = 0;  // chunk ends above e
+  if (e != R) {
+    above = 1;
+    for (int c = R - t, d = 0; c > e;) { const int st = gn_chunk_step(d); c -= st; d += st; above++; }
+  }
+  return gn_nch(R, t) - 1 - above;
+}
+__host__ __device__ inline int gn_nch_diag(int J) { return gn_nch(J - 2, kGnTailChain); }
+__host__ __device__ inline int gn_nch_sub(int J) { return gn_nch(J - 1, kGnTailChain); }
+__host__ __device__ inline int gn_ntask_other(int J) { return gn_nch(J - 1, kGnKC) + 1; }
 inline int gn_chol64_ntasks(int nbm) {
   long long t = 0;
   for (int J = 0; J < nbm; J++) {

@@ -47,7 +47,7 @@ constexpr int kStageD = 2 * kPanel;
 constexpr int kTileC = MB * LDC;
 constexpr int kWindow = 8;         // block columns ahead of the chain whose tiles are kept up to date
 constexpr int kMaxSlots = 4096;    // (nbm + 1) * (kWindow + 1) sort groups of the task list
-constexpr int kChainTiles = 3;
+constexpr int kChainTiles = 6;  // T, X, Lp, Tn, Xn, Y of the chain CTA
 constexpr size_t kSmemDoubles =
     (size_t)kStages * kStageD > (size_t)kChainTiles * kTileC ? (size_t)kStages * kStageD : (size_t)kChainTiles * kTileC;
 constexpr size_t kSmemBytes = kSmemDoubles * sizeof(double);
@@ -74,24 +74,19 @@ __host__ __device__ inline int queue_index(int nbm) { return 2 * nbm * nbm + 2 *
 template <class F>
 __host__ __device__ __forceinline__ void tasks_ending_at(int nbm, int J, int e, F&& f) {
   if (e > J) return;
-  if (e == 0) {
-    if (J == 0)
-      for (int I = 2; I < nbm; I++) f(I, 0, 0, (int)kTaskFinal, 0);
-    return;
+  // chain tiles (their last terms are the chain's own)
+  if (gn_chunk_end(J - 2, kGnTailChain, e))
+    f(J, gn_chunk_k0(J - 2, kGnTailChain, e), e, (int)kTaskUpdate, gn_chunk_index(J - 2, kGnTailChain, e));
+  if (J + 1 < nbm && gn_chunk_end(J - 1, kGnTailChain, e))
+    f(J + 1, gn_chunk_k0(J - 1, kGnTailChain, e), e, (int)kTaskUpdate, gn_chunk_index(J - 1, kGnTailChain, e));
+  // the other tiles of the column
+  if (gn_chunk_end(J - 1, kGnKC, e)) {
+    const int k0 = gn_chunk_k0(J - 1, kGnKC, e), kc = gn_chunk_index(J - 1, kGnKC, e);
+    for (int I = J + 2; I < nbm; I++) f(I, k0, e, (int)kTaskUpdate, kc);
   }
-  const bool reg = (e % kGnKC) == 0;
-  if (e <= J - 1 && (reg || e == J - 1)) {  // chunks of [0, J-1): diagonal and sub-diagonal tile
-    const int kc = (e - 1) / kGnKC, k0 = kc * kGnKC;
-    f(J, k0, e, (int)kTaskUpdate, kc);
-    if (J + 1 < nbm) f(J + 1, k0, e, (int)kTaskUpdate, kc);
-  } else if (e == J && J + 1 < nbm) {       // the sub-diagonal tile's last term, alone
-    f(J + 1, J - 1, J, (int)kTaskUpdate, gn_nch_diag(J));
-  }
-  if (e < J && reg) {
-    for (int I = J + 2; I < nbm; I++) f(I, e - kGnKC, e, (int)kTaskUpdate, e / kGnKC - 1);
-  } else if (e == J) {
-    const int kc = (J - 1) / kGnKC;
-    for (int I = J + 2; I < nbm; I++) f(I, kc * kGnKC, J, (int)kTaskFinal, kc);
+  if (e == J) {  // the last term and the TRSM
+    const int kc = gn_nch(J - 1, kGnKC), k0 = J > 0 ? J - 1 : 0;
+    for (int I = J + 2; I < nbm; I++) f(I, k0, J, (int)kTaskFinal, kc);
   }
 }
 
@@ -104,15 +99,27 @@ __host__ __device__ __forceinline__ void tasks_of_group(int nbm, int v, int J, F
   }
 }
 
+struct TaskCount {
+  int n;
+  __host__ __device__ void operator()(int, int, int, int, int) { n++; }
+};
+struct TaskEmit {
+  int4* tasks; int ntasks, J, o;
+  __host__ __device__ void operator()(int I, int k0, int k1, int kind, int kc) {
+    if (o < ntasks) tasks[o] = make_int4(I | (J << 16), k0 | (k1 << 16), kind, kc);
+    o++;
+  }
+};
+
 __global__ void __launch_bounds__(1024)
 chol64_tasklist_kernel(int nbm, int ntasks, int4* __restrict__ tasks) {
   __shared__ int offs[kMaxSlots];
   const int nslots = (nbm + 1) * (kWindow + 1);
   for (int s = threadIdx.x; s < nslots; s += blockDim.x) {
     const int v = s / (kWindow + 1), J = v + s % (kWindow + 1);
-    int cnt = 0;
-    if (J < nbm) tasks_of_group(nbm, v, J, [&](int, int, int, int, int) { cnt++; });
-    offs[s] = cnt;
+    TaskCount cnt{0};
+    if (J < nbm) tasks_of_group(nbm, v, J, cnt);
+    offs[s] = cnt.n;
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -124,11 +131,8 @@ chol64_tasklist_kernel(int nbm, int ntasks, int4* __restrict__ tasks) {
   for (int s = threadIdx.x; s < nslots; s += blockDim.x) {
     const int v = s / (kWindow + 1), J = v + s % (kWindow + 1);
     if (J >= nbm) continue;
-    int o = offs[s];
-    tasks_of_group(nbm, v, J, [&](int I, int k0, int k1, int kind, int kc) {
-      if (o < ntasks) tasks[o] = make_int4(I | (J << 16), k0 | (k1 << 16), kind, kc);
-      o++;
-    });
+    TaskEmit emit{tasks, ntasks, J, offs[s]};
+    tasks_of_group(nbm, v, J, emit);
   }
 }
 
@@ -201,12 +205,19 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src)
   const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
 }
+__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gmem_src) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gmem_src) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // team barrier: exactly the 128 threads of team `t` (warps 4t..4t+3)
 __device__ __forceinline__ void team_sync(int t) { asm volatile("bar.sync %0, 128;" ::"r"(1 + t) : "memory"); }
+// one-way barrier over all 256 threads: the arriving team does not wait for the waiting one
+__device__ __forceinline__ void cta_arrive(int id) { asm volatile("bar.arrive %0, 256;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ void cta_wait(int id) { asm volatile("bar.sync %0, 256;" ::"r"(id) : "memory"); }
 
 template <int LD>
 struct TileLd {
@@ -272,6 +283,91 @@ __device__ __forceinline__ void potrf64(double* T, int g0, int D, double* dinv, 
   __syncthreads();
 }
 
+// POTRF of the 32x32 block at the top of a 64x32 panel AND the TRSM of the 32 rows below it, in
+// one pass of potrf_team's loop: lane r owns rows r and 32 + r.  Row 32 + r goes through the same
+// 4-column steps as a row below the current diagonal block (solve against the 4x4 block, rank-4
+// update of the columns to the right), so the panel below is finished when the factor is — the
+// separate T10 <- T10 L00^-T (1.4 us per block column on the critical path) disappears.  Same
+// operation order per element as potrf_team / trsm_team.
+template <class Tile>
+__device__ __forceinline__ void rank4_rows2(const Tile s, int r, int p0, int jj0, const double (&x)[4],
+                                            const double (&x2)[4], double (&t)[4], double (&t2)[4]) {
+  double v[4][4];
+#pragma unroll
+  for (int u = 0; u < 4; u++) {
+#pragma unroll
+    for (int k = 0; k < 4; k++) v[u][k] = s(jj0 + u, p0 + k);
+    t[u] = s(r, jj0 + u);
+    t2[u] = s(32 + r, jj0 + u);
+  }
+#pragma unroll
+  for (int u = 0; u < 4; u++) {
+#pragma unroll
+    for (int k = 0; k < 4; k++) { t[u] = fma(-x[k], v[u][k], t[u]); t2[u] = fma(-x2[k], v[u][k], t2[u]); }
+  }
+#pragma unroll
+  for (int u = 0; u < 4; u++) {
+    if (jj0 + u <= r) s(r, jj0 + u) = t[u];
+    s(32 + r, jj0 + u) = t2[u];
+  }
+}
+
+template <class Tile, class Sync>
+__device__ __forceinline__ void potrf_tall_team(const Tile s, int w, int g0, int D, double* __restrict__ dinv,
+                                                GnHeader* hdr, Sync sync) {
+  const int r = threadIdx.x & 31;
+  double x[4] = {0.0, 0.0, 0.0, 0.0}, cur[4] = {0.0, 0.0, 0.0, 0.0};      // row r
+  double x2[4] = {0.0, 0.0, 0.0, 0.0}, cur2[4] = {0.0, 0.0, 0.0, 0.0};    // row 32 + r
+  if (w == 0) {
+#pragma unroll
+    for (int j = 0; j < 4; j++) { cur[j] = s(r, j); cur2[j] = s(32 + r, j); }
+  }
+#pragma unroll 1
+  for (int c0 = 0; c0 < NB; c0 += 4) {
+    if (w == 0) {
+      double b[4][4], rr[4];
+#pragma unroll
+      for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j <= i; j++) b[i][j] = s(c0 + i, c0 + j);
+      const bool fail = factor4(b, rr, g0 + c0, D);
+      if (r == 0) {
+        if (fail) hdr->chol_fail = 1;
+#pragma unroll
+        for (int j = 0; j < 4; j++) dinv[c0 + j] = rr[j];
+      }
+      const int i = r - c0;
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        double v = cur[j], v2 = cur2[j];
+#pragma unroll
+        for (int k = 0; k < j; k++) { v = fma(-x[k], b[j][k], v); v2 = fma(-x2[k], b[j][k], v2); }
+        x[j] = v * rr[j];
+        x2[j] = v2 * rr[j];
+        if (i == j) x[j] = b[j][j];
+        if (i < j) x[j] = 0.0;
+      }
+      if (i >= 0) {
+#pragma unroll
+        for (int j = 0; j < 4; j++) s(r, c0 + j) = x[j];
+      }
+#pragma unroll
+      for (int j = 0; j < 4; j++) s(32 + r, c0 + j) = x2[j];
+    }
+    sync();
+    if (w == 0) {
+      if (c0 + 4 < NB) rank4_rows2(s, r, c0, c0 + 4, x, x2, cur, cur2);
+      __syncwarp();
+    } else {
+      double xw[4], xw2[4], t[4], t2[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) { xw[k] = s(r, c0 + k); xw2[k] = s(32 + r, c0 + k); }
+#pragma unroll 1
+      for (int jj = c0 + 8 + 4 * (w - 1); jj < NB; jj += 12) rank4_rows2(s, r, c0, jj, xw, xw2, t, t2);
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // Bulk tasks: one chunk of a tile's left-looking sum, and (kTaskFinal) the tile's TRSM
 // ------------------------------------------------------------------------------------------
@@ -285,13 +381,22 @@ __device__ __forceinline__ void issue_stage(const Args& a, int I, int J, int kco
   }
 }
 
+// publish by the LAST warp: its ~1 us fence then overlaps the next task's queue pop and flag polls,
+// which are warp 0's
+__device__ __forceinline__ void post_flag_last(int* f, int value) {
+  __syncthreads();
+  if (threadIdx.x == kThreads - 1) { __threadfence(); st_release(f, value); }
+}
+
 __device__ __forceinline__ void run_task(const Args& a, const int4 tk, int epoch, double* smem, double* s_dinv,
-                                         int slot) {
+                                         int slot, int* s_task) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, q = lane & 3;
   const int wr = warp >> 2, wc = warp & 3;
   const int I = tk.x & 0xffff, J = tk.x >> 16, k0 = tk.y & 0xffff, k1 = tk.y >> 16, kind = tk.z, kc = tk.w;
   chol_debug_stall(a.c, I, J, epoch, 0);
   const unsigned long long t_begin = a.c.trace ? gtimer() : 0ull;
+  // (Drawing the NEXT list entry here, to hide the atomic's round trip, was tried: an urgent entry
+  // then sits behind its holder's current task, up to 48 us — chain stalls of 50-70 us.)
   // inputs: L(I,k) and L(J,k) for every block column of the chunk
   if (tid < 2 * (k1 - k0)) {
     const int* f = tile_flag(a, (tid & 1) ? J : I, k0 + (tid >> 1));
@@ -332,7 +437,8 @@ __device__ __forceinline__ void run_task(const Args& a, const int4 tk, int epoch
         }
     }
     chol_debug_stall(a.c, I, J, epoch, 1);
-    post_flag(prog_flag(a, I, J), (epoch << 12) | (kc + 1));
+    if (tid == 0) *s_task = atomicAdd(a.c.flags + queue_index(a.nbm), 1);
+    post_flag_last(prog_flag(a, I, J), (epoch << 12) | (kc + 1));
     trace_put(a.c, slot, 3, I, J, t_begin, t_ready);
     return;
   }
@@ -356,106 +462,379 @@ __device__ __forceinline__ void run_task(const Args& a, const int4 tk, int epoch
   trsm64(X, Ls, s_dinv);
   chol_debug_stall(a.c, I, J, epoch, 1);
   store_tile64(a.c.A, a.c.Dp, I, J, X);
-  post_flag(tile_flag(a, I, J), epoch);
+  if (tid == 0) *s_task = atomicAdd(a.c.flags + queue_index(a.nbm), 1);
+  post_flag_last(tile_flag(a, I, J), epoch);
   trace_put(a.c, slot, 1, I, J, t_begin, t_diag);
 }
 
 // ------------------------------------------------------------------------------------------
-// The chain: diagonal tiles and the sub-diagonal tile of every block column, one CTA
+// The chain: diagonal tiles and the sub-diagonal tile of every block column, one CTA.
+//
+// One step, J >= 1.  In shared memory: T = tile (J,J) with its bulk chunks (k < J-1) applied,
+// X = tile (J,J-1) with ALL its terms applied, Lp = L(J-1,J-1) from the previous step.
+//   all 8 warps   X <- X Lp^-T                      (trsm64: X is L(J,J-1) now)
+//   all 8 warps   T00 -= X0 X0^T, T10 -= X1 X0^T    (what POTRF(T00) and the TRSM of T10 need)
+//   team 0 (warps 0-3)                  | team 1 (warps 4-7)
+//     POTRF(T00)                        |   publish L(J,J-1); T11 -= X1 X1^T
+//     T10 <- T10 L00^-T                 |   fetch Tn = tile (J+1,J+1) and Xn = tile (J+1,J), bulk chunks applied
+//     ---- barrier ----                 |   ---- barrier ----
+//     T11 -= T10 T10^T                  |   fetch Y = L(J+1,J-1) as soon as its owner has flagged it
+//     POTRF(T11), publish L(J,J)        |   Xn -= Y X^T   (the last term of the next sub-diagonal tile)
+// The publishing (32 KB store, fence, flag), the loads of the next step's tiles and, above all, the
+// last term of the next sub-diagonal tile — which as a list task sat on the critical path with two
+// flag hops, an L2 round trip of the tile and a cold 2-step pipeline (16 us per step instead of
+// the 14 the arithmetic needs) — run beside the two POTRFs, which keep only four warps busy.
 // ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void team_wait(const int* f, int value, int team) {
+  if ((threadIdx.x & 127) == 0) while (ld_acquire(f) != value) __nanosleep(20);
+  team_sync(team);
+}
+__device__ __forceinline__ void team_load_tile64(const double* __restrict__ A, int Dp, int bi, int bj, double* s) {
+  const double* src = A + (size_t)bi * MB * Dp + (size_t)bj * MB;
+  for (int idx = threadIdx.x & 127; idx < MB * MB / 2; idx += 128) {
+    const int r = idx >> 5, c2 = (idx & 31) * 2;
+    const double2 v = __ldcg(reinterpret_cast<const double2*>(src + (size_t)r * Dp + c2));
+    s[r * LDC + c2] = v.x; s[r * LDC + c2 + 1] = v.y;
+  }
+}
+// the calling team stores the shared tile to global tile (bi,bj) and raises `flag`
+__device__ __forceinline__ void team_publish_tile64(double* __restrict__ A, int Dp, int bi, int bj, const double* s,
+                                                    int* flag, int epoch, int team) {
+  double* dst = A + (size_t)bi * MB * Dp + (size_t)bj * MB;
+  for (int idx = threadIdx.x & 127; idx < MB * MB; idx += 128) __stcg(dst + (size_t)(idx >> 6) * Dp + (idx & 63), s[(idx >> 6) * LDC + (idx & 63)]);
+  team_sync(team);
+  if ((threadIdx.x & 127) == 0) { __threadfence(); st_release(flag, epoch); }
+}
+
+// diagnostics: a trace entry written by the calling thread (team 1's timeline inside a chain step)
+__device__ __forceinline__ void trace_put3(const CholArgs& c, int slot, int kind, int i, int j,
+                                           unsigned long long t0, unsigned long long t1, unsigned long long t2) {
+  if (c.trace && slot < c.trace_cap) {
+    unsigned long long* p = c.trace + 4 * (size_t)slot;
+    p[0] = ((unsigned long long)kind << 32) | ((unsigned long long)i << 16) | (unsigned long long)j;
+    p[1] = t0; p[2] = t1; p[3] = t2;
+  }
+}
+
 __device__ __forceinline__ void run_chain(const Args& a, int epoch, double* smem, double* s_dinv) {
-  const int warp = threadIdx.x >> 5, wr = warp >> 2, wc = warp & 3;
+  const int tid = threadIdx.x, warp = tid >> 5, team = warp >> 2, w = warp & 3;
   double* T = smem;
   double* X = smem + kTileC;
   double* Lp = smem + 2 * kTileC;
+  double* Tn = smem + 3 * kTileC;
+  double* Xn = smem + 4 * kTileC;
+  double* Y = smem + 5 * kTileC;
   double* dT = s_dinv;
   double* dP = s_dinv + MB;
+  load_tile64(a.c.A, a.c.Dp, 0, 0, T);
+  __syncthreads();
   for (int J = 0; J < a.nbm; J++) {
     chol_debug_stall(a.c, J, J, epoch, 0);
     const unsigned long long t_begin = a.c.trace ? gtimer() : 0ull;
-    const int nd = gn_nch_diag(J);
-    if (nd) wait_flag(prog_flag(a, J, J), (epoch << 12) | nd);
-    load_tile64(a.c.A, a.c.Dp, J, J, T);
-    unsigned long long t_ready = t_begin;
     if (J > 0) {
-      const int ns = gn_nch_sub(J - 1);
-      if (ns) wait_flag(prog_flag(a, J, J - 1), (epoch << 12) | ns);
-      if (a.c.trace) t_ready = gtimer();
-      load_tile64(a.c.A, a.c.Dp, J, J - 1, X);
-      __syncthreads();
       trsm64(X, Lp, dP);
-      store_tile64(a.c.A, a.c.Dp, J, J - 1, X);
-      post_flag(tile_flag(a, J, J - 1), epoch);  // L(J,J-1) for the rest of block column J
-      double acc[4][2][2];
-      zero_acc(acc);
-      if (!(wc * 16 > wr * 32 + 31)) {  // T -= X X^T, lower fragments only
-        warp_mma<4, 2, LDC>(X + wr * 32 * LDC, X + wc * 16 * LDC, 4, acc);
-        sub_acc_smem(T, wr * 32, wc * 16, acc);
+      {  // T00 -= X0 X0^T (warps 0-3), T10 -= X1 X0^T (warps 4-7); 16x16 outputs per warp
+        const int r0 = team * 32 + (w >> 1) * 16, c0 = (w & 1) * 16;
+        double acc[2][2][2];
+        zero_acc(acc);
+        warp_mma<2, 2, LDC>(X + r0 * LDC, X + c0 * LDC, 4, acc);
+        sub_acc_smem(T, r0, c0, acc);
+      }
+      __syncthreads();
+    }
+    const unsigned long long t_ready = a.c.trace ? gtimer() : 0ull;
+    if (team == 0) {
+      potrf_tall_team(TileC{T}, w, J * MB, a.c.D, dT, a.c.hdr, [] { team_sync(0); });  // L00 and T10 <- T10 L00^-T
+      team_sync(0);
+      const unsigned long long p1 = a.c.trace ? gtimer() : 0ull;
+      const unsigned long long p2 = p1;
+      cta_wait(3);  // (1) team 1 has finished T11 -= X1 X1^T (it arrived and went on)
+      {                 // T11 -= T10 T10^T, 16x16 outputs per warp
+        const int r0 = 32 + (w >> 1) * 16, c0 = 32 + (w & 1) * 16;
+        double acc[2][2][2];
+        zero_acc(acc);
+        warp_mma<2, 2, LDC>(T + r0 * LDC, T + c0 * LDC, 2, acc);
+        sub_acc_smem(T, r0, c0, acc);
+      }
+      team_sync(0);
+      const unsigned long long p3 = a.c.trace ? gtimer() : 0ull;
+      potrf_team(TileC{T + 32 * LDC + 32}, w, J * MB + 32, a.c.D, dT + 32, a.c.hdr, [] { team_sync(0); });
+      team_sync(0);
+      if (tid == 0) {  // team 0's timeline: POTRF(T00) done, TRSM(T10) done, T11 updated | .., POTRF(T11) done
+        const int base = a.nbm + a.ntasks + 4 * a.nbm;
+        trace_put3(a.c, base + 2 * J, 6, J, J, p1, p2, p3);
+        trace_put3(a.c, base + 2 * J + 1, 7, J, J, p3, gtimer(), gtimer());
+      }
+      chol_debug_stall(a.c, J, J, epoch, 1);
+      if (tid < MB) a.c.x[a.c.Dp + J * MB + tid] = dT[tid];
+      // L(J,J) and 1/diag.  The fence stalls its warp for ~1 us: by now team 0 only waits for team 1.
+      team_publish_tile64(a.c.A, a.c.Dp, J, J, T, tile_flag(a, J, J), epoch, 0);
+    } else {
+      if (J > 0) {
+        team_publish_tile64(a.c.A, a.c.Dp, J, J - 1, X, tile_flag(a, J, J - 1), epoch, 1);  // L(J,J-1)
+        const int r0 = 32 + (w >> 1) * 16, c0 = 32 + (w & 1) * 16;  // T11 -= X1 X1^T
+        double acc[2][2][2];
+        zero_acc(acc);
+        warp_mma<2, 2, LDC>(X + r0 * LDC, X + c0 * LDC, 4, acc);
+        sub_acc_smem(T, r0, c0, acc);
+      }
+      cta_arrive(3);  // (1) team 0 may touch T11 now; this team does not wait for it
+      const unsigned long long q0 = a.c.trace ? gtimer() : 0ull;
+      unsigned long long q1 = q0, q2 = q0, q3 = q0, q4 = q0;
+      if (J + 1 < a.nbm) {  // the next step's tiles, as soon as their bulk chunks are in
+        const int nd = gn_nch_diag(J + 1), ns = gn_nch_sub(J);
+        if ((tid & 127) == 0) {
+          if (nd) while (ld_acquire(prog_flag(a, J + 1, J + 1)) != ((epoch << 12) | nd)) __nanosleep(20);
+          if (ns) while (ld_acquire(prog_flag(a, J + 1, J)) != ((epoch << 12) | ns)) __nanosleep(20);
+          if (J > 0) while (ld_acquire(tile_flag(a, J + 1, J - 1)) != epoch) __nanosleep(20);
+        }
+        team_sync(1);
+        if (a.c.trace) q1 = gtimer();
+        // three tiles in flight at once (8-byte cp.async: the rows of a chain tile are 8-byte aligned only;
+        // each of these lines is read once per launch by this SM, right after an acquire)
+        for (int idx = tid & 127; idx < MB * MB; idx += 128) {
+          const int rr = idx >> 6, cc = idx & 63;
+          cp_async8(Tn + rr * LDC + cc, a.c.A + (size_t)((J + 1) * MB + rr) * a.c.Dp + (J + 1) * MB + cc);
+          cp_async8(Xn + rr * LDC + cc, a.c.A + (size_t)((J + 1) * MB + rr) * a.c.Dp + J * MB + cc);
+          if (J > 0) cp_async8(Y + rr * LDC + cc, a.c.A + (size_t)((J + 1) * MB + rr) * a.c.Dp + (J - 1) * MB + cc);
+        }
+        cp_async_commit();
+        cp_async_wait<0>();
+        team_sync(1);
+        if (a.c.trace) q2 = q3 = q4 = gtimer();
+        // The last terms of the next step's two tiles, with Y = L(J+1,J-1) and X = L(J,J-1) in shared memory:
+        //   Xn -= Y X^T (k = J-1 of tile (J+1,J)),  Tn -= Y Y^T (k = J-1 of tile (J+1,J+1), lower blocks).
+        // 14 blocks of 32x16 outputs on THREE warps: the fourth (warp 4) shares its scheduler and fp64
+        // pipe with warp 0, whose POTRF is the critical path of the whole factorisation — with DMMA
+        // streams on all four sub-partitions POTRF(T11) took 7.2 us instead of 4.
+        if (J > 0 && w > 0) {
+#pragma unroll 1
+          for (int blk = w - 1; blk < 14; blk += 3) {
+            int r0, c0; const double* Bop; double* Cout;
+            if (blk < 8) { r0 = (blk >> 2) * 32; c0 = (blk & 3) * 16; Bop = X; Cout = Xn; }
+            else { const int t = blk - 8; r0 = t < 2 ? 0 : 32; c0 = t < 2 ? t * 16 : (t - 2) * 16; Bop = Y; Cout = Tn; }
+            double acc[4][2][2];
+            zero_acc(acc);
+            warp_mma<4, 2, LDC>(Y + r0 * LDC, Bop + c0 * LDC, 4, acc);
+            sub_acc_smem(Cout, r0, c0, acc);
+          }
+        }
+      }
+      if (tid == 128) {  // team 1's timeline: barrier (1), diagonal chunks in, sub-diagonal chunks in | Y wanted, Y flagged, done
+        const int base = a.nbm + a.ntasks + 2 * a.nbm;
+        trace_put3(a.c, base + 2 * J, 4, J, J, q0, q1, q2);
+        trace_put3(a.c, base + 2 * J + 1, 5, J, J, q3, q4, gtimer());
       }
     }
-    __syncthreads();
-    potrf64(T, J * MB, a.c.D, dT, a.c.hdr);
-    chol_debug_stall(a.c, J, J, epoch, 1);
-    store_tile64(a.c.A, a.c.Dp, J, J, T);
-    if (threadIdx.x < MB) a.c.x[a.c.Dp + J * MB + threadIdx.x] = dT[threadIdx.x];
-    post_flag(tile_flag(a, J, J), epoch);
+    __syncthreads();  // (2)
     trace_put(a.c, J, 0, J, J, t_begin, t_ready);
-    double* t = T; T = Lp; Lp = t;
+    double* t = Lp; Lp = T; T = Tn; Tn = t;
+    t = X; X = Xn; Xn = t;
     t = dT; dT = dP; dP = t;
   }
 }
 
 // ------------------------------------------------------------------------------------------
-// Back substitution L^T x = y (y^T = row D of L), 32 columns per task, tasks dealt round robin:
+// Back substitution L^T x = y (y^T = row D of L), 64 columns per step:
 //   x_c = L_cc^-T ( y_c - sum_{m>c} L_mc^T x_m ),  entries with global index >= D are 0.
+// The 32-column form dealt round robin took 0.40 ms at N = 512: 112 steps, each a flag hop, an L2
+// round trip for x_m and a fence.  Here the dependent chain — the last kBackNear terms of the sum
+// and the 64-step triangular solve — stays in ONE CTA (block 0): x lives in its shared memory, the
+// tiles it needs next are in flight (registers) while it solves.  The far part of every column's
+// sum, m > c + kBackNear, is the work of a helper CTA per column that follows the chain kBackNear
+// steps behind, so its flag is normally up when the chain arrives.  Fixed summation order.
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ void back_task(const Args& a, int c, int epoch, double* smem, int slot) {
-  constexpr int kParts = kThreads / 32, kRows = NB / kParts;
-  const int tid = threadIdx.x, t = tid & 31, part = tid >> 5;
-  const int nb = a.c.nb;
-  double (*sA)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(smem);
-  double* sx = smem + NB * (NB + 1);
-  double* sred = sx + NB;
+constexpr int kBackNear = 3;
+__device__ __forceinline__ int* far_flag(const Args& a, int c) { return a.c.flags + 2 * a.nbm * a.nbm + a.nbm + c; }
+__device__ __forceinline__ int* winv_flag(const Args& a, int c) { return a.c.flags + queue_index(a.nbm) + 1 + c; }
+
+// Helper of column c.  (i) Inverts the two 32x32 diagonal blocks of L(c,c): W^T = L^-T goes into the
+// strictly upper part of the block in the factor (unused otherwise; its diagonal is 1/diag(L), kept
+// in x[Dp..]) — with it the chain's 64-step dependent triangular solve becomes three 32x32
+// matrix-vector products.  (ii) far_c = sum_{m > c + kBackNear} L(m,c)^T x_m -> x[2 Dp + 64 c ..].
+// Then far_flag(c).
+__device__ __forceinline__ void back_far(const Args& a, int c, int epoch, double* smem, double* s_dinv, int slot) {
+  const int tid = threadIdx.x, j = tid & 63, p = tid >> 6;  // column j of the tile, rows 16p .. 16p+15
+  const int m_lo = c + kBackNear + 1;
   const unsigned long long t_begin = a.c.trace ? gtimer() : 0ull;
-  // the last diagonal tile depends, transitively, on every tile of the factor
-  wait_flag(tile_flag(a, a.nbm - 1, a.nbm - 1), epoch);
-  double s = 0.0;
-  for (int m = nb - 1; m > c; m--) {
-    wait_flag(x_flag(a, m), epoch);
-    if (tid < NB) sx[tid] = __ldcg(a.c.x + m * NB + tid);
+  {
+    const int team = tid >> 7, lt = tid & 127, w = lt >> 5, off = 32 * team;  // team t inverts block (t,t)
+    double* Lt = smem;
+    double* Ws = smem + kTileC + team * 32 * LDC;
+    load_tile64(a.c.A, a.c.Dp, c, c, Lt);
+    if (tid < MB) s_dinv[tid] = __ldcg(a.c.x + a.c.Dp + c * MB + tid);
+    for (int idx = lt; idx < 32 * 32; idx += 128) Ws[(idx >> 5) * LDC + (idx & 31)] = (idx >> 5) == (idx & 31) ? 1.0 : 0.0;
     __syncthreads();
-    const double* Lmc = a.c.A + (size_t)m * NB * a.c.Dp + (size_t)c * NB;
-#pragma unroll
-    for (int r = part * kRows; r < part * kRows + kRows; r++)
-      s = fma(__ldcg(Lmc + (size_t)r * a.c.Dp + t), sx[r], s);
+    trsm_team(TileC{Ws}, TileC{Lt + off * LDC + off}, s_dinv + off, w, [team] { team_sync(team); });
+    team_sync(team);
+    double* dst = a.c.A + (size_t)(c * MB + off) * a.c.Dp + (size_t)c * MB + off;
+    for (int idx = lt; idx < 32 * 32; idx += 128) {
+      const int r = idx >> 5, cc = idx & 31;
+      if (cc > r) __stcg(dst + (size_t)r * a.c.Dp + cc, Ws[r * LDC + cc]);
+    }
+    post_flag(winv_flag(a, c), epoch);
     __syncthreads();
   }
   const unsigned long long t_ready = a.c.trace ? gtimer() : 0ull;
-  if (part > 0) sred[(part - 1) * NB + t] = s;
-  {
-    const double* src = a.c.A + (size_t)c * NB * a.c.Dp + (size_t)c * NB;
-    for (int idx = tid; idx < NB * NB; idx += kThreads) sA[idx >> 5][idx & 31] = __ldcg(src + (size_t)(idx >> 5) * a.c.Dp + (idx & 31));
-  }
-  __syncthreads();
-  if (tid < NB) {
-    const int gi = c * NB + t;
-    double tot = s;
+  if (m_lo <= a.nbm - 1) {
+    double* xs = smem;
+    double* sred = smem + MB;
+    double cur[16], nxt[16], s = 0.0;
+    auto fetch = [&](int m, double (&v)[16]) {
+      const double* T = a.c.A + (size_t)(m * MB + p * 16) * a.c.Dp + (size_t)c * MB + j;
 #pragma unroll
-    for (int pp = 1; pp < kParts; pp++) tot += sred[(pp - 1) * NB + t];
-    double rhs = (gi < a.c.D) ? __ldcg(a.c.A + (size_t)a.c.D * a.c.Dp + gi) - tot : 0.0;
-    const double dinv = __ldcg(a.c.x + a.c.Dp + gi);
-    double xo = 0.0;
+      for (int r = 0; r < 16; r++) v[r] = __ldcg(T + (size_t)r * a.c.Dp);
+    };
+    fetch(a.nbm - 1, cur);
+    for (int m = a.nbm - 1; m >= m_lo; m--) {
+      if (m - 1 >= m_lo) fetch(m - 1, nxt);
+      if (tid == 0) while (ld_acquire(a.c.flags + 2 * a.nbm * a.nbm + m) != epoch) { }
+      __syncthreads();
+      if (tid < MB) xs[tid] = __ldcg(a.c.x + m * MB + tid);
+      __syncthreads();
 #pragma unroll
-    for (int k = NB - 1; k >= 0; k--) {
-      double xk = __shfl_sync(0xffffffffu, rhs * dinv, k);
-      if (c * NB + k >= a.c.D) xk = 0.0;
-      if (t == k) xo = xk;
-      if (t < k) rhs = fma(-sA[k][t], xk, rhs);
+      for (int r = 0; r < 16; r++) s = fma(cur[r], xs[p * 16 + r], s);
+#pragma unroll
+      for (int r = 0; r < 16; r++) cur[r] = nxt[r];
     }
-    a.c.x[gi] = xo;
+    sred[p * MB + j] = s;
+    __syncthreads();
+    if (tid < MB) a.c.x[2 * a.c.Dp + c * MB + tid] = (sred[tid] + sred[MB + tid]) + (sred[2 * MB + tid] + sred[3 * MB + tid]);
+    post_flag(far_flag(a, c), epoch);
   }
-  post_flag(x_flag(a, c), epoch);
-  trace_put(a.c, slot, 2, c, c, t_begin, t_ready);
+  trace_put(a.c, slot, 2, c, 0, t_begin, t_ready);
+}
+
+__device__ __forceinline__ void back_chain(const Args& a, int epoch, double* smem, int slot0) {
+  const int tid = threadIdx.x, j = tid & 63, p = tid >> 6, lane = tid & 31;
+  const int nbm = a.nbm, Dp = a.c.Dp, D = a.c.D;
+  double* xr = smem;                       // ring of the last 4 x blocks
+  double* sred = smem + 4 * MB;            // [4][64] partial near sums
+  double* dg = smem + 16 * MB;             // two diagonal tiles [64][LDC] (after xr, sred, ex, xb: 672 doubles)
+  double nt[kBackNear][16];
+  double2 dreg[MB * MB / 2 / kThreads];
+  double yv = 0.0, dv = 0.0;
+  // loads of step c, issued one step ahead: near tiles L(c+1+i, c), the diagonal tile, y_c, 1/diag
+  auto issue = [&](int c) {
+#pragma unroll
+    for (int i = 0; i < kBackNear; i++) {
+      const int m = c + 1 + i;
+      if (m < nbm) {
+        const double* T = a.c.A + (size_t)(m * MB + p * 16) * Dp + (size_t)c * MB + j;
+#pragma unroll
+        for (int r = 0; r < 16; r++) nt[i][r] = __ldcg(T + (size_t)r * Dp);
+      }
+    }
+    const double* src = a.c.A + (size_t)c * MB * Dp + (size_t)c * MB;
+#pragma unroll
+    for (int qd = 0; qd < MB * MB / 2 / kThreads; qd++) {
+      const int idx = tid + qd * kThreads;
+      dreg[qd] = __ldcg(reinterpret_cast<const double2*>(src + (size_t)(idx >> 5) * Dp + (idx & 31) * 2));
+    }
+    if (tid < MB) {
+      const int gi = c * MB + tid;
+      yv = gi < D ? __ldcg(a.c.A + (size_t)D * Dp + gi) : 0.0;
+      dv = __ldcg(a.c.x + Dp + gi);
+    }
+  };
+  auto land = [&](int c) {  // the diagonal tile of step c into its shared-memory buffer
+    double* d = dg + (c & 1) * kTileC;
+#pragma unroll
+    for (int qd = 0; qd < MB * MB / 2 / kThreads; qd++) {
+      const int idx = tid + qd * kThreads;
+      d[(idx >> 5) * LDC + (idx & 31) * 2] = dreg[qd].x;
+      d[(idx >> 5) * LDC + (idx & 31) * 2 + 1] = dreg[qd].y;
+    }
+  };
+  // winv_flag(c): the block inverses inside the diagonal tile of column c are written — needed BEFORE
+  // the loads of step c are issued (one step ahead); far_flag(c): the far sum, needed in step c.
+  // Both are polled one step early by a thread that has nothing else to do during the solve, so
+  // that no acquire round trip sits on the chain.
+  auto poll = [&](int c) {  // everything step c needs
+    if (c > 0) while (ld_acquire(winv_flag(a, c - 1)) != epoch) { }
+    if (c + kBackNear + 1 <= nbm - 1) while (ld_acquire(far_flag(a, c)) != epoch) { }
+  };
+  if (tid == 0) { while (ld_acquire(winv_flag(a, nbm - 1)) != epoch) { } poll(nbm - 1); }
+  __syncthreads();
+  issue(nbm - 1);
+  land(nbm - 1);
+  __syncthreads();
+  for (int c = nbm - 1; c >= 0; c--) {
+    const unsigned long long t_begin = a.c.trace ? gtimer() : 0ull;
+    // near part of the sum (x of the last kBackNear steps is in the ring)
+    double s = 0.0;
+#pragma unroll
+    for (int i = 0; i < kBackNear; i++) {
+      const int m = c + 1 + i;
+      if (m < nbm) {
+        const double* xm = xr + (m & 3) * MB + p * 16;
+#pragma unroll
+        for (int r = 0; r < 16; r++) s = fma(nt[i][r], xm[r], s);
+      }
+    }
+    sred[p * MB + j] = s;
+    const double y_c = yv, d_c = dv;  // this step's; the registers are reloaded for the next one now
+    const bool has_far = c + kBackNear + 1 <= nbm - 1;
+    __syncthreads();
+    if (c > 0) issue(c - 1);
+    if (tid == 64 && c > 0) poll(c - 1);  // done before this step's last barrier
+    const unsigned long long t_ready = a.c.trace ? gtimer() : 0ull;
+    // rhs and 1/diag of the two 32-blocks meet in warp 0: lane t holds entries t (A) and 32 + t (B)
+    double* ex = sred + 4 * MB;  // [2][64]: rhs, dinv
+    if (tid < MB) {
+      double rhs = y_c - ((sred[tid] + sred[MB + tid]) + (sred[2 * MB + tid] + sred[3 * MB + tid]));
+      if (has_far) rhs -= __ldcg(a.c.x + 2 * Dp + c * MB + tid);
+      if (c * MB + tid >= D) rhs = 0.0;
+      ex[tid] = rhs; ex[MB + tid] = d_c;
+    }
+    __syncthreads();
+    if (tid < 32) {
+      // x = L_cc^-T rhs with the inverses W^T = L^-T of the two 32x32 diagonal blocks (strictly upper part
+      // of the block, diagonal = 1/diag(L)):  x_B = W11^T r_B ; r_A -= L10^T x_B ; x_A = W00^T r_A
+      const double* Ld = dg + (c & 1) * kTileC;
+      double* xb = ex + 2 * MB;  // [32] exchange
+      const double rB = ex[32 + lane], iA = ex[MB + lane], iB = ex[MB + 32 + lane];
+      double rA = ex[lane];
+      double p0 = iB * rB, p1 = 0.0, p2 = 0.0, p3 = 0.0;
+#pragma unroll
+      for (int k = 0; k < 32; k += 4) {
+        if (k + 0 > lane) p0 = fma(Ld[(32 + lane) * LDC + 32 + k + 0], ex[32 + k + 0], p0);
+        if (k + 1 > lane) p1 = fma(Ld[(32 + lane) * LDC + 32 + k + 1], ex[32 + k + 1], p1);
+        if (k + 2 > lane) p2 = fma(Ld[(32 + lane) * LDC + 32 + k + 2], ex[32 + k + 2], p2);
+        if (k + 3 > lane) p3 = fma(Ld[(32 + lane) * LDC + 32 + k + 3], ex[32 + k + 3], p3);
+      }
+      const double xB = (p0 + p1) + (p2 + p3);
+      xb[lane] = xB;
+      __syncwarp();
+      p0 = p1 = p2 = p3 = 0.0;
+#pragma unroll
+      for (int k = 0; k < 32; k += 4) {
+        p0 = fma(Ld[(32 + k + 0) * LDC + lane], xb[k + 0], p0);
+        p1 = fma(Ld[(32 + k + 1) * LDC + lane], xb[k + 1], p1);
+        p2 = fma(Ld[(32 + k + 2) * LDC + lane], xb[k + 2], p2);
+        p3 = fma(Ld[(32 + k + 3) * LDC + lane], xb[k + 3], p3);
+      }
+      rA -= (p0 + p1) + (p2 + p3);
+      __syncwarp();
+      xb[lane] = rA;
+      __syncwarp();
+      p0 = iA * rA; p1 = p2 = p3 = 0.0;
+#pragma unroll
+      for (int k = 0; k < 32; k += 4) {
+        if (k + 0 > lane) p0 = fma(Ld[lane * LDC + k + 0], xb[k + 0], p0);
+        if (k + 1 > lane) p1 = fma(Ld[lane * LDC + k + 1], xb[k + 1], p1);
+        if (k + 2 > lane) p2 = fma(Ld[lane * LDC + k + 2], xb[k + 2], p2);
+        if (k + 3 > lane) p3 = fma(Ld[lane * LDC + k + 3], xb[k + 3], p3);
+      }
+      const double xA = (p0 + p1) + (p2 + p3);
+      xr[(c & 3) * MB + lane] = xA; xr[(c & 3) * MB + 32 + lane] = xB;
+      a.c.x[c * MB + lane] = xA; a.c.x[c * MB + 32 + lane] = xB;
+    }
+    if (c > 0) land(c - 1);
+    __syncthreads();
+    if (tid == kThreads - 1) { __threadfence(); st_release(a.c.flags + 2 * nbm * nbm + c, epoch); }  // x_c for the helpers
+    trace_put(a.c, slot0 + c, 2, c, c, t_begin, t_ready);
+  }
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -472,24 +851,27 @@ chol64_kernel(const Args a) {
     run_chain(a, epoch, smem, s_dinv);
   } else {
     int* queue = a.c.flags + queue_index(a.nbm);
+    if (threadIdx.x == 0) s_task = atomicAdd(queue, 1);
     for (;;) {
-      if (threadIdx.x == 0) s_task = atomicAdd(queue, 1);
       __syncthreads();
       const int t = s_task;
       __syncthreads();
       if (t >= a.ntasks) break;
-      run_task(a, __ldg(a.tasks + t), epoch, smem, s_dinv, a.nbm + t);
+      run_task(a, __ldg(a.tasks + t), epoch, smem, s_dinv, a.nbm + t, &s_task);  // leaves the next entry in s_task
     }
   }
-  for (int c = a.c.nb - 1; c >= 0; c--)
-    if (c % G == cta) {
-      back_task(a, c, epoch, smem, a.nbm + a.ntasks + c);
-      if (c == 0) {  // x complete: this CTA finishes the iteration
-        __syncthreads();
-        gn_update_block(a.c.Twc, a.c.x, a.c.N, a.c.D, a.c.delta_thresh, a.c.dx, a.c.hdr, red, kThreads,
-                        threadIdx.x, [] { __syncthreads(); });
-      }
-    }
+  // back substitution: block 0 runs the chain, blocks 1.. the far sums of the columns (descending)
+  if (cta == 0) {
+    __syncthreads();
+    back_chain(a, epoch, smem, a.nbm + a.ntasks + a.nbm);
+    __syncthreads();  // x complete
+    gn_update_block(a.c.Twc, a.c.x, a.c.N, a.c.D, a.c.delta_thresh, a.c.dx, a.c.hdr, red, kThreads, threadIdx.x,
+                    [] { __syncthreads(); });
+  } else {
+    // the last diagonal tile depends, transitively, on every tile of the factor
+    wait_flag(tile_flag(a, a.nbm - 1, a.nbm - 1), epoch);
+    for (int c = a.nbm - 1 - (cta - 1); c >= 0; c -= G - 1) back_far(a, c, epoch, smem, s_dinv, a.nbm + a.ntasks + c);
+  }
 }
 
 static int max_ctas() {

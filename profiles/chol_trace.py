@@ -26,7 +26,7 @@ big = nb > 16  # macro-tile kernel (m3r_gn_chol64.cu): slots = chain steps, then
 if big:
     nbm = (7 * (N - 1) + 1 + 63) // 64
     nb = 2 * nbm
-    cap = nbm + be._lib.m3r_debug_chol64_tasklist(nbm, None, 0) + nb
+    cap = nbm + be._lib.m3r_debug_chol64_tasklist(nbm, None, 0) + nb + 4 * nbm
 else:
     cap = nb * (nb + 1) // 2 + nb
 buf = torch.zeros((cap, 4), dtype=torch.int64, device=dev)
@@ -38,10 +38,13 @@ a.record(); s.solve_step(0.0); z.record()
 torch.cuda.synchronize()
 be._lib.m3r_debug_chol_trace(None, 0)
 t = buf.cpu().numpy()
+if len(sys.argv) > 2:
+    import numpy as _np
+    _np.save(sys.argv[2] + ".npy", t)
 t0 = t[t[:, 1] > 0, 1].min()
 lines = [f"N={N} nb={nb} solve_step {a.elapsed_time(z) * 1e3:.1f} us (event); kernel span "
          f"{(t[:, 3].max() - t0) / 1e3:.1f} us"]
-kinds = {0: "potrf", 1: "trsm ", 2: "back ", 3: "chunk"}
+kinds = {0: "potrf", 1: "trsm ", 2: "back ", 3: "chunk", 4: "team1a", 5: "team1b", 6: "team0a", 7: "team0b"}
 if big:  # summary by kind: busy time between inputs-ready and end, and waiting before it
     tt = t[t[:, 3] > 0]
     for k, name in kinds.items():
@@ -58,7 +61,10 @@ for r in order:
     if t[r, 3] == 0:
         continue
     k, i, j = int(t[r, 0] >> 32), int((t[r, 0] >> 16) & 0xFFFF), int(t[r, 0] & 0xFFFF)
-    if big and (k == 3 or (k == 1 and i > j + 2) or (k == 2 and i % 8)):
+    if big and (k == 3 or (k == 1 and i > j + 2) or (k == 2 and i % 8) or (k >= 4 and not 18 <= i <= 24)):
+        continue
+    if k >= 4:
+        lines.append(f"{kinds[k]} ({i:3d}) " + "  ".join(f"{(t[r, q] - t0) / 1e3:8.2f}" for q in (1, 2, 3)))
         continue
     if (not big) and nb > 16 and not (k != 1 or i == j + 1):
         continue

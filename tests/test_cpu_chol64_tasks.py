@@ -32,12 +32,28 @@ def tasklist(backends):
     return get
 
 
-def _nch_diag(J):
-    return -(-(J - 1) // KC) if J >= 2 else 0
+TAIL_CHAIN = 2
 
 
-def _nch_sub(J):
-    return (1 if J >= 1 else 0) + _nch_diag(J)
+RECENT, KC_OLD = 8, 16
+
+
+def _nch(R, t):  # chunks of [0, R) from the end: a tail of t, RECENT / KC chunks of KC, then chunks of KC_OLD
+    if R <= 0:
+        return 0
+    n, e, d = 1, R - t, 0
+    while e > 0:
+        st = KC if d < RECENT else KC_OLD
+        e -= st; d += st; n += 1
+    return n
+
+
+def _nch_diag(J):  # list tasks cover [0, J-2); the chain adds k = J-2 and k = J-1 itself
+    return _nch(J - 2, TAIL_CHAIN)
+
+
+def _nch_sub(J):  # list tasks cover [0, J-1); the chain adds the last term (k = J-1) itself
+    return _nch(J - 1, TAIL_CHAIN)
 
 
 @pytest.mark.parametrize("nbm", [1, 2, 3, 5, 9, 13, 20, 56])
@@ -56,15 +72,16 @@ def test_coverage_and_chunk_order(tasklist, nbm):
             for _, t in ts:
                 assert t["k0"] == k
                 k = t["k1"]
-            if I == J:       # the chain adds k = J-1 itself
-                assert k == max(J - 1, 0) and all(t["kind"] == 0 for _, t in ts) and len(ts) == _nch_diag(J)
-            elif I == J + 1:  # all of [0, J) by update tasks, the last term alone; the chain does the TRSM
-                assert k == J and all(t["kind"] == 0 for _, t in ts) and len(ts) == _nch_sub(J)
-                if J >= 1:
-                    assert (ts[-1][1]["k0"], ts[-1][1]["k1"]) == (J - 1, J)
+            if I == J:       # the chain adds k = J-2 and k = J-1 itself
+                assert k == max(J - 2, 0) and all(t["kind"] == 0 for _, t in ts) and len(ts) == _nch_diag(J)
+            elif I == J + 1:  # [0, J-1) by update tasks; the chain adds k = J-1 and does the TRSM
+                assert k == max(J - 1, 0) and all(t["kind"] == 0 for _, t in ts) and len(ts) == _nch_sub(J)
             else:             # exactly one final task, last, covering the tail of [0, J)
                 assert k == J and [t["kind"] for _, t in ts] == [0] * (len(ts) - 1) + [1]
-            assert all(t["k1"] - t["k0"] <= KC for _, t in ts)
+            assert all(t["k1"] - t["k0"] <= KC_OLD for _, t in ts)
+            assert all(t["k1"] - t["k0"] <= KC for _, t in ts if t["k1"] > J - 1 - RECENT)
+            if I <= J + 1 and ts:  # chain tiles: the chunk released last is short
+                assert ts[-1][1]["k1"] - ts[-1][1]["k0"] <= TAIL_CHAIN
 
 
 def _chain_needs(J):
@@ -75,6 +92,11 @@ def _chain_needs(J):
     if J >= 1 and _nch_sub(J - 1):
         need.append(((J, J - 1), _nch_sub(J - 1)))
     return need
+
+
+def _chain_needs_final(J):
+    """Published tile the chain needs before step J: L(J,J-2), for the last term of tile (J,J-1)."""
+    return (J, J - 2) if J >= 2 else None
 
 
 @pytest.mark.parametrize("nbm", [3, 9, 20, 56])
@@ -92,6 +114,8 @@ def test_list_is_a_topological_order(tasklist, nbm):
     for J in range(nbm):
         for (tile, n) in _chain_needs(J):
             worst = max(worst, pos_chunk[(tile[0], tile[1], n - 1)])
+        if _chain_needs_final(J):
+            worst = max(worst, pos_final[_chain_needs_final(J)])
         chain_after.append(worst)
 
     def producer_pos(I, k):  # list position after which L(I,k) exists
@@ -131,7 +155,9 @@ def test_scheduler_model_always_finishes(tasklist, nbm, ctas, seed):
         rng.shuffle(order)
         for w in order:
             if w == ctas:  # the chain
-                if chain_J < nbm and all(progress.get(tile, 0) == n for tile, n in _chain_needs(chain_J)):
+                fin = _chain_needs_final(chain_J)
+                if chain_J < nbm and all(progress.get(tile, 0) == n for tile, n in _chain_needs(chain_J)) and \
+                        (fin is None or fin in ready):
                     if chain_J >= 1:
                         ready.add((chain_J, chain_J - 1))
                     ready.add((chain_J, chain_J))
@@ -153,7 +179,8 @@ def test_scheduler_model_always_finishes(tasklist, nbm, ctas, seed):
                 moved = True
         if not moved:
             blocked = [t for t in holding if t is not None and not inputs_ready(t)]
+            fin = _chain_needs_final(chain_J) if chain_J < nbm else None
             assert len(blocked) < sum(t is not None for t in holding) or chain_J < nbm and all(
-                progress.get(tile, 0) == n for tile, n in _chain_needs(chain_J)), \
+                progress.get(tile, 0) == n for tile, n in _chain_needs(chain_J)) and (fin is None or fin in ready), \
                 f"deadlock at chain step {chain_J}, {done_tasks}/{len(tasks)} tasks done"
     assert len(ready) == nbm * (nbm + 1) // 2
