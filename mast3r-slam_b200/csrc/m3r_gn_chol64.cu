@@ -179,6 +179,32 @@ __device__ __forceinline__ void warp_mma(const double* __restrict__ A, const dou
   }
 }
 
+// the same with a compile-time k extent: fully unrolled, so that a lone warp on its scheduler (the chain
+// CTA's helpers) has the next fragments in flight while the current DMMAs issue
+template <int MI, int NI, int LD, int K16>
+__device__ __forceinline__ void warp_mma_k(const double* __restrict__ A, const double* __restrict__ B,
+                                           double (&acc)[MI][NI][2]) {
+  const int lane = threadIdx.x & 31, g = lane >> 2, q = lane & 3;
+  const double* pa = A + g * LD;
+  const double* pb = B + g * LD;
+#pragma unroll
+  for (int kb = 0; kb < K16; kb++) {
+#pragma unroll
+    for (int kk = 0; kk < 4; kk++) {
+      const int k = kb * 16 + frag_k<LD>(q, kk);
+      double av[MI], bv[NI];
+#pragma unroll
+      for (int mi = 0; mi < MI; mi++) av[mi] = pa[mi * 8 * LD + k];
+#pragma unroll
+      for (int ni = 0; ni < NI; ni++) bv[ni] = pb[ni * 8 * LD + k];
+#pragma unroll
+      for (int mi = 0; mi < MI; mi++)
+#pragma unroll
+        for (int ni = 0; ni < NI; ni++) dmma(acc[mi][ni], av[mi], bv[ni]);
+    }
+  }
+}
+
 template <int MI, int NI>
 __device__ __forceinline__ void zero_acc(double (&acc)[MI][NI][2]) {
 #pragma unroll
@@ -570,60 +596,92 @@ __device__ __forceinline__ void run_chain(const Args& a, int epoch, double* smem
       // L(J,J) and 1/diag.  The fence stalls its warp for ~1 us: by now team 0 only waits for team 1.
       team_publish_tile64(a.c.A, a.c.Dp, J, J, T, tile_flag(a, J, J), epoch, 0);
     } else {
-      if (J > 0) {
-        team_publish_tile64(a.c.A, a.c.Dp, J, J - 1, X, tile_flag(a, J, J - 1), epoch, 1);  // L(J,J-1)
-        const int r0 = 32 + (w >> 1) * 16, c0 = 32 + (w & 1) * 16;  // T11 -= X1 X1^T
-        double acc[2][2][2];
-        zero_acc(acc);
-        warp_mma<2, 2, LDC>(X + r0 * LDC, X + c0 * LDC, 4, acc);
-        sub_acc_smem(T, r0, c0, acc);
-      }
-      cta_arrive(3);  // (1) team 0 may touch T11 now; this team does not wait for it
-      const unsigned long long q0 = a.c.trace ? gtimer() : 0ull;
-      unsigned long long q1 = q0, q2 = q0, q3 = q0, q4 = q0;
-      if (J + 1 < a.nbm) {  // the next step's tiles, as soon as their bulk chunks are in
-        const int nd = gn_nch_diag(J + 1), ns = gn_nch_sub(J);
-        if ((tid & 127) == 0) {
-          if (nd) while (ld_acquire(prog_flag(a, J + 1, J + 1)) != ((epoch << 12) | nd)) __nanosleep(20);
-          if (ns) while (ld_acquire(prog_flag(a, J + 1, J)) != ((epoch << 12) | ns)) __nanosleep(20);
-          if (J > 0) while (ld_acquire(tile_flag(a, J + 1, J - 1)) != epoch) __nanosleep(20);
+      // warp 4 publishes L(J,J-1) on its own (store, fence, flag: ~1.5 us) and then rests: it shares its
+      // scheduler and fp64 pipe with warp 0, whose POTRF is the critical path of the whole factorisation
+      // (with DMMA streams on all four sub-partitions POTRF(T11) took 7.2 us instead of 4).  Warps 5-7
+      // do the arithmetic: T11 -= X1 X1^T first (team 0 waits for it), then the next step's tiles.
+      unsigned long long q0 = 0ull, q1 = 0ull, q2 = 0ull;
+      if (w == 0) {
+        cta_arrive(3);  // (1) does not touch T11
+        const int lane = tid & 31;
+        if (J > 0) {
+          double* dst = a.c.A + (size_t)J * MB * a.c.Dp + (size_t)(J - 1) * MB;
+          for (int idx = lane; idx < MB * MB; idx += 32) __stcg(dst + (size_t)(idx >> 6) * a.c.Dp + (idx & 63), X[(idx >> 6) * LDC + (idx & 63)]);
+          __syncwarp();
+          if (lane == 0) { __threadfence(); st_release(tile_flag(a, J, J - 1), epoch); }
         }
-        team_sync(1);
-        if (a.c.trace) q1 = gtimer();
-        // three tiles in flight at once (8-byte cp.async: the rows of a chain tile are 8-byte aligned only;
-        // each of these lines is read once per launch by this SM, right after an acquire)
-        for (int idx = tid & 127; idx < MB * MB; idx += 128) {
-          const int rr = idx >> 6, cc = idx & 63;
-          cp_async8(Tn + rr * LDC + cc, a.c.A + (size_t)((J + 1) * MB + rr) * a.c.Dp + (J + 1) * MB + cc);
-          cp_async8(Xn + rr * LDC + cc, a.c.A + (size_t)((J + 1) * MB + rr) * a.c.Dp + J * MB + cc);
-          if (J > 0) cp_async8(Y + rr * LDC + cc, a.c.A + (size_t)((J + 1) * MB + rr) * a.c.Dp + (J - 1) * MB + cc);
+        if (J + 1 < a.nbm) {  // Xn = tile (J+1,J): its bulk chunks are normally in long before
+          const int ns = gn_nch_sub(J);
+          if (lane == 0 && ns) while (ld_acquire(prog_flag(a, J + 1, J)) != ((epoch << 12) | ns)) __nanosleep(20);
+          __syncwarp();
+          // 8-byte cp.async: the rows of a chain tile are 8-byte aligned only; each of these lines is read
+          // once per launch by this SM, right after an acquire
+          for (int idx = lane; idx < MB * MB; idx += 32)
+            cp_async8(Xn + (idx >> 6) * LDC + (idx & 63), a.c.A + (size_t)((J + 1) * MB + (idx >> 6)) * a.c.Dp + J * MB + (idx & 63));
+          cp_async_commit();
+          cp_async_wait<0>();
+          asm volatile("bar.arrive 5, 128;" ::: "memory");  // Xn is in shared memory (warps 5-7 wait for it)
         }
-        cp_async_commit();
-        cp_async_wait<0>();
-        team_sync(1);
-        if (a.c.trace) q2 = q3 = q4 = gtimer();
-        // The last terms of the next step's two tiles, with Y = L(J+1,J-1) and X = L(J,J-1) in shared memory:
-        //   Xn -= Y X^T (k = J-1 of tile (J+1,J)),  Tn -= Y Y^T (k = J-1 of tile (J+1,J+1), lower blocks).
-        // 14 blocks of 32x16 outputs on THREE warps: the fourth (warp 4) shares its scheduler and fp64
-        // pipe with warp 0, whose POTRF is the critical path of the whole factorisation — with DMMA
-        // streams on all four sub-partitions POTRF(T11) took 7.2 us instead of 4.
-        if (J > 0 && w > 0) {
+      } else {
+        const int t3 = tid - 160;  // 0..95
+        if (J > 0) {
 #pragma unroll 1
-          for (int blk = w - 1; blk < 14; blk += 3) {
-            int r0, c0; const double* Bop; double* Cout;
-            if (blk < 8) { r0 = (blk >> 2) * 32; c0 = (blk & 3) * 16; Bop = X; Cout = Xn; }
-            else { const int t = blk - 8; r0 = t < 2 ? 0 : 32; c0 = t < 2 ? t * 16 : (t - 2) * 16; Bop = Y; Cout = Tn; }
-            double acc[4][2][2];
+          for (int blk = w - 1; blk < 8; blk += 3) {  // T11 -= X1 X1^T in 16x8 blocks
+            const int r0 = 32 + (blk >> 2) * 16, c0 = 32 + (blk & 3) * 8;
+            double acc[2][1][2];
             zero_acc(acc);
-            warp_mma<4, 2, LDC>(Y + r0 * LDC, Bop + c0 * LDC, 4, acc);
-            sub_acc_smem(Cout, r0, c0, acc);
+            warp_mma<2, 1, LDC>(X + r0 * LDC, X + c0 * LDC, 4, acc);
+            sub_acc_smem(T, r0, c0, acc);
+          }
+        }
+        cta_arrive(3);  // (1) team 0 may touch T11 now; this team does not wait for it
+        if (a.c.trace) q0 = gtimer();
+        if (J + 1 < a.nbm) {
+          // Tn = tile (J+1,J+1) once its bulk chunks are in, Y = L(J+1,J-1) once its owner has flagged it
+          const int nd = gn_nch_diag(J + 1);
+          if (t3 == 0 && nd) while (ld_acquire(prog_flag(a, J + 1, J + 1)) != ((epoch << 12) | nd)) __nanosleep(20);
+          if (t3 == 32 && J > 0) while (ld_acquire(tile_flag(a, J + 1, J - 1)) != epoch) __nanosleep(20);
+          asm volatile("bar.sync 4, 96;" ::: "memory");
+          if (a.c.trace) q1 = gtimer();
+          for (int idx = t3; idx < MB * MB; idx += 96) {
+            const int rr = idx >> 6, cc = idx & 63;
+            cp_async8(Tn + rr * LDC + cc, a.c.A + (size_t)((J + 1) * MB + rr) * a.c.Dp + (J + 1) * MB + cc);
+            if (J > 0) cp_async8(Y + rr * LDC + cc, a.c.A + (size_t)((J + 1) * MB + rr) * a.c.Dp + (J - 1) * MB + cc);
+          }
+          cp_async_commit();
+          cp_async_wait<0>();
+          asm volatile("bar.sync 4, 96;" ::: "memory");
+          if (a.c.trace) q2 = gtimer();
+          // The last terms of the next step's two tiles, with Y = L(J+1,J-1) and X = L(J,J-1) in shared memory,
+          // in blocks of 32x16 outputs:  Tn -= Y Y^T (k = J-1 of tile (J+1,J+1), 6 lower blocks) first, then,
+          // when warp 4 has brought Xn in,  Xn -= Y X^T (k = J-1 of tile (J+1,J), 8 blocks).
+          if (J > 0) {
+#pragma unroll 1
+            for (int blk = w - 1; blk < 6; blk += 3) {
+              const int r0 = blk < 2 ? 0 : 32, c0 = blk < 2 ? blk * 16 : (blk - 2) * 16;
+              double acc[4][2][2];
+              zero_acc(acc);
+              warp_mma<4, 2, LDC>(Y + r0 * LDC, Y + c0 * LDC, 4, acc);
+              sub_acc_smem(Tn, r0, c0, acc);
+            }
+          }
+          asm volatile("bar.sync 5, 128;" ::: "memory");
+          if (J > 0) {
+#pragma unroll 1
+            for (int blk = w - 1; blk < 8; blk += 3) {
+              const int r0 = (blk >> 2) * 32, c0 = (blk & 3) * 16;
+              double acc[4][2][2];
+              zero_acc(acc);
+              warp_mma<4, 2, LDC>(Y + r0 * LDC, X + c0 * LDC, 4, acc);
+              sub_acc_smem(Xn, r0, c0, acc);
+            }
           }
         }
       }
-      if (tid == 128) {  // team 1's timeline: barrier (1), diagonal chunks in, sub-diagonal chunks in | Y wanted, Y flagged, done
+      if (tid == 160) {  // warps 5-7: T11 term done, inputs of the next step flagged, tiles loaded | .., .., done
         const int base = a.nbm + a.ntasks + 2 * a.nbm;
         trace_put3(a.c, base + 2 * J, 4, J, J, q0, q1, q2);
-        trace_put3(a.c, base + 2 * J + 1, 5, J, J, q3, q4, gtimer());
+        trace_put3(a.c, base + 2 * J + 1, 5, J, J, q2, q2, gtimer());
       }
     }
     __syncthreads();  // (2)
@@ -706,12 +764,12 @@ __device__ __forceinline__ void back_far(const Args& a, int c, int epoch, double
 }
 
 __device__ __forceinline__ void back_chain(const Args& a, int epoch, double* smem, int slot0) {
-  const int tid = threadIdx.x, j = tid & 63, p = tid >> 6, lane = tid & 31;
+  const int tid = threadIdx.x, j2 = tid & 31, p8 = tid >> 5, lane = tid & 31;  // near sums: columns 2 j2, 2 j2 + 1; rows 8 p8 ..
   const int nbm = a.nbm, Dp = a.c.Dp, D = a.c.D;
   double* xr = smem;                       // ring of the last 4 x blocks
-  double* sred = smem + 4 * MB;            // [4][64] partial near sums
-  double* dg = smem + 16 * MB;             // two diagonal tiles [64][LDC] (after xr, sred, ex, xb: 672 doubles)
-  double nt[kBackNear][16];
+  double* sred = smem + 4 * MB;            // [8][64] partial near sums
+  double* dg = smem + 16 * MB;             // two diagonal tiles [64][LDC] (after xr, sred, ex, xb: 928 doubles)
+  double2 nt[kBackNear][8];
   double2 dreg[MB * MB / 2 / kThreads];
   double yv = 0.0, dv = 0.0;
   // loads of step c, issued one step ahead: near tiles L(c+1+i, c), the diagonal tile, y_c, 1/diag
@@ -720,9 +778,9 @@ __device__ __forceinline__ void back_chain(const Args& a, int epoch, double* sme
     for (int i = 0; i < kBackNear; i++) {
       const int m = c + 1 + i;
       if (m < nbm) {
-        const double* T = a.c.A + (size_t)(m * MB + p * 16) * Dp + (size_t)c * MB + j;
+        const double* T = a.c.A + (size_t)(m * MB + p8 * 8) * Dp + (size_t)c * MB + 2 * j2;
 #pragma unroll
-        for (int r = 0; r < 16; r++) nt[i][r] = __ldcg(T + (size_t)r * Dp);
+        for (int r = 0; r < 8; r++) nt[i][r] = __ldcg(reinterpret_cast<const double2*>(T + (size_t)r * Dp));
       }
     }
     const double* src = a.c.A + (size_t)c * MB * Dp + (size_t)c * MB;
@@ -762,17 +820,17 @@ __device__ __forceinline__ void back_chain(const Args& a, int epoch, double* sme
   for (int c = nbm - 1; c >= 0; c--) {
     const unsigned long long t_begin = a.c.trace ? gtimer() : 0ull;
     // near part of the sum (x of the last kBackNear steps is in the ring)
-    double s = 0.0;
+    double s0 = 0.0, s1 = 0.0;
 #pragma unroll
     for (int i = 0; i < kBackNear; i++) {
       const int m = c + 1 + i;
       if (m < nbm) {
-        const double* xm = xr + (m & 3) * MB + p * 16;
+        const double* xm = xr + (m & 3) * MB + p8 * 8;
 #pragma unroll
-        for (int r = 0; r < 16; r++) s = fma(nt[i][r], xm[r], s);
+        for (int r = 0; r < 8; r++) { s0 = fma(nt[i][r].x, xm[r], s0); s1 = fma(nt[i][r].y, xm[r], s1); }
       }
     }
-    sred[p * MB + j] = s;
+    sred[p8 * MB + 2 * j2] = s0; sred[p8 * MB + 2 * j2 + 1] = s1;
     const double y_c = yv, d_c = dv;  // this step's; the registers are reloaded for the next one now
     const bool has_far = c + kBackNear + 1 <= nbm - 1;
     __syncthreads();
@@ -780,9 +838,10 @@ __device__ __forceinline__ void back_chain(const Args& a, int epoch, double* sme
     if (tid == 64 && c > 0) poll(c - 1);  // done before this step's last barrier
     const unsigned long long t_ready = a.c.trace ? gtimer() : 0ull;
     // rhs and 1/diag of the two 32-blocks meet in warp 0: lane t holds entries t (A) and 32 + t (B)
-    double* ex = sred + 4 * MB;  // [2][64]: rhs, dinv
+    double* ex = sred + 8 * MB;  // [2][64]: rhs, dinv
     if (tid < MB) {
-      double rhs = y_c - ((sred[tid] + sred[MB + tid]) + (sred[2 * MB + tid] + sred[3 * MB + tid]));
+      double rhs = y_c - (((sred[tid] + sred[MB + tid]) + (sred[2 * MB + tid] + sred[3 * MB + tid])) +
+                          ((sred[4 * MB + tid] + sred[5 * MB + tid]) + (sred[6 * MB + tid] + sred[7 * MB + tid])));
       if (has_far) rhs -= __ldcg(a.c.x + 2 * Dp + c * MB + tid);
       if (c * MB + tid >= D) rhs = 0.0;
       ex[tid] = rhs; ex[MB + tid] = d_c;
