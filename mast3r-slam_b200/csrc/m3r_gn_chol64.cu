@@ -984,16 +984,25 @@ int gn_chol64_launch(float* Twc, int N, float delta_thresh, float* dx, void* ws,
 // on the HOST by the same enumeration the device kernel runs (4 ints per task:
 // I | J << 16, k0 | k1 << 16, kind, chunk index).  Returns the number of tasks; writes at most
 // `capacity` of them.
+namespace {
+struct HostTaskSink {
+  int* out; int capacity; int J; int o;
+  __host__ __device__ void operator()(int I, int k0, int k1, int kind, int kc) {
+    if (out && o < capacity) {
+      out[4 * o] = I | (J << 16); out[4 * o + 1] = k0 | (k1 << 16); out[4 * o + 2] = kind; out[4 * o + 3] = kc;
+    }
+    o++;
+  }
+};
+}  // namespace
+
 extern "C" int m3r_debug_chol64_tasklist(int nbm, int* out, int capacity) {
   using namespace m3r;
-  int o = 0;
+  HostTaskSink sink{out, capacity, 0, 0};
   for (int v = 0; v <= nbm; v++)
-    for (int J = v; J <= v + c64::kWindow && J < nbm; J++)
-      c64::tasks_of_group(nbm, v, J, [&](int I, int k0, int k1, int kind, int kc) {
-        if (out && o < capacity) {
-          out[4 * o] = I | (J << 16); out[4 * o + 1] = k0 | (k1 << 16); out[4 * o + 2] = kind; out[4 * o + 3] = kc;
-        }
-        o++;
-      });
-  return o == gn_chol64_ntasks(nbm) ? o : -1;
+    for (int J = v; J <= v + c64::kWindow && J < nbm; J++) {
+      sink.J = J;
+      c64::tasks_of_group(nbm, v, J, sink);
+    }
+  return sink.o == gn_chol64_ntasks(nbm) ? sink.o : -1;
 }
