@@ -4,6 +4,7 @@
 #include <cuda_fp16.h>
 #include <stdint.h>
 #include <atomic>
+#include <nvtx3/nvToolsExt.h>
 
 #include "../../include/m3r_b200.h"
 
@@ -26,6 +27,16 @@ inline int check_cuda(cudaError_t e) {
   if (e != cudaSuccess) { g_last_cuda_error = (int)e; return M3R_ELAUNCH; }
   return M3R_OK;
 }
+
+// NVTX range around a C-ABI entry point: visible as a named span on the host timeline of
+// nsys / ncu --nvtx; a few nanoseconds when no tool is attached (nvtx3 is header-only and lazy).
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
+#define M3R_NVTX(name) ::m3r::NvtxRange m3r_nvtx_range_(name)
 
 #define M3R_TRY(expr) do { int _rc = (expr); if (_rc != M3R_OK) return _rc; } while (0)
 

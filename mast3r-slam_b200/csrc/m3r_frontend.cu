@@ -315,6 +315,7 @@ static int edge_build_impl(const int64_t* idx_src2dst, const uint8_t* valid_matc
 extern "C" int m3r_edge_build(const int64_t* idx_src2dst, const uint8_t* valid_match,
                               const float* Q_src, const float* Q_dst, int num_edges, int n,
                               float Q_conf, float* Q_out, int* valid_count, m3r_stream_t stream) {
+  M3R_NVTX("m3r_edge_build");
   if (num_edges > 0 && n > 0 && !Q_out) return M3R_EINVAL;
   return edge_build_impl(idx_src2dst, valid_match, Q_src, Q_dst, num_edges, n, Q_conf, Q_out, nullptr,
                          valid_count, stream);
@@ -324,6 +325,7 @@ extern "C" int m3r_edge_build_packed(const int64_t* idx_src2dst, const uint8_t* 
                                      const float* Q_src, const float* Q_dst, int num_edges, int n,
                                      float Q_conf, m3r_packed_match* packed_out, float* Q_out,
                                      int* valid_count, m3r_stream_t stream) {
+  M3R_NVTX("m3r_edge_build_packed");
   if (num_edges > 0 && n > 0 && !packed_out) return M3R_EINVAL;
   return edge_build_impl(idx_src2dst, valid_match, Q_src, Q_dst, num_edges, n, Q_conf, Q_out, packed_out,
                          valid_count, stream);
@@ -331,6 +333,7 @@ extern "C" int m3r_edge_build_packed(const int64_t* idx_src2dst, const uint8_t* 
 
 extern "C" int m3r_edge_pack(const int64_t* idx, const uint8_t* valid_match, const float* Q, size_t count,
                              m3r_packed_match* packed_out, m3r_stream_t stream) {
+  M3R_NVTX("m3r_edge_pack");
   if (count == 0) return M3R_OK;
   if (!idx || !valid_match || !Q || !packed_out) return M3R_EINVAL;
   const size_t blocks = (count + kFeThreads - 1) / kFeThreads;
@@ -341,6 +344,7 @@ extern "C" int m3r_edge_pack(const int64_t* idx, const uint8_t* valid_match, con
 
 extern "C" int m3r_edge_unpack(const m3r_packed_match* packed, size_t count, int64_t* idx,
                                uint8_t* valid_match, float* Q, m3r_stream_t stream) {
+  M3R_NVTX("m3r_edge_unpack");
   if (count == 0) return M3R_OK;
   if (!packed) return M3R_EINVAL;
   const size_t blocks = (count + kFeThreads - 1) / kFeThreads;
@@ -351,6 +355,7 @@ extern "C" int m3r_edge_unpack(const m3r_packed_match* packed, size_t count, int
 
 extern "C" int m3r_pointmap_update(float* X_canon, float* C, const float* X_new, const float* C_new,
                                    const float* T_act, int n, int mode, m3r_stream_t stream) {
+  M3R_NVTX("m3r_pointmap_update");
   if (n < 0 || mode < 0 || mode > 2) return M3R_EINVAL;
   if (n == 0) return M3R_OK;
   if (!X_canon || !C || !X_new || !C_new) return M3R_EINVAL;

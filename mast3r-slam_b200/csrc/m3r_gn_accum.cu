@@ -737,6 +737,7 @@ extern "C" int m3r_gn_prepare(const float* Xs, const float* Cs, const int64_t* i
                               const int64_t* jj, int num_poses, int n, int num_edges,
                               int local_edges, void* workspace, size_t workspace_bytes,
                               m3r_stream_t stream) {
+  M3R_NVTX("m3r_gn_prepare");
   return gn_prepare_impl(Xs, Cs, ii, jj, 0, num_poses, n, num_edges, local_edges, workspace,
                          workspace_bytes, stream);
 }
@@ -745,6 +746,7 @@ extern "C" int m3r_gn_prepare_two_way(const float* Xs, const float* Cs, const in
                                       const int64_t* jj, int num_poses, int n, int num_edges,
                                       int local_edges, void* workspace, size_t workspace_bytes,
                                       m3r_stream_t stream) {
+  M3R_NVTX("m3r_gn_prepare_two_way");
   return gn_prepare_impl(Xs, Cs, ii, jj, 1, num_poses, n, num_edges, local_edges, workspace,
                          workspace_bytes, stream);
 }
@@ -841,6 +843,7 @@ extern "C" int m3r_gn_accumulate(const m3r_gn_params* prm, const float* Twc,
                                  const float* Q, int num_poses, int n, int num_edges,
                                  int edge_begin, int edge_count, double* blocks, void* workspace,
                                  size_t workspace_bytes, m3r_stream_t stream) {
+  M3R_NVTX("m3r_gn_accumulate");
   return gn_accumulate_impl(prm, Twc, reference_streams(idx_ii2jj, valid_match, Q), num_poses, n,
                             num_edges, edge_begin, edge_count, blocks, nullptr, workspace,
                             workspace_bytes, stream);
@@ -852,6 +855,7 @@ extern "C" int m3r_gn_accumulate_packed(const m3r_gn_params* prm, const float* T
                                         int edge_begin, int edge_count, double* blocks,
                                         const m3r_gn_peers* peers, void* workspace,
                                         size_t workspace_bytes, m3r_stream_t stream) {
+  M3R_NVTX("m3r_gn_accumulate_packed");
   return gn_accumulate_impl(prm, Twc, packed_streams(pk0, pk1, split), num_poses, n, num_edges,
                             edge_begin, edge_count, blocks, peers, workspace, workspace_bytes, stream);
 }
@@ -861,6 +865,7 @@ extern "C" int m3r_gn_accumulate_p2p(const m3r_gn_params* prm, const float* Twc,
                                      const float* Q, int num_poses, int n, int num_edges,
                                      int edge_begin, int edge_count, const m3r_gn_peers* peers,
                                      void* workspace, size_t workspace_bytes, m3r_stream_t stream) {
+  M3R_NVTX("m3r_gn_accumulate_p2p");
   if (!peers) return M3R_EINVAL;
   return gn_accumulate_impl(prm, Twc, reference_streams(idx_ii2jj, valid_match, Q), num_poses, n,
                             num_edges, edge_begin, edge_count, nullptr, peers, workspace,
@@ -870,6 +875,7 @@ extern "C" int m3r_gn_accumulate_p2p(const m3r_gn_params* prm, const float* Twc,
 extern "C" int m3r_gn_solve_step_p2p(float* Twc, const m3r_gn_peers* peers, int num_poses,
                                      int num_edges, float delta_thresh, float* dx, void* workspace,
                                      size_t workspace_bytes, m3r_stream_t stream) {
+  M3R_NVTX("m3r_gn_solve_step_p2p");
   if (!peers || peers->world < 1 || peers->world > M3R_MAX_PEERS || peers->rank < 0 ||
       peers->rank >= peers->world)
     return M3R_EINVAL;
@@ -884,6 +890,7 @@ extern "C" int m3r_gn_solve_step_p2p(float* Twc, const m3r_gn_peers* peers, int 
 extern "C" int m3r_gn_solve_step(float* Twc, const double* blocks, int num_poses, int num_edges,
                                  float delta_thresh, float* dx, void* workspace,
                                  size_t workspace_bytes, m3r_stream_t stream) {
+  M3R_NVTX("m3r_gn_solve_step");
   if (num_poses < 2 || num_edges <= 0 || !Twc || !blocks || !dx || !workspace) return M3R_EINVAL;
   const GnLayout L = gn_layout(num_poses, num_edges, 0, 0);  // offsets up to `x` need (N, M) only
   if (workspace_bytes < L.xc) return M3R_EWORKSPACE;
@@ -938,6 +945,7 @@ extern "C" int m3r_gauss_newton(const m3r_gn_params* prm, float* Twc, const floa
                                 const float* Q, int num_poses, int n, int num_edges, int max_iter,
                                 float delta_thresh, float* dx, void* workspace,
                                 size_t workspace_bytes, m3r_stream_t stream) {
+  M3R_NVTX("m3r_gauss_newton");
   if (max_iter > 0 && (!idx_ii2jj || !valid_match || !Q)) return M3R_EINVAL;
   return gauss_newton_impl(prm, Twc, Xs, Cs, ii, jj, 0, reference_streams(idx_ii2jj, valid_match, Q),
                            num_poses, n, num_edges, max_iter, delta_thresh, dx, workspace,
@@ -950,6 +958,7 @@ extern "C" int m3r_gauss_newton_packed(const m3r_gn_params* prm, float* Twc, con
                                        const m3r_packed_match* pk1, int split, int num_poses, int n,
                                        int num_edges, int max_iter, float delta_thresh, float* dx,
                                        void* workspace, size_t workspace_bytes, m3r_stream_t stream) {
+  M3R_NVTX("m3r_gauss_newton_packed");
   if (max_iter > 0 && (!pk0 || split < 0 || (split < num_edges && !pk1))) return M3R_EINVAL;
   return gauss_newton_impl(prm, Twc, Xs, Cs, ii, jj, two_way, packed_streams(pk0, pk1, split),
                            num_poses, n, num_edges, max_iter, delta_thresh, dx, workspace,

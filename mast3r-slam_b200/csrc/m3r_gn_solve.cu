@@ -577,6 +577,7 @@ extern "C" void m3r_debug_chol_delay(int delay_us, int which) {
 
 extern "C" int m3r_pose_retr(float* poses, const float* dx, int num_poses, int num_fix,
                              m3r_stream_t stream) {
+  M3R_NVTX("m3r_pose_retr");
   if (num_poses < 0 || num_fix < 0 || !poses || !dx) return M3R_EINVAL;
   const int cnt = num_poses - num_fix;
   if (cnt <= 0) return M3R_OK;

@@ -213,6 +213,7 @@ extern "C" int m3r_iter_proj(const float* rays_img_with_grad, const float* pts_3
                              const float* p_init, int b, int H, int W, int n, int max_iter,
                              float lambda_init, float cost_thresh, float* p_new,
                              uint8_t* converged, m3r_stream_t stream) {
+  M3R_NVTX("m3r_iter_proj");
   if (b < 0 || n < 0 || H < 3 || W < 3 || max_iter < 0) return M3R_EINVAL;
   if (b == 0 || n == 0) return M3R_OK;
   if (!rays_img_with_grad || !pts_3d_norm || !p_init || !p_new || !converged) return M3R_EINVAL;
@@ -248,6 +249,7 @@ extern "C" int m3r_match_iter_proj_fused(const float* rays_img_with_grad, const 
                                          int H, int W, int max_iter, float lambda_init,
                                          float cost_thresh, float dist_thresh, int64_t* p1,
                                          uint8_t* valid, float* p_new, m3r_stream_t stream) {
+  M3R_NVTX("m3r_match_iter_proj_fused");
   return iter_proj_fused_launch(9, rays_img_with_grad, X11, X21, idx_init, b, H, W, max_iter, lambda_init,
                                 cost_thresh, dist_thresh, p1, valid, p_new, stream);
 }
@@ -257,6 +259,7 @@ extern "C" int m3r_match_iter_proj_packed(const float* rays_packed, const float*
                                           int H, int W, int max_iter, float lambda_init,
                                           float cost_thresh, float dist_thresh, int64_t* p1,
                                           uint8_t* valid, float* p_new, m3r_stream_t stream) {
+  M3R_NVTX("m3r_match_iter_proj_packed");
   return iter_proj_fused_launch(12, rays_packed, X11, X21, idx_init, b, H, W, max_iter, lambda_init,
                                 cost_thresh, dist_thresh, p1, valid, p_new, stream);
 }

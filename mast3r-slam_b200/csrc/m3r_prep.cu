@@ -159,6 +159,7 @@ using namespace m3r;
 
 extern "C" int m3r_img_gradient(const float* img, int planes, int H, int W, float* gx, float* gy,
                                 m3r_stream_t stream) {
+  M3R_NVTX("m3r_img_gradient");
   if (planes < 0 || H < 2 || W < 2 || planes > 65535) return M3R_EINVAL;  // reflect padding needs 2 rows / columns
   if (planes == 0) return M3R_OK;
   if (!img || !gx || !gy) return M3R_EINVAL;
@@ -204,10 +205,12 @@ static int match_prep_launch(const float* X11, const float* D11, int b, int H, i
 
 extern "C" int m3r_match_prep(const float* X11, const float* D11, int b, int H, int W, int F,
                               float* rays_img_with_grad, uint16_t* D11h, m3r_stream_t stream) {
+  M3R_NVTX("m3r_match_prep");
   return match_prep_launch<9>(X11, D11, b, H, W, F, rays_img_with_grad, D11h, stream);
 }
 
 extern "C" int m3r_match_prep_packed(const float* X11, const float* D11, int b, int H, int W, int F,
                                      float* rays_packed, uint16_t* D11h, m3r_stream_t stream) {
+  M3R_NVTX("m3r_match_prep_packed");
   return match_prep_launch<12>(X11, D11, b, H, W, F, rays_packed, D11h, stream);
 }

@@ -417,6 +417,7 @@ extern "C" int m3r_refine_matches_f16(const uint16_t* D11, const uint16_t* D21,
                                       const int64_t* p1, int b, int H, int W, int n, int F,
                                       int radius, int dilation_max, int64_t* p1_new,
                                       m3r_stream_t stream) {
+  M3R_NVTX("m3r_refine_matches_f16");
   if (!refine_args_ok(b, H, W, F, radius) || n < 0) return M3R_EINVAL;
   if (b == 0 || n == 0) return M3R_OK;
   if (!D11 || !D21 || !p1 || !p1_new) return M3R_EINVAL;
@@ -434,6 +435,7 @@ extern "C" int m3r_match_refine_fused(const uint16_t* D11h, const float* D21,
                                       const int64_t* p1, int b, int H, int W, int F, int radius,
                                       int dilation_max, int64_t* idx_1_to_2,
                                       m3r_stream_t stream) {
+  M3R_NVTX("m3r_match_refine_fused");
   if (!refine_args_ok(b, H, W, F, radius)) return M3R_EINVAL;
   if (b == 0) return M3R_OK;
   if (!D11h || !D21 || !p1 || !idx_1_to_2) return M3R_EINVAL;
@@ -447,6 +449,7 @@ extern "C" int m3r_match_refine_fused(const uint16_t* D11h, const float* D21,
 extern "C" int m3r_refine_matches_f32(const float* D11, const float* D21, const int64_t* p1,
                                       int b, int H, int W, int n, int F, int radius,
                                       int dilation_max, int64_t* p1_new, m3r_stream_t stream) {
+  M3R_NVTX("m3r_refine_matches_f32");
   if (b < 0 || n < 0 || H <= 0 || W <= 0 || F <= 0 || radius < 0 || b > 65535) return M3R_EINVAL;
   if (b == 0 || n == 0) return M3R_OK;
   if (!D11 || !D21 || !p1 || !p1_new) return M3R_EINVAL;

@@ -489,6 +489,7 @@ extern "C" void m3r_render_default_opts(m3r_render_opts* o) {
 
 extern "C" int m3r_render_clear(uint64_t* fb, int width, int height, uint32_t clear_rgba,
                                 m3r_stream_t stream) {
+  M3R_NVTX("m3r_render_clear");
   if (!fb || width <= 0 || height <= 0) return M3R_EINVAL;
   const size_t count = (size_t)width * height;
   const unsigned long long word = ((unsigned long long)0x3F800000u << 32) | clear_rgba;  // depth 1.0
@@ -518,6 +519,7 @@ extern "C" int m3r_render_surfels(const float* X, const float* C, const float* i
                                   const float* models, int num_keyframes, int H, int W,
                                   const m3r_render_view* view, const m3r_render_opts* opts,
                                   uint64_t* fb, m3r_stream_t stream) {
+  M3R_NVTX("m3r_render_surfels");
   return render_launch(0, X, C, img, models, num_keyframes, H, W, view, opts, fb, stream);
 }
 
@@ -525,11 +527,13 @@ extern "C" int m3r_render_triangles(const float* X, const float* C, const float*
                                     const float* models, int num_keyframes, int H, int W,
                                     const m3r_render_view* view, const m3r_render_opts* opts,
                                     uint64_t* fb, m3r_stream_t stream) {
+  M3R_NVTX("m3r_render_triangles");
   return render_launch(1, X, C, img, models, num_keyframes, H, W, view, opts, fb, stream);
 }
 
 extern "C" int m3r_render_resolve(const uint64_t* fb, int width, int height, uint8_t* rgba,
                                   float* depth, m3r_stream_t stream) {
+  M3R_NVTX("m3r_render_resolve");
   if (!fb || width <= 0 || height <= 0) return M3R_EINVAL;
   const size_t count = (size_t)width * height;
   const int grid = (int)((count + 255) / 256 < (size_t)(kNumSMs * 8) ? (count + 255) / 256 : (size_t)(kNumSMs * 8));

@@ -306,6 +306,7 @@ extern "C" int m3r_track_ray_dist(const float* Xf, const float* Xk, const float*
                                   float huber_k, int max_iters, float rel_error, float delta_norm,
                                   float* T_CkCf, int* status, float* cost, void* workspace,
                                   size_t workspace_bytes, m3r_stream_t stream) {
+  M3R_NVTX("m3r_track_ray_dist");
   if (n <= 0 || max_iters < 0 || !Xf || !Xk || !Qk || !valid || !T_CkCf || !status || !workspace)
     return M3R_EINVAL;
   if (sigma_ray == 0.f || sigma_dist == 0.f) return M3R_EINVAL;
@@ -325,6 +326,7 @@ extern "C" int m3r_track_calib(const float* Xf, const float* meas_k, const float
                                float huber_k, int max_iters, float rel_error, float delta_norm,
                                float* T_CkCf, int* status, float* cost, void* workspace,
                                size_t workspace_bytes, m3r_stream_t stream) {
+  M3R_NVTX("m3r_track_calib");
   if (n <= 0 || max_iters < 0 || !Xf || !meas_k || !Qk || !valid || !valid_meas_k || !K_dev || !T_CkCf ||
       !status || !workspace)
     return M3R_EINVAL;
@@ -380,6 +382,7 @@ extern "C" int m3r_track_ray_dist_noalloc(const float* Xf, const float* Xk, cons
                                           float sigma_dist, float huber_k, int max_iters,
                                           float rel_error, float delta_norm, float* T_CkCf,
                                           int* status, float* cost, m3r_stream_t stream) {
+  M3R_NVTX("m3r_track_ray_dist_noalloc");
   if (n <= 0 || max_iters < 0 || !Xf || !Xk || !Qk || !valid || !T_CkCf || !status) return M3R_EINVAL;
   if (sigma_ray == 0.f || sigma_dist == 0.f) return M3R_EINVAL;
   if (n > M3R_TRACK_NOALLOC_MAX_N) return M3R_ETOOLARGE;
