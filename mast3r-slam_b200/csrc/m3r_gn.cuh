@@ -18,6 +18,8 @@
 //   tickets  : int32[M+2]    per-edge count of finished point-splits (the last one to arrive runs
 //                            the edge's fp64 epilogue), [M] = edges finished in this pass
 #pragma once
+#include <cstdlib>
+
 #include "m3r_common.cuh"
 
 namespace m3r {
@@ -139,6 +141,17 @@ inline void gn_splits(int n, int M, int& S, int& chunk) {
   if (S < 1) S = 1;
 }
 
+// Largest system (in 32-wide panels) that the 32x32 dataflow kernel takes; M3R_GN_SMALL_MAX_NB overrides the
+// default for experiments (profiles/time_gn_threshold.py), read once per process.
+inline int gn_small_max_nb() {
+  static const int v = [] {
+    const char* e = getenv("M3R_GN_SMALL_MAX_NB");
+    const int x = e ? atoi(e) : kGnSmallMaxNb;
+    return x < 1 ? 1 : x;
+  }();
+  return v;
+}
+
 inline GnLayout gn_layout(int N, int M, int Ml, int n) {
   GnLayout L;
   size_t off = 0;
@@ -148,7 +161,7 @@ inline GnLayout gn_layout(int N, int M, int Ml, int n) {
   L.D = 7 * (N - 1);
   L.Dp = (L.D + 1 + kGnNB - 1) / kGnNB * kGnNB;
   L.nbm = 0; L.ntasks = 0;
-  if (L.Dp / kGnNB > kGnSmallMaxNb) {  // large system: macro tiles
+  if (L.Dp / kGnNB > gn_small_max_nb()) {  // large system: macro tiles
     L.Dp = (L.D + 1 + kGnMB - 1) / kGnMB * kGnMB;
     L.nbm = L.Dp / kGnMB;
     L.ntasks = gn_chol64_ntasks(L.nbm);

@@ -16,6 +16,7 @@ KEYS = [
     ("sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_elapsed", "fmaheavy_%", 1),
     ("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "alu_%", 1),
     ("sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_elapsed", "fp64_%", 1),
+    ("sm__pipe_tensor_subpipe_dmma_cycles_active.avg.pct_of_peak_sustained_active", "dmma_%", 1),
     ("smsp__issue_active.avg.pct_of_peak_sustained_active", "issue_%", 1),
     ("sm__warps_active.avg.pct_of_peak_sustained_active", "occ_%", 1),
     ("launch__registers_per_thread", "regs", 1),
