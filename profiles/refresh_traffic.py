@@ -14,7 +14,7 @@ hdr, units = rows[0], rows[1]
 col = {k: i for i, k in enumerate(hdr)}
 scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 want = {"refine_fused": "refine_fused_kernel", "iter_proj_fused": "iter_proj_fused_kernel", "match_prep": "match_prep",
-        "gn_accum_stream_kernel<rays>": "gn_accum_stream_kernel"}
+        "gn_accum_stream_kernel<rays>": "gn_accum_stream_kernel<0, 0>"}
 out = {"source": source}
 for key, pat in want.items():
     best = None
