@@ -307,7 +307,7 @@ void m3r_debug_chol_trace(unsigned long long* device_buf, int capacity_tasks);
  * delay_us <= 0 switches it off (default). */
 void m3r_debug_chol_delay(int delay_us, int which);
 
-/* Diagnostics / tests: systems of more than 16 panels of 32 (more than ~74 keyframes) are
+/* Diagnostics / tests: systems of more than 5 panels of 32 (more than 23 keyframes) are
  * factorised in 64x64 macro tiles by a kernel whose work is a statically ordered task list
  * (csrc/m3r_gn_chol64.cu).  This returns that list for `nbm` 64-wide block columns, built on the
  * host by the same enumeration the device runs: 4 ints per task {I | J << 16, k0 | k1 << 16,

@@ -13,7 +13,7 @@
 //   A        : double[Dp*Dp] augmented normal matrix [H b; b^T 1], padded to 32
 //   x        : double[3*Dp]  the solution x, 1/diag(L), scratch sink
 //   flags    : int32[nb*nb + nb] tile-ready / x-block-ready epochs of the dataflow Cholesky
-//   tasks    : int4[ntasks]  large systems only (Dp > 16 panels): the statically ordered task list of
+//   tasks    : int4[ntasks]  large systems only (Dp > 5 panels of 32): the statically ordered task list of
 //                            the 64x64 macro-tile Cholesky (m3r_gn_chol64.cu), built once per solve
 //   tickets  : int32[M+2]    per-edge count of finished point-splits (the last one to arrive runs
 //                            the edge's fp64 epilogue), [M] = edges finished in this pass
@@ -44,7 +44,10 @@ __device__ __forceinline__ bool gn_stopped(const GnHeader* hdr) {
 
 // ---- large systems: 64x64 macro tiles (m3r_gn_chol64.cu) ----------------------------------
 // A system of more than kGnSmallMaxNb 32-wide panels is padded to a multiple of 64 and
-// factorised by the macro-tile kernel.  The left-looking sum of tile (I,J) over block columns
+// factorised by the macro-tile kernel (measured, profiles/r3/r3_gn_threshold.txt: the macro kernel is
+// level with the 32x32 dataflow kernel at 2 and 4 panels, loses at 3 and 5 — an odd panel count pays for
+// the padding to 64 — and wins from 6 panels on: 97 against 105 us at 7 panels (N = 32), 163 against 228 us
+// at 14 (N = 64), 394 against 583 us at 33 (N = 150)).  The left-looking sum of tile (I,J) over block columns
 // k is cut into chunks; every chunk is one task.  A tile's list tasks cover k in [0, R) and the
 // chunks are laid out FROM THE END: a tail of `t` block columns (the chunk released last, one
 // or two chain steps before the tile is needed, is short), then chunks of kGnKC going down;
@@ -55,7 +58,7 @@ __device__ __forceinline__ bool gn_stopped(const GnHeader* hdr) {
 //   sub-diagonal tile (J+1,J): R = J-1, t = 2; the chain CTA adds k = J-1 itself
 //   any other tile (I >= J+2): R = J-1, t = 4; k = J-1 is alone in the tile's final (TRSM) task
 // Shared by the host (workspace size) and the device (task list, progress counters).
-constexpr int kGnSmallMaxNb = 16;
+constexpr int kGnSmallMaxNb = 5;
 constexpr int kGnMB = 64;
 constexpr int kGnKC = 4;
 constexpr int kGnTailChain = 2;

@@ -1,5 +1,5 @@
-// m3r_gn_chol64.cu — fp64 Cholesky solve of LARGE normal-equation systems (more than 16 panels
-// of 32, i.e. more than ~74 keyframes; BASELINE config 5 has N = 512, D = 3577), sm_100a.
+// m3r_gn_chol64.cu — fp64 Cholesky solve of LARGE normal-equation systems (more than 5 panels
+// of 32, i.e. more than 23 keyframes; BASELINE config 5 has N = 512, D = 3577), sm_100a.
 //
 // Replaces, like m3r_gn_solve.cu for small systems, SparseBlock::solve of the reference
 // (gn_kernels.cu:132-153: Eigen::SimplicialLLT in fp64 on the host) plus the retraction and the

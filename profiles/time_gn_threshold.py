@@ -16,7 +16,7 @@ from tests import synth  # noqa: E402
 dev = torch.device("cuda", 0)
 prm = be._params(be.GN_RAYS, 0.003, 10.0, 0.0, 1.5)
 out = []
-for N in (16, 32, 48, 64, 75, 100, 150, 260):
+for N in [int(v) for v in os.environ.get("M3R_SIZES", "16,32,48,64,75,100,150,260").split(",")]:
     g = synth.make_graph(N=N, counts={1: None, 2: N - 2, 5: N - 5, "random": N // 4}, H=48, W=64, seed=1236, device=dev)
     s = be.GNSolver(prm, g["Twc"].clone(), g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"])
     for _ in range(3):
