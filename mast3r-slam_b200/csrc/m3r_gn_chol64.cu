@@ -47,7 +47,7 @@ constexpr int kStageD = 2 * kPanel;
 constexpr int kTileC = MB * LDC;
 constexpr int kWindow = 8;         // block columns ahead of the chain whose tiles are kept up to date
 constexpr int kMaxSlots = 4096;    // (nbm + 1) * (kWindow + 1) sort groups of the task list
-constexpr int kChainTiles = 6;  // T, X, Lp, Tn, Xn, Y of the chain CTA
+constexpr int kChainTiles = 5;  // T, X, Lp, Tn, Xn of the chain CTA
 constexpr size_t kSmemDoubles =
     (size_t)kStages * kStageD > (size_t)kChainTiles * kTileC ? (size_t)kStages * kStageD : (size_t)kChainTiles * kTileC;
 constexpr size_t kSmemBytes = kSmemDoubles * sizeof(double);
@@ -163,32 +163,6 @@ __device__ __forceinline__ void warp_mma(const double* __restrict__ A, const dou
   const double* pa = A + g * LD;
   const double* pb = B + g * LD;
   for (int kb = 0; kb < k16; kb++) {
-#pragma unroll
-    for (int kk = 0; kk < 4; kk++) {
-      const int k = kb * 16 + frag_k<LD>(q, kk);
-      double av[MI], bv[NI];
-#pragma unroll
-      for (int mi = 0; mi < MI; mi++) av[mi] = pa[mi * 8 * LD + k];
-#pragma unroll
-      for (int ni = 0; ni < NI; ni++) bv[ni] = pb[ni * 8 * LD + k];
-#pragma unroll
-      for (int mi = 0; mi < MI; mi++)
-#pragma unroll
-        for (int ni = 0; ni < NI; ni++) dmma(acc[mi][ni], av[mi], bv[ni]);
-    }
-  }
-}
-
-// the same with a compile-time k extent: fully unrolled, so that a lone warp on its scheduler (the chain
-// CTA's helpers) has the next fragments in flight while the current DMMAs issue
-template <int MI, int NI, int LD, int K16>
-__device__ __forceinline__ void warp_mma_k(const double* __restrict__ A, const double* __restrict__ B,
-                                           double (&acc)[MI][NI][2]) {
-  const int lane = threadIdx.x & 31, g = lane >> 2, q = lane & 3;
-  const double* pa = A + g * LD;
-  const double* pb = B + g * LD;
-#pragma unroll
-  for (int kb = 0; kb < K16; kb++) {
 #pragma unroll
     for (int kk = 0; kk < 4; kk++) {
       const int k = kb * 16 + frag_k<LD>(q, kk);
@@ -494,22 +468,84 @@ __device__ __forceinline__ void run_task(const Args& a, const int4 tk, int epoch
 }
 
 // ------------------------------------------------------------------------------------------
+// Sidekicks: the LAST terms of the two tiles the chain needs next, each on an SM of its own.
+// While the chain CTA is in step J (factorising tile (J,J)), block 1 forms
+//   tile (J+1,J)   -= L(J+1,J-1) L(J,J-1)^T      (k = J-1, the sub-diagonal tile's last term)
+// and block 2
+//   tile (J+1,J+1) -= L(J+1,J-1) L(J+1,J-1)^T    (k = J-1 of the next diagonal tile; k = J is the chain's own)
+// in place, as one more "chunk" of the tile's progress counter.  Both products need L(J+1,J-1) (a list
+// task's TRSM, finished early in step J), block 1 also L(J,J-1), which the chain publishes at the start of
+// step J.  These two products used to run on the chain CTA's idle team; their DMMA streams shared the SM's
+// four fp64 pipes with the POTRFs (4.3 -> 5.1 us each, and the products themselves took 7.5 us on three
+// warps); as list tasks they sat behind the queue.  Here they take ~2 us on an otherwise idle SM.
+// ------------------------------------------------------------------------------------------
+constexpr int LDS2 = 66;  // row stride of the sidekicks' 64x64 operands: 16-byte rows, == 2 (mod 16)
+__device__ __forceinline__ void run_sidekick(const Args& a, int which, int epoch, double* smem) {
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, q = lane & 3;
+  double* Ys = smem;
+  double* Xs = which == 0 ? smem + MB * LDS2 : Ys;
+  // one 32x16 block of outputs per warp: all 8 for tile (J+1,J); the 6 lower ones for the diagonal tile
+  int r0, c0;
+  bool active = true;
+  if (which == 0) { r0 = (warp >> 2) * 32; c0 = (warp & 3) * 16; }
+  else { r0 = warp < 2 ? 0 : 32; c0 = warp < 2 ? warp * 16 : (warp - 2) * 16; active = warp < 6; }
+  for (int J = 1; J + 1 < a.nbm; J++) {
+    const int bi = J + 1, bj = which == 0 ? J : J + 1;
+    const int nbulk = which == 0 ? gn_nch_sub(J) : gn_nch_diag(J + 1);
+    chol_debug_stall(a.c, bi, bj, epoch, 0);
+    if (tid == 0) while (ld_acquire(tile_flag(a, J + 1, J - 1)) != epoch) __nanosleep(20);
+    if (tid == 32 && nbulk) while (ld_acquire(prog_flag(a, bi, bj)) != ((epoch << 12) | nbulk)) __nanosleep(20);
+    if (tid == 64 && which == 0) while (ld_acquire(tile_flag(a, J, J - 1)) != epoch) { }
+    __syncthreads();
+    for (int ch = tid; ch < MB * 32; ch += kThreads) {
+      const int r = ch >> 5, seg = (ch & 31) * 2;
+      cp_async16(Ys + r * LDS2 + seg, a.c.A + (size_t)((J + 1) * MB + r) * a.c.Dp + (size_t)(J - 1) * MB + seg);
+      if (which == 0) cp_async16(Xs + r * LDS2 + seg, a.c.A + (size_t)(J * MB + r) * a.c.Dp + (size_t)(J - 1) * MB + seg);
+    }
+    cp_async_commit();
+    double* tile = a.c.A + (size_t)bi * MB * a.c.Dp + (size_t)bj * MB;
+    double2 base[4][2];
+    if (active) {
+#pragma unroll
+      for (int mi = 0; mi < 4; mi++)
+#pragma unroll
+        for (int ni = 0; ni < 2; ni++)
+          base[mi][ni] = __ldcg(reinterpret_cast<const double2*>(tile + (size_t)(r0 + mi * 8 + g) * a.c.Dp + c0 + ni * 8 + 2 * q));
+    }
+    cp_async_wait<0>();
+    __syncthreads();
+    if (active) {
+      double acc[4][2][2];
+      zero_acc(acc);
+      warp_mma<4, 2, LDS2>(Ys + r0 * LDS2, Xs + c0 * LDS2, 4, acc);
+#pragma unroll
+      for (int mi = 0; mi < 4; mi++)
+#pragma unroll
+        for (int ni = 0; ni < 2; ni++) {
+          double2 v = base[mi][ni];
+          v.x -= acc[mi][ni][0]; v.y -= acc[mi][ni][1];
+          __stcg(reinterpret_cast<double2*>(tile + (size_t)(r0 + mi * 8 + g) * a.c.Dp + c0 + ni * 8 + 2 * q), v);
+        }
+    }
+    chol_debug_stall(a.c, bi, bj, epoch, 1);
+    post_flag_last(prog_flag(a, bi, bj), (epoch << 12) | (nbulk + 1));  // (its barrier also frees the operand buffers)
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // The chain: diagonal tiles and the sub-diagonal tile of every block column, one CTA.
 //
-// One step, J >= 1.  In shared memory: T = tile (J,J) with its bulk chunks (k < J-1) applied,
-// X = tile (J,J-1) with ALL its terms applied, Lp = L(J-1,J-1) from the previous step.
-//   all 8 warps   X <- X Lp^-T                      (trsm64: X is L(J,J-1) now)
-//   all 8 warps   T00 -= X0 X0^T, T10 -= X1 X0^T    (what POTRF(T00) and the TRSM of T10 need)
-//   team 0 (warps 0-3)                  | team 1 (warps 4-7)
-//     POTRF(T00)                        |   publish L(J,J-1); T11 -= X1 X1^T
-//     T10 <- T10 L00^-T                 |   fetch Tn = tile (J+1,J+1) and Xn = tile (J+1,J), bulk chunks applied
-//     ---- barrier ----                 |   ---- barrier ----
-//     T11 -= T10 T10^T                  |   fetch Y = L(J+1,J-1) as soon as its owner has flagged it
-//     POTRF(T11), publish L(J,J)        |   Xn -= Y X^T   (the last term of the next sub-diagonal tile)
-// The publishing (32 KB store, fence, flag), the loads of the next step's tiles and, above all, the
-// last term of the next sub-diagonal tile — which as a list task sat on the critical path with two
-// flag hops, an L2 round trip of the tile and a cold 2-step pipeline (16 us per step instead of
-// the 14 the arithmetic needs) — run beside the two POTRFs, which keep only four warps busy.
+// One step, J >= 1.  In shared memory: T = tile (J,J) with all terms but k = J-1 applied, X = tile (J,J-1)
+// with ALL its terms applied (list chunks plus the sidekicks' last term), Lp = L(J-1,J-1) from the previous step.
+//   all 8 warps   X <- X Lp^-T                      (trsm64: X is L(J,J-1) now), stored to the factor
+//   warps 0-6     T00 -= X0 X0^T, T10 -= X1 X0^T    | warp 7  fence + flag of L(J,J-1)
+//   team 0 (warps 0-3)                               | team 1 (warps 4-7)
+//     tall POTRF: L00 and T10 <- T10 L00^-T          |   T11 -= X1 X1^T
+//     ---- one-way barrier: waits for team 1 ----    |   ---- arrives, does not wait ----
+//     T11 -= T10 T10^T                               |   waits for the sidekicks' chunks of tiles (J+1,J+1), (J+1,J)
+//     POTRF(T11), publish L(J,J)                     |   fetches them (cp.async) as Tn, Xn for the next step
+// Publishing (32 KB store, fence, flag) and the loads of the next step's tiles run beside the two POTRFs, which
+// keep only four warps busy; the DMMA products for the next tiles' last terms run on two other SMs (above).
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ void team_wait(const int* f, int value, int team) {
   if ((threadIdx.x & 127) == 0) while (ld_acquire(f) != value) __nanosleep(20);
@@ -549,7 +585,6 @@ __device__ __forceinline__ void run_chain(const Args& a, int epoch, double* smem
   double* Lp = smem + 2 * kTileC;
   double* Tn = smem + 3 * kTileC;
   double* Xn = smem + 4 * kTileC;
-  double* Y = smem + 5 * kTileC;
   double* dT = s_dinv;
   double* dP = s_dinv + MB;
   load_tile64(a.c.A, a.c.Dp, 0, 0, T);
@@ -559,8 +594,15 @@ __device__ __forceinline__ void run_chain(const Args& a, int epoch, double* smem
     const unsigned long long t_begin = a.c.trace ? gtimer() : 0ull;
     if (J > 0) {
       trsm64(X, Lp, dP);
-      {  // T00 -= X0 X0^T (warps 0-3), T10 -= X1 X0^T (warps 4-7); 16x16 outputs per warp
-        const int r0 = team * 32 + (w >> 1) * 16, c0 = (w & 1) * 16;
+      // L(J,J-1) goes out at once: sidekick 1 and the column's list tasks wait for it.  Warp 7 fences and flags
+      // while warps 0-6 form  T00 -= X0 X0^T (3 lower 16x16 blocks)  and  T10 -= X1 X0^T (4 blocks).
+      store_tile64(a.c.A, a.c.Dp, J, J - 1, X);
+      __syncthreads();
+      if (warp == 7) {
+        if ((tid & 31) == 0) { __threadfence(); st_release(tile_flag(a, J, J - 1), epoch); }
+      } else {
+        const int r0 = warp < 3 ? (warp == 0 ? 0 : 16) : 32 + ((warp - 3) >> 1) * 16;
+        const int c0 = warp < 3 ? (warp == 2 ? 16 : 0) : ((warp - 3) & 1) * 16;
         double acc[2][2][2];
         zero_acc(acc);
         warp_mma<2, 2, LDC>(X + r0 * LDC, X + c0 * LDC, 4, acc);
@@ -596,89 +638,41 @@ __device__ __forceinline__ void run_chain(const Args& a, int epoch, double* smem
       // L(J,J) and 1/diag.  The fence stalls its warp for ~1 us: by now team 0 only waits for team 1.
       team_publish_tile64(a.c.A, a.c.Dp, J, J, T, tile_flag(a, J, J), epoch, 0);
     } else {
-      // warp 4 publishes L(J,J-1) on its own (store, fence, flag: ~1.5 us) and then rests: it shares its
-      // scheduler and fp64 pipe with warp 0, whose POTRF is the critical path of the whole factorisation
-      // (with DMMA streams on all four sub-partitions POTRF(T11) took 7.2 us instead of 4).  Warps 5-7
-      // do the arithmetic: T11 -= X1 X1^T first (team 0 waits for it), then the next step's tiles.
+      // team 1: T11 -= X1 X1^T (team 0 waits for it), then the next step's two tiles, whose last terms the
+      // sidekick CTAs have added by now (progress counters one past the list's chunks)
       unsigned long long q0 = 0ull, q1 = 0ull, q2 = 0ull;
-      if (w == 0) {
-        cta_arrive(3);  // (1) does not touch T11
-        const int lane = tid & 31;
-        if (J > 0) {
-          double* dst = a.c.A + (size_t)J * MB * a.c.Dp + (size_t)(J - 1) * MB;
-          for (int idx = lane; idx < MB * MB; idx += 32) __stcg(dst + (size_t)(idx >> 6) * a.c.Dp + (idx & 63), X[(idx >> 6) * LDC + (idx & 63)]);
-          __syncwarp();
-          if (lane == 0) { __threadfence(); st_release(tile_flag(a, J, J - 1), epoch); }
-        }
-        if (J + 1 < a.nbm) {  // Xn = tile (J+1,J): its bulk chunks are normally in long before
-          const int ns = gn_nch_sub(J);
-          if (lane == 0 && ns) while (ld_acquire(prog_flag(a, J + 1, J)) != ((epoch << 12) | ns)) __nanosleep(20);
-          __syncwarp();
-          // 8-byte cp.async: the rows of a chain tile are 8-byte aligned only; each of these lines is read
-          // once per launch by this SM, right after an acquire
-          for (int idx = lane; idx < MB * MB; idx += 32)
-            cp_async8(Xn + (idx >> 6) * LDC + (idx & 63), a.c.A + (size_t)((J + 1) * MB + (idx >> 6)) * a.c.Dp + J * MB + (idx & 63));
-          cp_async_commit();
-          cp_async_wait<0>();
-          asm volatile("bar.arrive 5, 128;" ::: "memory");  // Xn is in shared memory (warps 5-7 wait for it)
-        }
-      } else {
-        const int t3 = tid - 160;  // 0..95
-        if (J > 0) {
+      if (J > 0) {
 #pragma unroll 1
-          for (int blk = w - 1; blk < 8; blk += 3) {  // T11 -= X1 X1^T in 16x8 blocks
-            const int r0 = 32 + (blk >> 2) * 16, c0 = 32 + (blk & 3) * 8;
-            double acc[2][1][2];
-            zero_acc(acc);
-            warp_mma<2, 1, LDC>(X + r0 * LDC, X + c0 * LDC, 4, acc);
-            sub_acc_smem(T, r0, c0, acc);
-          }
-        }
-        cta_arrive(3);  // (1) team 0 may touch T11 now; this team does not wait for it
-        if (a.c.trace) q0 = gtimer();
-        if (J + 1 < a.nbm) {
-          // Tn = tile (J+1,J+1) once its bulk chunks are in, Y = L(J+1,J-1) once its owner has flagged it
-          const int nd = gn_nch_diag(J + 1);
-          if (t3 == 0 && nd) while (ld_acquire(prog_flag(a, J + 1, J + 1)) != ((epoch << 12) | nd)) __nanosleep(20);
-          if (t3 == 32 && J > 0) while (ld_acquire(tile_flag(a, J + 1, J - 1)) != epoch) __nanosleep(20);
-          asm volatile("bar.sync 4, 96;" ::: "memory");
-          if (a.c.trace) q1 = gtimer();
-          for (int idx = t3; idx < MB * MB; idx += 96) {
-            const int rr = idx >> 6, cc = idx & 63;
-            cp_async8(Tn + rr * LDC + cc, a.c.A + (size_t)((J + 1) * MB + rr) * a.c.Dp + (J + 1) * MB + cc);
-            if (J > 0) cp_async8(Y + rr * LDC + cc, a.c.A + (size_t)((J + 1) * MB + rr) * a.c.Dp + (J - 1) * MB + cc);
-          }
-          cp_async_commit();
-          cp_async_wait<0>();
-          asm volatile("bar.sync 4, 96;" ::: "memory");
-          if (a.c.trace) q2 = gtimer();
-          // The last terms of the next step's two tiles, with Y = L(J+1,J-1) and X = L(J,J-1) in shared memory,
-          // in blocks of 32x16 outputs:  Tn -= Y Y^T (k = J-1 of tile (J+1,J+1), 6 lower blocks) first, then,
-          // when warp 4 has brought Xn in,  Xn -= Y X^T (k = J-1 of tile (J+1,J), 8 blocks).
-          if (J > 0) {
-#pragma unroll 1
-            for (int blk = w - 1; blk < 6; blk += 3) {
-              const int r0 = blk < 2 ? 0 : 32, c0 = blk < 2 ? blk * 16 : (blk - 2) * 16;
-              double acc[4][2][2];
-              zero_acc(acc);
-              warp_mma<4, 2, LDC>(Y + r0 * LDC, Y + c0 * LDC, 4, acc);
-              sub_acc_smem(Tn, r0, c0, acc);
-            }
-          }
-          asm volatile("bar.sync 5, 128;" ::: "memory");
-          if (J > 0) {
-#pragma unroll 1
-            for (int blk = w - 1; blk < 8; blk += 3) {
-              const int r0 = (blk >> 2) * 32, c0 = (blk & 3) * 16;
-              double acc[4][2][2];
-              zero_acc(acc);
-              warp_mma<4, 2, LDC>(Y + r0 * LDC, X + c0 * LDC, 4, acc);
-              sub_acc_smem(Xn, r0, c0, acc);
-            }
-          }
+        for (int blk = w; blk < 8; blk += 4) {  // 16x8 blocks
+          const int r0 = 32 + (blk >> 2) * 16, c0 = 32 + (blk & 3) * 8;
+          double acc[2][1][2];
+          zero_acc(acc);
+          warp_mma<2, 1, LDC>(X + r0 * LDC, X + c0 * LDC, 4, acc);
+          sub_acc_smem(T, r0, c0, acc);
         }
       }
-      if (tid == 160) {  // warps 5-7: T11 term done, inputs of the next step flagged, tiles loaded | .., .., done
+      cta_arrive(3);  // (1) team 0 may touch T11 now; this team does not wait for it
+      if (a.c.trace) q0 = gtimer();
+      if (J + 1 < a.nbm) {
+        const int extra = J > 0 ? 1 : 0;  // the sidekicks' chunk
+        const int nd = gn_nch_diag(J + 1) + extra, ns = gn_nch_sub(J) + extra;
+        const int lt = tid & 127;
+        if (lt == 0 && nd) while (ld_acquire(prog_flag(a, J + 1, J + 1)) != ((epoch << 12) | nd)) __nanosleep(20);
+        if (lt == 32 && ns) while (ld_acquire(prog_flag(a, J + 1, J)) != ((epoch << 12) | ns)) __nanosleep(20);
+        team_sync(1);
+        if (a.c.trace) q1 = gtimer();
+        // 8-byte cp.async: the rows of a chain tile are 8-byte aligned only; each of these lines is read once
+        // per launch by this SM, right after an acquire
+        for (int idx = lt; idx < MB * MB; idx += 128) {
+          const int rr = idx >> 6, cc = idx & 63;
+          cp_async8(Tn + rr * LDC + cc, a.c.A + (size_t)((J + 1) * MB + rr) * a.c.Dp + (J + 1) * MB + cc);
+          cp_async8(Xn + rr * LDC + cc, a.c.A + (size_t)((J + 1) * MB + rr) * a.c.Dp + J * MB + cc);
+        }
+        cp_async_commit();
+        cp_async_wait<0>();
+        if (a.c.trace) q2 = gtimer();
+      }
+      if (tid == 128) {  // team 1's timeline: T11 term done, next tiles flagged, loaded
         const int base = a.nbm + a.ntasks + 2 * a.nbm;
         trace_put3(a.c, base + 2 * J, 4, J, J, q0, q1, q2);
         trace_put3(a.c, base + 2 * J + 1, 5, J, J, q2, q2, gtimer());
@@ -908,6 +902,8 @@ chol64_kernel(const Args a) {
   const int G = gridDim.x, cta = blockIdx.x;
   if (cta == 0) {
     run_chain(a, epoch, smem, s_dinv);
+  } else if (cta <= 2) {
+    run_sidekick(a, cta - 1, epoch, smem);
   } else {
     int* queue = a.c.flags + queue_index(a.nbm);
     if (threadIdx.x == 0) s_task = atomicAdd(queue, 1);
@@ -969,8 +965,8 @@ int gn_chol64_launch(float* Twc, int N, float delta_thresh, float* dx, void* ws,
   M3R_TRY(check_cuda(cudaFuncSetAttribute(c64::chol64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)c64::kSmemBytes)));
   int grid = c64::max_ctas();
-  if (grid < 2) return M3R_ELAUNCH;  // the chain CTA and at least one worker must be co-resident
-  if (grid > 1 + L.ntasks) grid = 1 + (L.ntasks > 0 ? L.ntasks : 1);
+  if (grid < 4) return M3R_ELAUNCH;  // the chain CTA, two sidekicks and at least one worker must be co-resident
+  if (grid > 3 + L.ntasks) grid = 3 + (L.ntasks > 0 ? L.ntasks : 1);
   void* args[] = {&a};
   const cudaError_t e = cudaLaunchCooperativeKernel((const void*)c64::chol64_kernel, dim3(grid),
                                                     dim3(c64::kThreads), args, c64::kSmemBytes, st);
