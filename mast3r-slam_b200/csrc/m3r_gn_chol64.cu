@@ -547,18 +547,6 @@ __device__ __forceinline__ void run_sidekick(const Args& a, int which, int epoch
 // Publishing (32 KB store, fence, flag) and the loads of the next step's tiles run beside the two POTRFs, which
 // keep only four warps busy; the DMMA products for the next tiles' last terms run on two other SMs (above).
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ void team_wait(const int* f, int value, int team) {
-  if ((threadIdx.x & 127) == 0) while (ld_acquire(f) != value) __nanosleep(20);
-  team_sync(team);
-}
-__device__ __forceinline__ void team_load_tile64(const double* __restrict__ A, int Dp, int bi, int bj, double* s) {
-  const double* src = A + (size_t)bi * MB * Dp + (size_t)bj * MB;
-  for (int idx = threadIdx.x & 127; idx < MB * MB / 2; idx += 128) {
-    const int r = idx >> 5, c2 = (idx & 31) * 2;
-    const double2 v = __ldcg(reinterpret_cast<const double2*>(src + (size_t)r * Dp + c2));
-    s[r * LDC + c2] = v.x; s[r * LDC + c2 + 1] = v.y;
-  }
-}
 // the calling team stores the shared tile to global tile (bi,bj) and raises `flag`
 __device__ __forceinline__ void team_publish_tile64(double* __restrict__ A, int Dp, int bi, int bj, const double* s,
                                                     int* flag, int epoch, int team) {

@@ -292,6 +292,36 @@ def test_gn_edge_cases(backends, orc):
     assert float((T - g2["T_gt"]).abs().max()) < 0.5 * float((g2["Twc"] - g2["T_gt"]).abs().max())
 
 
+@pytest.mark.parametrize("N", [32, 100])
+def test_macro_tile_cholesky_failure_and_early_exit(backends, N):
+    """The 64x64 macro-tile kernel (systems of more than 5 panels of 32): a singular system (no usable match) is
+    a zero step with the poses untouched — SimplicialLLT failure in the reference, gn_kernels.cu:142-150 — also
+    when only ONE keyframe is cut off (non-positive pivot deep inside the factorisation: the chain, its
+    sidekicks, the list workers and the back substitution all still have to finish); a converged solve turns the
+    remaining iterations into no-ops; and a solve after a failed one on the same inputs is unaffected."""
+    g = synth.make_graph(N=N, counts={1: None, 2: N - 2, "random": N // 4}, H=24, W=32, seed=1300 + N, device=DEV)
+    args = (g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"])
+    T = g["Twc"].clone()
+    (dx,) = backends.gauss_newton_rays(T, *args, torch.zeros_like(g["valid"]), g["Q"], 0.003, 10.0, 0.0, 1.5, 3, 0.0)
+    torch.cuda.synchronize()
+    assert torch.equal(T, g["Twc"]) and float(dx.abs().max()) == 0.0
+    # cut off keyframe N-3: every edge that touches it loses its matches => its 7x7 diagonal block is zero
+    cut = ((g["ii"] == N - 3) | (g["jj"] == N - 3)).view(-1, 1, 1)
+    valid = g["valid"] & ~cut
+    T = g["Twc"].clone()
+    (dx,) = backends.gauss_newton_rays(T, *args, valid, g["Q"], 0.003, 10.0, 0.0, 1.5, 2, 0.0)
+    torch.cuda.synchronize()
+    assert torch.equal(T, g["Twc"]) and float(dx.abs().max()) == 0.0
+    # the regular solve, then the same with an early exit after the first iteration
+    T1 = g["Twc"].clone()
+    (dx1,) = backends.gauss_newton_rays(T1, *args, g["valid"], g["Q"], 0.003, 10.0, 0.0, 1.5, 1, 0.0)
+    T2 = g["Twc"].clone()
+    (dx2,) = backends.gauss_newton_rays(T2, *args, g["valid"], g["Q"], 0.003, 10.0, 0.0, 1.5, 5, 1e9)
+    torch.cuda.synchronize()
+    assert float(dx1.abs().max()) > 0 and torch.isfinite(dx1).all()
+    assert torch.equal(T1, T2) and torch.equal(dx1, dx2)
+
+
 def test_pose_retr_vs_oracle(backends, orc):
     gen = torch.Generator(device=DEV).manual_seed(11)
     N = 300
