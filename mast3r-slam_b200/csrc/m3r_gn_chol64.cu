@@ -50,7 +50,7 @@ constexpr int kMaxSlots = 4096;    // (nbm + 1) * (kWindow + 1) sort groups of t
 constexpr int kChainTiles = 5;  // T, X, Lp, Tn, Xn of the chain CTA
 constexpr size_t kSmemDoubles =
     (size_t)kStages * kStageD > (size_t)kChainTiles * kTileC ? (size_t)kStages * kStageD : (size_t)kChainTiles * kTileC;
-constexpr size_t kSmemBytes = kSmemDoubles * sizeof(double);
+constexpr size_t kSmemBytesFact = kSmemDoubles * sizeof(double);  // factorisation; the back substitution may need more (below)
 
 enum { kTaskUpdate = 0, kTaskFinal = 1 };
 
@@ -684,7 +684,7 @@ __device__ __forceinline__ void run_chain(const Args& a, int epoch, double* smem
 // sum, m > c + kBackNear, is the work of a helper CTA per column that follows the chain kBackNear
 // steps behind, so its flag is normally up when the chain arrives.  Fixed summation order.
 // ------------------------------------------------------------------------------------------
-constexpr int kBackNear = 3;
+constexpr int kBackNear = 2;
 __device__ __forceinline__ int* far_flag(const Args& a, int c) { return a.c.flags + 2 * a.nbm * a.nbm + a.nbm + c; }
 __device__ __forceinline__ int* winv_flag(const Args& a, int c) { return a.c.flags + queue_index(a.nbm) + 1 + c; }
 
@@ -745,135 +745,164 @@ __device__ __forceinline__ void back_far(const Args& a, int c, int epoch, double
   trace_put(a.c, slot, 2, c, 0, t_begin, t_ready);
 }
 
+// The chain of the back substitution (block 0).  One step per block column c, descending; roles by warp:
+//   warp 0      the solve: rhs = y_c - far_c - near sums, then x_c = L_cc^-T rhs as three 32x32 matrix-vector
+//               products with the block inverses; x_c goes to the ring in shared memory and to global memory
+//   warps 1-6   the near part of the sum, sum_{m = c+1 .. c+kBackNear} L(m,c)^T x_m, from tiles that a
+//               cp.async ring brought into shared memory ONE STEP EARLIER, and the cp.async of the next step
+//   warp 7      fence + flag of x_c (it has no loads in flight, so the fence is short); polls the flags the
+//               NEXT step needs while the others work, so that no acquire round trip sits on the chain
+// Everything a step loads — kBackNear near tiles and the diagonal tile, 96 KB — goes through cp.async into one
+// of two shared-memory slots: no registers are tied up by loads in flight (an earlier form kept them in 160
+// registers per thread across the solve; at the 255-register cap the solve's own loads were then serialised,
+// 2 900 cycles for 96 fma, and the step took 3.7 us), and the issuing warps are not the solving one (the load
+// queue of one SM takes ~2 300 cycles to accept a step's loads).
+constexpr int kBackSlot = kBackNear * MB * MB + MB * LDS2;  // doubles per slot: near tiles [64][64], diagonal [64][66]
+constexpr int kBackScratch = 16 * MB;                       // xr, sred, ex, xb
+constexpr size_t kBackSmemBytes = (size_t)(kBackScratch + 2 * kBackSlot) * sizeof(double);
+constexpr size_t kSmemBytes = kSmemBytesFact > kBackSmemBytes ? kSmemBytesFact : kBackSmemBytes;  // 206 848 B
+static_assert(kSmemBytes <= 227 * 1024, "dynamic shared memory of chol64_kernel exceeds the 227 KB of sm_100a");
+
 __device__ __forceinline__ void back_chain(const Args& a, int epoch, double* smem, int slot0) {
-  const int tid = threadIdx.x, j2 = tid & 31, p8 = tid >> 5, lane = tid & 31;  // near sums: columns 2 j2, 2 j2 + 1; rows 8 p8 ..
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int nbm = a.nbm, Dp = a.c.Dp, D = a.c.D;
+  // warp 4 shares its scheduler (and its queue towards the load/store unit) with warp 0: it is the one that
+  // stays quiet; the six loaders are warps 1-3 and 5-7
+  const bool loader = warp != 0 && warp != 4;
+  const int part = warp < 4 ? warp - 1 : warp - 2;  // 0..5 among the loaders
   double* xr = smem;                       // ring of the last 4 x blocks
-  double* sred = smem + 4 * MB;            // [8][64] partial near sums
-  double* dg = smem + 16 * MB;             // two diagonal tiles [64][LDC] (after xr, sred, ex, xb: 928 doubles)
-  double2 nt[kBackNear][8];
-  double2 dreg[MB * MB / 2 / kThreads];
-  double yv = 0.0, dv = 0.0;
-  // loads of step c, issued one step ahead: near tiles L(c+1+i, c), the diagonal tile, y_c, 1/diag
+  double* sred = smem + 4 * MB;            // [6][64] partial near sums
+  double* xb = smem + 10 * MB;             // [64] exchange inside warp 0
+  double* farv = smem + 11 * MB;           // [2][64] far sums of this and the next step (fetched by warp 4)
+  double* slots = smem + kBackScratch;
+  // loads of step c into slot c & 1 (warps 1-6, 192 threads): near tiles L(c+1+i, c) and the diagonal tile
   auto issue = [&](int c) {
+    double* sl = slots + (c & 1) * kBackSlot;
+    const int t6 = part * 32 + lane;
 #pragma unroll
     for (int i = 0; i < kBackNear; i++) {
       const int m = c + 1 + i;
       if (m < nbm) {
-        const double* T = a.c.A + (size_t)(m * MB + p8 * 8) * Dp + (size_t)c * MB + 2 * j2;
-#pragma unroll
-        for (int r = 0; r < 8; r++) nt[i][r] = __ldcg(reinterpret_cast<const double2*>(T + (size_t)r * Dp));
+        const double* T = a.c.A + (size_t)m * MB * Dp + (size_t)c * MB;
+        for (int ch = t6; ch < MB * 32; ch += 192) cp_async16(sl + i * MB * MB + (ch >> 5) * MB + (ch & 31) * 2, T + (size_t)(ch >> 5) * Dp + (ch & 31) * 2);
       }
     }
-    const double* src = a.c.A + (size_t)c * MB * Dp + (size_t)c * MB;
-#pragma unroll
-    for (int qd = 0; qd < MB * MB / 2 / kThreads; qd++) {
-      const int idx = tid + qd * kThreads;
-      dreg[qd] = __ldcg(reinterpret_cast<const double2*>(src + (size_t)(idx >> 5) * Dp + (idx & 31) * 2));
-    }
-    if (tid < MB) {
-      const int gi = c * MB + tid;
-      yv = gi < D ? __ldcg(a.c.A + (size_t)D * Dp + gi) : 0.0;
-      dv = __ldcg(a.c.x + Dp + gi);
-    }
+    const double* T = a.c.A + (size_t)c * MB * Dp + (size_t)c * MB;
+    double* dg = sl + kBackNear * MB * MB;
+    for (int ch = t6; ch < MB * 32; ch += 192) cp_async16(dg + (ch >> 5) * LDS2 + (ch & 31) * 2, T + (size_t)(ch >> 5) * Dp + (ch & 31) * 2);
+    cp_async_commit();
   };
-  auto land = [&](int c) {  // the diagonal tile of step c into its shared-memory buffer
-    double* d = dg + (c & 1) * kTileC;
-#pragma unroll
-    for (int qd = 0; qd < MB * MB / 2 / kThreads; qd++) {
-      const int idx = tid + qd * kThreads;
-      d[(idx >> 5) * LDC + (idx & 31) * 2] = dreg[qd].x;
-      d[(idx >> 5) * LDC + (idx & 31) * 2 + 1] = dreg[qd].y;
-    }
-  };
-  // winv_flag(c): the block inverses inside the diagonal tile of column c are written — needed BEFORE
-  // the loads of step c are issued (one step ahead); far_flag(c): the far sum, needed in step c.
-  // Both are polled one step early by a thread that has nothing else to do during the solve, so
-  // that no acquire round trip sits on the chain.
-  auto poll = [&](int c) {  // everything step c needs
+  // winv_flag(c): the block inverses inside the diagonal tile of column c are written (needed before the loads of
+  // step c are issued); far_flag(c): the far sum of column c (needed by step c's rhs)
+  auto poll = [&](int c) {  // what step c itself and the issue inside step c need
     if (c > 0) while (ld_acquire(winv_flag(a, c - 1)) != epoch) { }
     if (c + kBackNear + 1 <= nbm - 1) while (ld_acquire(far_flag(a, c)) != epoch) { }
   };
+  double yA = 0.0, yB = 0.0, iA = 0.0, iB = 0.0;  // warp 0: y_c and 1/diag(L_cc), entries lane and 32 + lane
+  auto load_y = [&](int c) {
+    const int gA = c * MB + lane, gB = gA + 32;
+    yA = gA < D ? __ldcg(a.c.A + (size_t)D * Dp + gA) : 0.0;
+    yB = gB < D ? __ldcg(a.c.A + (size_t)D * Dp + gB) : 0.0;
+    iA = __ldcg(a.c.x + Dp + gA);
+    iB = __ldcg(a.c.x + Dp + gB);
+  };
   if (tid == 0) { while (ld_acquire(winv_flag(a, nbm - 1)) != epoch) { } poll(nbm - 1); }
   __syncthreads();
-  issue(nbm - 1);
-  land(nbm - 1);
-  __syncthreads();
+  if (loader) issue(nbm - 1);
+  if (warp == 0) load_y(nbm - 1);
   for (int c = nbm - 1; c >= 0; c--) {
     const unsigned long long t_begin = a.c.trace ? gtimer() : 0ull;
-    // near part of the sum (x of the last kBackNear steps is in the ring)
-    double s0 = 0.0, s1 = 0.0;
+    const double* sl = slots + (c & 1) * kBackSlot;
+    if (loader) cp_async_wait<0>();
+    __syncthreads();  // (T) slot c & 1 has landed; x_{c+1} is in the ring
+    if (loader) {
+      // rows [r_lo, r_hi) of every near tile, columns 2 lane and 2 lane + 1
+      const int r_lo = part * MB / 6, r_hi = (part + 1) * MB / 6;
+      double s0 = 0.0, s1 = 0.0;
 #pragma unroll
-    for (int i = 0; i < kBackNear; i++) {
-      const int m = c + 1 + i;
-      if (m < nbm) {
-        const double* xm = xr + (m & 3) * MB + p8 * 8;
-#pragma unroll
-        for (int r = 0; r < 8; r++) { s0 = fma(nt[i][r].x, xm[r], s0); s1 = fma(nt[i][r].y, xm[r], s1); }
+      for (int i = 0; i < kBackNear; i++) {
+        const int m = c + 1 + i;
+        if (m < nbm) {
+          const double* tile = sl + i * MB * MB + 2 * lane;
+          const double* xm = xr + (m & 3) * MB;
+          for (int r = r_lo; r < r_hi; r++) {
+            const double2 v = *reinterpret_cast<const double2*>(tile + r * MB);
+            s0 = fma(v.x, xm[r], s0); s1 = fma(v.y, xm[r], s1);
+          }
+        }
       }
+      sred[part * MB + 2 * lane] = s0; sred[part * MB + 2 * lane + 1] = s1;
     }
-    sred[p8 * MB + 2 * j2] = s0; sred[p8 * MB + 2 * j2 + 1] = s1;
-    const double y_c = yv, d_c = dv;  // this step's; the registers are reloaded for the next one now
-    const bool has_far = c + kBackNear + 1 <= nbm - 1;
-    __syncthreads();
-    if (c > 0) issue(c - 1);
-    if (tid == 64 && c > 0) poll(c - 1);  // done before this step's last barrier
+    __syncthreads();  // (A) near sums are in; the other slot is free
     const unsigned long long t_ready = a.c.trace ? gtimer() : 0ull;
-    // rhs and 1/diag of the two 32-blocks meet in warp 0: lane t holds entries t (A) and 32 + t (B)
-    double* ex = sred + 8 * MB;  // [2][64]: rhs, dinv
-    if (tid < MB) {
-      double rhs = y_c - (((sred[tid] + sred[MB + tid]) + (sred[2 * MB + tid] + sred[3 * MB + tid])) +
-                          ((sred[4 * MB + tid] + sred[5 * MB + tid]) + (sred[6 * MB + tid] + sred[7 * MB + tid])));
-      if (has_far) rhs -= __ldcg(a.c.x + 2 * Dp + c * MB + tid);
-      if (c * MB + tid >= D) rhs = 0.0;
-      ex[tid] = rhs; ex[MB + tid] = d_c;
-    }
-    __syncthreads();
-    if (tid < 32) {
+    if (loader) {
+      if (c > 0) issue(c - 1);
+    } else if (warp == 4) {
+      if (c > 0) {  // for the next step, off the chain: its flags, then its far sum into shared memory
+        if (lane == 0) poll(c - 1);
+        __syncwarp();
+        if (c - 1 + kBackNear + 1 <= nbm - 1) {
+          farv[((c - 1) & 1) * MB + lane] = __ldcg(a.c.x + 2 * Dp + (c - 1) * MB + lane);
+          farv[((c - 1) & 1) * MB + 32 + lane] = __ldcg(a.c.x + 2 * Dp + (c - 1) * MB + 32 + lane);
+        }
+      }
+    } else {
       // x = L_cc^-T rhs with the inverses W^T = L^-T of the two 32x32 diagonal blocks (strictly upper part
       // of the block, diagonal = 1/diag(L)):  x_B = W11^T r_B ; r_A -= L10^T x_B ; x_A = W00^T r_A
-      const double* Ld = dg + (c & 1) * kTileC;
-      double* xb = ex + 2 * MB;  // [32] exchange
-      const double rB = ex[32 + lane], iA = ex[MB + lane], iB = ex[MB + 32 + lane];
-      double rA = ex[lane];
-      double p0 = iB * rB, p1 = 0.0, p2 = 0.0, p3 = 0.0;
+      const double* Ld = sl + kBackNear * MB * MB;
+      const bool has_far = c + kBackNear + 1 <= nbm - 1;
+      double rA = yA, rB = yB;
+#pragma unroll
+      for (int pp = 0; pp < 6; pp++) { rA -= sred[pp * MB + lane]; rB -= sred[pp * MB + 32 + lane]; }
+      if (has_far) { rA -= farv[(c & 1) * MB + lane]; rB -= farv[(c & 1) * MB + 32 + lane]; }
+      if (c * MB + lane >= D) rA = 0.0;
+      if (c * MB + 32 + lane >= D) rB = 0.0;
+      const double dA = iA, dB = iB;
+      if (c > 0) load_y(c - 1);  // next step's y and 1/diag, in flight during the solve
+      xb[32 + lane] = rB;
+      __syncwarp();
+      double p0 = dB * rB, p1 = 0.0, p2 = 0.0, p3 = 0.0;
 #pragma unroll
       for (int k = 0; k < 32; k += 4) {
-        if (k + 0 > lane) p0 = fma(Ld[(32 + lane) * LDC + 32 + k + 0], ex[32 + k + 0], p0);
-        if (k + 1 > lane) p1 = fma(Ld[(32 + lane) * LDC + 32 + k + 1], ex[32 + k + 1], p1);
-        if (k + 2 > lane) p2 = fma(Ld[(32 + lane) * LDC + 32 + k + 2], ex[32 + k + 2], p2);
-        if (k + 3 > lane) p3 = fma(Ld[(32 + lane) * LDC + 32 + k + 3], ex[32 + k + 3], p3);
+        const double l0 = k + 0 > lane ? Ld[(32 + lane) * LDS2 + 32 + k + 0] : 0.0;
+        const double l1 = k + 1 > lane ? Ld[(32 + lane) * LDS2 + 32 + k + 1] : 0.0;
+        const double l2 = k + 2 > lane ? Ld[(32 + lane) * LDS2 + 32 + k + 2] : 0.0;
+        const double l3 = k + 3 > lane ? Ld[(32 + lane) * LDS2 + 32 + k + 3] : 0.0;
+        p0 = fma(l0, xb[32 + k + 0], p0); p1 = fma(l1, xb[32 + k + 1], p1);
+        p2 = fma(l2, xb[32 + k + 2], p2); p3 = fma(l3, xb[32 + k + 3], p3);
       }
       const double xB = (p0 + p1) + (p2 + p3);
+      __syncwarp();
       xb[lane] = xB;
       __syncwarp();
       p0 = p1 = p2 = p3 = 0.0;
 #pragma unroll
       for (int k = 0; k < 32; k += 4) {
-        p0 = fma(Ld[(32 + k + 0) * LDC + lane], xb[k + 0], p0);
-        p1 = fma(Ld[(32 + k + 1) * LDC + lane], xb[k + 1], p1);
-        p2 = fma(Ld[(32 + k + 2) * LDC + lane], xb[k + 2], p2);
-        p3 = fma(Ld[(32 + k + 3) * LDC + lane], xb[k + 3], p3);
+        p0 = fma(Ld[(32 + k + 0) * LDS2 + lane], xb[k + 0], p0);
+        p1 = fma(Ld[(32 + k + 1) * LDS2 + lane], xb[k + 1], p1);
+        p2 = fma(Ld[(32 + k + 2) * LDS2 + lane], xb[k + 2], p2);
+        p3 = fma(Ld[(32 + k + 3) * LDS2 + lane], xb[k + 3], p3);
       }
       rA -= (p0 + p1) + (p2 + p3);
       __syncwarp();
       xb[lane] = rA;
       __syncwarp();
-      p0 = iA * rA; p1 = p2 = p3 = 0.0;
+      p0 = dA * rA; p1 = p2 = p3 = 0.0;
 #pragma unroll
       for (int k = 0; k < 32; k += 4) {
-        if (k + 0 > lane) p0 = fma(Ld[lane * LDC + k + 0], xb[k + 0], p0);
-        if (k + 1 > lane) p1 = fma(Ld[lane * LDC + k + 1], xb[k + 1], p1);
-        if (k + 2 > lane) p2 = fma(Ld[lane * LDC + k + 2], xb[k + 2], p2);
-        if (k + 3 > lane) p3 = fma(Ld[lane * LDC + k + 3], xb[k + 3], p3);
+        const double l0 = k + 0 > lane ? Ld[lane * LDS2 + k + 0] : 0.0;
+        const double l1 = k + 1 > lane ? Ld[lane * LDS2 + k + 1] : 0.0;
+        const double l2 = k + 2 > lane ? Ld[lane * LDS2 + k + 2] : 0.0;
+        const double l3 = k + 3 > lane ? Ld[lane * LDS2 + k + 3] : 0.0;
+        p0 = fma(l0, xb[k + 0], p0); p1 = fma(l1, xb[k + 1], p1);
+        p2 = fma(l2, xb[k + 2], p2); p3 = fma(l3, xb[k + 3], p3);
       }
       const double xA = (p0 + p1) + (p2 + p3);
       xr[(c & 3) * MB + lane] = xA; xr[(c & 3) * MB + 32 + lane] = xB;
       a.c.x[c * MB + lane] = xA; a.c.x[c * MB + 32 + lane] = xB;
     }
-    if (c > 0) land(c - 1);
-    __syncthreads();
-    if (tid == kThreads - 1) { __threadfence(); st_release(a.c.flags + 2 * nbm * nbm + c, epoch); }  // x_c for the helpers
+    __syncthreads();  // (C) x_c is written
+    if (tid == 4 * 32) { __threadfence(); st_release(a.c.flags + 2 * nbm * nbm + c, epoch); }  // x_c for the helpers
     trace_put(a.c, slot0 + c, 2, c, c, t_begin, t_ready);
   }
 }

@@ -26,7 +26,7 @@ big = nb > 16  # macro-tile kernel (m3r_gn_chol64.cu): slots = chain steps, then
 if big:
     nbm = (7 * (N - 1) + 1 + 63) // 64
     nb = 2 * nbm
-    cap = nbm + be._lib.m3r_debug_chol64_tasklist(nbm, None, 0) + nb + 4 * nbm
+    cap = nbm + be._lib.m3r_debug_chol64_tasklist(nbm, None, 0) + nb + 4 * nbm + 8 * nbm + 8
 else:
     cap = nb * (nb + 1) // 2 + nb
 buf = torch.zeros((cap, 4), dtype=torch.int64, device=dev)
@@ -61,6 +61,8 @@ for r in order:
     if t[r, 3] == 0:
         continue
     k, i, j = int(t[r, 0] >> 32), int((t[r, 0] >> 16) & 0xFFFF), int(t[r, 0] & 0xFFFF)
+    if k >= 8:
+        continue
     if big and (k == 3 or (k == 1 and i > j + 2) or (k == 2 and i % 8) or (k >= 4 and not 18 <= i <= 24)):
         continue
     if k >= 4:
