@@ -1,12 +1,13 @@
-// m3r_gn_chol64.cu — fp64 Cholesky solve of LARGE normal-equation systems (more than 5 panels
-// of 32, i.e. more than 23 keyframes; BASELINE config 5 has N = 512, D = 3577), sm_100a.
+// m3r_gn_chol64.cu — fp64 Cholesky solve of normal-equation systems of more than 5 panels
+// of 32 (more than 23 keyframes: BASELINE configs 3, 4 and 5 — N = 32, 64, 512), sm_100a.
 //
 // Replaces, like m3r_gn_solve.cu for small systems, SparseBlock::solve of the reference
 // (gn_kernels.cu:132-153: Eigen::SimplicialLLT in fp64 on the host) plus the retraction and the
 // convergence test that follow it (gn_kernels.cu:1209-1222).  Same augmented matrix [H b; b^T 1],
 // same failure semantics (non-positive pivot => zero step).
 //
-// Why a second kernel.  The 32x32 dataflow kernel ran N = 512 at 5.4 TFLOP/s: (i) every tile
+// Why a second kernel.  The 32x32 dataflow kernel (m3r_gn_solve.cu, still used up to 5 panels, where
+// it is the faster one) ran N = 512 at 5.4 TFLOP/s: (i) every tile
 // product pulled two 8 KB tiles from L2 for 32 K fma (3.8 GB per factorisation) and multiplied
 // them with DFMA from shared memory at 6 loads per 8 fma; (ii) a left-looking tile is summed by
 // ONE CTA, so the diagonal tile of a late block column (110 products) arrived long after the
@@ -14,9 +15,10 @@
 // Here:
 //   * tiles are 64x64, products run on the fp64 tensor pipe (mma.sync.m8n8k4.f64, DMMA): a CTA
 //     of 8 warps (2x4, 32x16 outputs each) streams 64x32 operand panels through a 4-stage
-//     cp.async ring; 2 shared-memory loads feed 8 fma per thread and a product moves 64 KB from
-//     L2 for 262 K fma (4x less traffic per flop);
-//   * the sum of a tile over block columns k is cut into CHUNKS of 4 block columns.  A chunk
+//     cp.async ring; 6 shared-memory loads feed 8 DMMA (64 fma per thread) and a product moves
+//     64 KB from L2 for 262 K fma (4x less traffic per flop);
+//   * the sum of a tile over block columns k is cut into CHUNKS (4 block columns near the
+//     chain, 16 far from it; layout in m3r_gn.cuh).  A chunk
 //     is a task of its own: any CTA computes it and subtracts it from the tile in place, in
 //     chunk order (a per-tile progress counter), so the bits do not depend on who ran what.
 //     Tasks sit in one statically sorted list; CTAs take the next entry with an atomic counter.
@@ -27,7 +29,10 @@
 //   * the critical path — POTRF(J-1) -> L(J,J-1) = S L^-T -> last SYRK term -> POTRF(J) — is
 //     ONE dedicated CTA (block 0) that never leaves its SM: L(J-1,J-1) stays in shared memory,
 //     the TRSM of the sub-diagonal tile is private, and inside a 64-wide diagonal block the two
-//     32-wide POTRFs, the TRSM and the update between them need no flag at all.
+//     32-wide POTRFs, the TRSM and the update between them need no flag at all.  The last terms
+//     of the two tiles the chain needs next are formed by two SIDEKICK CTAs (blocks 1, 2) on SMs
+//     of their own; the back substitution is block 0 again, with one helper CTA per block column.
+// Measured (profiles/r3/): N = 512 solve step 2.75 -> 1.35 ms, N = 64 228 -> 150 us, N = 32 105 -> 93 us.
 // Summation order differs from the 32x32 kernel (and from Eigen): results agree to fp64
 // rounding, not bit for bit; they ARE bit-identical from run to run and between a single-GPU and
 // an edge-sharded solve (same kernel, same inputs, fixed chunk order).
