@@ -46,7 +46,7 @@ constexpr int kThreads = 256;      // 8 warps: 2 (rows of 32) x 4 (columns of 16
 constexpr int LDP = 34;            // row stride of a 64x32 operand panel (16-B aligned rows for cp.async,
                                    // == 2 mod 16 for the conflict-free fragment pattern below)
 constexpr int LDC = 65;            // row stride of a 64x64 chain tile (odd: lane-per-row access is conflict free)
-constexpr int kStages = 4;
+constexpr int kStages = 6;  // three products of two 32-column stages each
 constexpr int kPanel = MB * LDP;
 constexpr int kStageD = 2 * kPanel;
 constexpr int kTileC = MB * LDC;
@@ -443,19 +443,26 @@ __device__ __forceinline__ void run_task(const Args& a, const int4 tk, int epoch
   const unsigned long long t_ready = a.c.trace ? gtimer() : 0ull;
   double acc[4][2][2];
   zero_acc(acc);
-  const int nsteps = 2 * (k1 - k0);  // 32 columns per step
-  for (int s = 0; s < kStages - 1; s++) {
-    if (s < nsteps) issue_stage(a, I, J, k0 * MB + s * 32, smem + s * kStageD);
+  // One product (64 block columns = two 32-column stages) per pipeline step, three steps in the ring: one
+  // CTA barrier and one round of copy issue per 262 K fma instead of two.
+  const int npairs = k1 - k0;
+  auto issue_pair = [&](int pq) {
+    double* slot = smem + (pq % 3) * 2 * kStageD;
+    issue_stage(a, I, J, (k0 + pq) * MB, slot);
+    issue_stage(a, I, J, (k0 + pq) * MB + 32, slot + kStageD);
+  };
+  for (int pq = 0; pq < 2; pq++) {
+    if (pq < npairs) issue_pair(pq);
     cp_async_commit();
   }
-  for (int s = 0; s < nsteps; s++) {
-    cp_async_wait<kStages - 2>();
-    __syncthreads();  // stage s has landed for everybody; stage s-1 is no longer read
-    const int nx = s + kStages - 1;
-    if (nx < nsteps) issue_stage(a, I, J, k0 * MB + nx * 32, smem + (nx % kStages) * kStageD);
+  for (int pq = 0; pq < npairs; pq++) {
+    cp_async_wait<1>();
+    __syncthreads();  // product pq has landed for everybody; the slot of product pq-1 is no longer read
+    if (pq + 2 < npairs) issue_pair(pq + 2);
     cp_async_commit();
-    const double* st = smem + (s % kStages) * kStageD;
+    const double* st = smem + (pq % 3) * 2 * kStageD;
     warp_mma<4, 2, LDP>(st + wr * 32 * LDP, (I != J ? st + kPanel : st) + wc * 16 * LDP, 2, acc);
+    warp_mma<4, 2, LDP>(st + kStageD + wr * 32 * LDP, (I != J ? st + kStageD + kPanel : st + kStageD) + wc * 16 * LDP, 2, acc);
   }
   cp_async_wait<0>();
   if (kc > 0) wait_flag(prog_flag(a, I, J), (epoch << 12) | kc);  // earlier chunks are in (fixed order)
@@ -805,6 +812,7 @@ constexpr int kBackSlot = kBackNear * MB * MB + MB * LDS2;  // doubles per slot:
 constexpr int kBackScratch = 16 * MB;                       // xr, sred, ex, xb
 constexpr size_t kBackSmemBytes = (size_t)(kBackScratch + 2 * kBackSlot) * sizeof(double);
 constexpr size_t kSmemBytes = kSmemBytesFact > kBackSmemBytes ? kSmemBytesFact : kBackSmemBytes;  // 206 848 B
+static_assert(kSmemBytes >= (size_t)kStages * kStageD * sizeof(double), "pipeline ring");
 static_assert(kSmemBytes <= 227 * 1024, "dynamic shared memory of chol64_kernel exceeds the 227 KB of sm_100a");
 
 __device__ __forceinline__ void back_chain(const Args& a, int epoch, double* smem, int slot0) {
