@@ -213,13 +213,12 @@ def test_cholesky_independent_of_cta_timing(backends, N):
 
 @pytest.mark.parametrize("N", [40, 150, 260])
 def test_many_keyframes_dense_cholesky(backends, orc, N):
-    """Graphs whose normal equations span many 32x32 tiles (N=40: 9x9 tiles, single-CTA back
-    substitution; N=150: 33x33, distributed back substitution; N=260: 57x57, pose rows beyond the
-    assembly kernel's shared-memory row buffer take its global-memory path): the
-    device assembly + tile-dataflow Cholesky (flags across >100 CTAs, back-substitution chain)
-    against a numpy fp64 assembly + solve of the SAME per-edge blocks (SparseBlock semantics,
-    gn_kernels.cu:71-153), which isolates the solver from the conditioning of these tiny-image
-    problems; the whole solve is then checked against the oracle and for determinism."""
+    """Graphs whose normal equations span many tiles — the 64x64 macro-tile kernel (N=40: 5 block columns;
+    N=150: 17; N=260: 29, pose rows beyond the assembly kernel's shared-memory row buffer take its
+    global-memory path): the device assembly + Cholesky (chain CTA, sidekicks, list workers, back
+    substitution with its helper CTAs) against a numpy fp64 assembly + solve of the SAME per-edge blocks
+    (SparseBlock semantics, gn_kernels.cu:71-153), which isolates the solver from the conditioning of these
+    tiny-image problems; the whole solve is then checked against the oracle and for determinism."""
     H, W = 12, 16
     g = synth.make_graph(N=N, counts={1: None, 2: N - 2, 7: N // 2, "random": N // 3}, H=H, W=W, seed=1240 + N,
                          device=DEV)
