@@ -68,8 +68,9 @@ __host__ __device__ inline int gn_cdiv(int a, int b) { return (a + b - 1) / b; }
 // the old ones are all available when the tile's column enters the task list's window and are
 // released TOGETHER — their subtractions from the tile are serialised by the progress counter, so
 // they are few and long (with chunks of 4 everywhere a column's tiles spent 30 % of their CTA time
-// waiting for their turn).
-constexpr int kGnRecent = 8;
+// waiting for their turn).  Swept at N = 512 (profiles/r3/r3_sweep_chunks.txt): recent region 4 / 8 / 12
+// block columns -> solve step 1.24 / 1.36 / 1.44 ms; old chunks of 8 / 16 / 24 / 32 within 2 %.
+constexpr int kGnRecent = 4;
 constexpr int kGnKCOld = 16;
 __host__ __device__ inline int gn_chunk_step(int d) { return d < kGnRecent ? kGnKC : kGnKCOld; }  // d = R - t - end
 __host__ __device__ inline int gn_nch(int R, int t) {

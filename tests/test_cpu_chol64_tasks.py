@@ -35,7 +35,7 @@ def tasklist(backends):
 TAIL_CHAIN = 2
 
 
-RECENT, KC_OLD = 8, 16
+RECENT, KC_OLD = 4, 16
 
 
 def _nch(R, t):  # chunks of [0, R) from the end: a tail of t, RECENT / KC chunks of KC, then chunks of KC_OLD
