@@ -14,11 +14,11 @@
 // column before it was finished; (iii) per 32 columns the critical path crossed two flag hops.
 // Here:
 //   * tiles are 64x64, products run on the fp64 tensor pipe (mma.sync.m8n8k4.f64, DMMA): a CTA
-//     of 8 warps (2x4, 32x16 outputs each) streams 64x32 operand panels through a 4-stage
-//     cp.async ring; 6 shared-memory loads feed 8 DMMA (64 fma per thread) and a product moves
+//     of 8 warps (2x4, 32x16 outputs each) streams 64x32 operand panels through a cp.async
+//     ring of three products (two 32-column stages each); 6 shared-memory loads feed 8 DMMA (64 fma per thread) and a product moves
 //     64 KB from L2 for 262 K fma (4x less traffic per flop);
-//   * the sum of a tile over block columns k is cut into CHUNKS (4 block columns near the
-//     chain, 16 far from it; layout in m3r_gn.cuh).  A chunk
+//   * the sum of a tile over block columns k is cut into CHUNKS (a tail of 2-4 block columns
+//     and one chunk of 4 near the chain, chunks of 16 far from it; layout in m3r_gn.cuh).  A chunk
 //     is a task of its own: any CTA computes it and subtracts it from the tile in place, in
 //     chunk order (a per-tile progress counter), so the bits do not depend on who ran what.
 //     Tasks sit in one statically sorted list; CTAs take the next entry with an atomic counter.
