@@ -291,6 +291,46 @@ def test_gn_edge_cases(backends, orc):
     assert float((T - g2["T_gt"]).abs().max()) < 0.5 * float((g2["Twc"] - g2["T_gt"]).abs().max())
 
 
+def test_cholesky_size_sweep(backends):
+    """Both Cholesky kernels over system sizes — every parity of the panel count, exact and padded dimensions,
+    the switch between the kernels at 5 panels of 32: one GN iteration against a numpy fp64 solve of the SAME
+    per-edge blocks (within fp32 rounding of dx), twice for bit-reproducibility (profiles/fuzz_chol64.py is the
+    longer form, 45 sizes: profiles/r3/r3_fuzz_chol64.txt)."""
+    prm = backends._params(backends.GN_RAYS, 0.003, 10.0, 0.0, 1.5)
+    for N in (2, 5, 10, 19, 23, 24, 25, 28, 33, 37, 42, 56, 65, 74, 101, 129, 184):
+        rng = np.random.RandomState(N)
+        counts = {1: None}
+        if N > 3:
+            counts[2] = int(rng.randint(1, N - 2))
+        if N > 9:
+            counts[int(rng.randint(3, 8))] = int(rng.randint(1, N - 8))
+            counts["random"] = int(rng.randint(1, max(2, N // 3)))
+        g = synth.make_graph(N=N, counts=counts, H=12, W=16, seed=7000 + N, device=DEV)
+        out = []
+        for _ in range(2):
+            s = backends.GNSolver(prm, g["Twc"].clone(), g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"])
+            blocks = _np(s.accumulate()).copy()
+            out.append(s.solve_step(0.0).clone())
+        torch.cuda.synchronize()
+        assert torch.equal(out[0], out[1]), f"N={N}: not reproducible"
+        D = 7 * (N - 1)
+        Hd, bd = np.zeros((D, D)), np.zeros(D)
+        ii, jj = _np(g["ii"]), _np(g["jj"])
+        for e in range(g["M"]):
+            S, v = blocks[e, :49].reshape(7, 7), blocks[e, 49:56]
+            i, j = int(ii[e]) - 1, int(jj[e]) - 1
+            si, sj = slice(7 * i, 7 * i + 7), slice(7 * j, 7 * j + 7)
+            if i >= 0:
+                Hd[si, si] += S; bd[si] -= v
+            if j >= 0:
+                Hd[sj, sj] += S; bd[sj] += v
+            if i >= 0 and j >= 0:
+                Hd[si, sj] -= S; Hd[sj, si] -= S
+        ref = (-np.linalg.solve(Hd, bd)).reshape(N - 1, 7)
+        err = np.abs(_np(out[0]) - ref).max() / max(1.0, np.abs(ref).max())
+        assert err < 2e-6, f"N={N}: |dx - numpy fp64 solve| = {err:.2e} relative"
+
+
 @pytest.mark.parametrize("N", [32, 100])
 def test_macro_tile_cholesky_failure_and_early_exit(backends, N):
     """The 64x64 macro-tile kernel (systems of more than 5 panels of 32): a singular system (no usable match) is
