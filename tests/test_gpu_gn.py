@@ -182,14 +182,14 @@ def test_rays_full_size_vs_reference_and_properties(backends, ref_ext):
     assert torch.equal(Ta, Tb)
 
 
-@pytest.mark.parametrize("N", [8, 20, 32, 40, 150])
+@pytest.mark.parametrize("N", [8, 20, 32, 40, 150, 260])
 def test_cholesky_independent_of_cta_timing(backends, N):
     """The tile-dataflow Cholesky hands tiles between CTAs through flags only.  Stalling the owners
     of the diagonal tiles (which = 1) or of the off-diagonal tiles (which = 2) for 40 us before
     they start, or every task for a random time before it starts and before it stores
     (which >= 3), must leave every bit of dx and of the poses unchanged.  N = 8, 20 (2 and 5 panels of 32):
     the 32x32 dataflow kernel with the private TRSM of the diagonal owners, whose source tile another CTA
-    overwrites in place; N = 32, 40, 150 (4, 5 and 17 block columns of 64): the macro-tile kernel — chunk
+    overwrites in place; N = 32, 40, 150, 260 (4, 5, 17 and 29 block columns of 64): the macro-tile kernel — chunk
     tasks subtracted in place in progress order, the chain CTA's two teams, the back-substitution helpers."""
     g = synth.make_graph(N=N, counts={1: None, 2: N - 2, "random": 2}, H=48, W=64, seed=1250 + N, device=DEV)
 
