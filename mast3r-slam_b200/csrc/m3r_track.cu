@@ -196,7 +196,9 @@ track_kernel(const TrackArgs a) {
     }
     __syncthreads();
     if (tid == 0) {
-      double L[7][7], rhs[7];
+      // 7x7 Cholesky solve on one thread: it is on the critical path of every iteration, so no fp64 square
+      // root or division (~35 of them, ~1.4 us): one rsqrt per pivot, everything else multiplies by it
+      double L[7][7], rhs[7], rinv[7];
       for (int r = 0; r < 7; r++) {
         for (int c = 0; c <= r; c++) L[r][c] = tot[r * (r + 1) / 2 + c];
         rhs[r] = -tot[28 + r];
@@ -205,14 +207,15 @@ track_kernel(const TrackArgs a) {
       bool okc = true;
       for (int j = 0; j < 7 && okc; j++) {  // torch.linalg.cholesky(H) (tracker.py:168)
         double d = L[j][j];
-        for (int k = 0; k < j; k++) d -= L[j][k] * L[j][k];
+        for (int k = 0; k < j; k++) d = fma(-L[j][k], L[j][k], d);
         if (!(d > 0.0)) { okc = false; break; }
-        const double ljj = sqrt(d);
-        L[j][j] = ljj;
+        const double rr = rsqrt(d);
+        rinv[j] = rr;
+        L[j][j] = d * rr;
         for (int i = j + 1; i < 7; i++) {
           double s = L[i][j];
-          for (int k = 0; k < j; k++) s -= L[i][k] * L[j][k];
-          L[i][j] = s / ljj;
+          for (int k = 0; k < j; k++) s = fma(-L[i][k], L[j][k], s);
+          L[i][j] = s * rr;
         }
       }
       int stop = 0;
@@ -221,13 +224,13 @@ track_kernel(const TrackArgs a) {
       } else {
         for (int i = 0; i < 7; i++) {  // cholesky_solve
           double s = rhs[i];
-          for (int k = 0; k < i; k++) s -= L[i][k] * rhs[k];
-          rhs[i] = s / L[i][i];
+          for (int k = 0; k < i; k++) s = fma(-L[i][k], rhs[k], s);
+          rhs[i] = s * rinv[i];
         }
         for (int i = 6; i >= 0; i--) {
           double s = rhs[i];
-          for (int k = i + 1; k < 7; k++) s -= L[k][i] * rhs[k];
-          rhs[i] = s / L[i][i];
+          for (int k = i + 1; k < 7; k++) s = fma(-L[k][i], rhs[k], s);
+          rhs[i] = s * rinv[i];
         }
         float tau[7], pose[8];
         float nn = 0.f;
