@@ -172,8 +172,7 @@ track_kernel(const TrackArgs a) {
       for (int w = 0; w < kTrkThreads / 32; w++) s += red[w][tid];
       part[(size_t)blockIdx.x * kTrkVals + tid] = s;
     }
-    __threadfence();
-    grid.sync();
+    grid.sync();  // (orders the partial stores before every CTA's loads below: no separate fence needed)
     // every CTA: identical fixed-order fp64 reduction + solve
     // 7 x 36 threads: thread (chunk, value) sums every 7th partial (independent L2 loads in
     // flight instead of one 296-long dependent walk per value), then the 7 chunk sums are added
