@@ -34,10 +34,12 @@ __device__ __forceinline__ void wait_flag(const int* f, int epoch) {
   }
   __syncthreads();
 }
-// Publish: every thread's global writes so far become visible to whoever acquires *f.
+// Publish: every thread's global writes so far become visible to whoever acquires *f (the CTA barrier orders
+// them before thread 0, whose st.release.gpu is cumulative: no separate __threadfence, which only added a
+// second MEMBAR).
 __device__ __forceinline__ void post_flag(int* f, int epoch) {
   __syncthreads();
-  if (threadIdx.x == 0) { __threadfence(); st_release(f, epoch); }
+  if (threadIdx.x == 0) { st_release(f, epoch); }
 }
 
 // Optional timeline of the dataflow kernel (diagnostics; set by m3r_debug_chol_trace): per

@@ -422,7 +422,7 @@ __device__ __forceinline__ void issue_stage(const Args& a, int I, int J, int kco
 // which are warp 0's
 __device__ __forceinline__ void post_flag_last(int* f, int value) {
   __syncthreads();
-  if (threadIdx.x == kThreads - 1) { __threadfence(); st_release(f, value); }
+  if (threadIdx.x == kThreads - 1) { st_release(f, value); }
 }
 
 __device__ __forceinline__ void run_task(const Args& a, const int4 tk, int epoch, double* smem, double* s_dinv,
@@ -614,7 +614,7 @@ __device__ __forceinline__ void team_publish_tile64(double* __restrict__ A, int 
   double* dst = A + (size_t)bi * MB * Dp + (size_t)bj * MB;
   for (int idx = threadIdx.x & 127; idx < MB * MB; idx += 128) __stcg(dst + (size_t)(idx >> 6) * Dp + (idx & 63), s[(idx >> 6) * LDC + (idx & 63)]);
   team_sync(team);
-  if ((threadIdx.x & 127) == 0) { __threadfence(); st_release(flag, epoch); }
+  if ((threadIdx.x & 127) == 0) { st_release(flag, epoch); }
 }
 
 // diagnostics: a trace entry written by the calling thread (team 1's timeline inside a chain step)
@@ -649,7 +649,7 @@ __device__ __forceinline__ void run_chain(const Args& a, int epoch, double* smem
       store_tile64(a.c.A, a.c.Dp, J, J - 1, X);
       __syncthreads();
       if (warp == 7) {
-        if ((tid & 31) == 0) { __threadfence(); st_release(tile_flag(a, J, J - 1), epoch); }
+        if ((tid & 31) == 0) { st_release(tile_flag(a, J, J - 1), epoch); }
       } else {
         const int r0 = warp < 3 ? (warp == 0 ? 0 : 16) : 32 + ((warp - 3) >> 1) * 16;
         const int c0 = warp < 3 ? (warp == 2 ? 16 : 0) : ((warp - 3) & 1) * 16;
@@ -971,7 +971,7 @@ __device__ __forceinline__ void back_chain(const Args& a, int epoch, double* sme
       a.c.x[c * MB + lane] = xA; a.c.x[c * MB + 32 + lane] = xB;
     }
     __syncthreads();  // (C) x_c is written
-    if (tid == 4 * 32) { __threadfence(); st_release(a.c.flags + 2 * nbm * nbm + c, epoch); }  // x_c for the helpers
+    if (tid == 4 * 32) { st_release(a.c.flags + 2 * nbm * nbm + c, epoch); }  // x_c for the helpers
     trace_put(a.c, slot0 + c, 2, c, c, t_begin, t_ready);
   }
 }
