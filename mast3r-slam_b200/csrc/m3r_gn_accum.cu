@@ -388,13 +388,17 @@ __device__ __forceinline__ void block_reduce_finish(const AccArgs& a, const floa
 #pragma unroll
     for (int w = 0; w < kAccThreads / 32; w++) s += red[w][threadIdx.x];
     a.part[((size_t)el * a.S + split) * kGnPartStride + threadIdx.x] = s;
-    __threadfence();  // the partial is visible device-wide before the ticket is taken
   }
   __syncthreads();
   if (threadIdx.x == 0) {
-    const int arrived = atomicAdd(a.tickets + e, 1);
+    // one acq_rel atomic is the whole hand-off: its release half publishes this split's partial (the CTA barrier
+    // above orders the 35 stores before it, and a release is cumulative), its acquire half lets the last split
+    // to arrive read the others' partials.  (It replaced a __threadfence by each of the 35 storing threads, the
+    // atomic and a second fence: ~1 us at the tail of every CTA.)
+    int arrived;
+    asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], 1;" : "=r"(arrived) : "l"(a.tickets + e) : "memory");
     const int last = arrived == a.S - 1;
-    if (last) { a.tickets[e] = 0; __threadfence(); }  // acquire side: the other splits' partials
+    if (last) a.tickets[e] = 0;
     s_last = last;
   }
   __syncthreads();
