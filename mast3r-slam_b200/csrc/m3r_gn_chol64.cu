@@ -32,7 +32,7 @@
 //     32-wide POTRFs, the TRSM and the update between them need no flag at all.  The last terms
 //     of the two tiles the chain needs next are formed by two SIDEKICK CTAs (blocks 1, 2) on SMs
 //     of their own; the back substitution is block 0 again, with one helper CTA per block column.
-// Measured (profiles/r3/): N = 512 solve step 2.75 -> 1.21 ms, N = 64 228 -> 150 us, N = 32 105 -> 93 us.
+// Measured (profiles/r3/): N = 512 solve step 2.75 -> 1.17 ms, N = 64 228 -> 150 us, N = 32 105 -> 91 us.
 // Summation order differs from the 32x32 kernel (and from Eigen): results agree to fp64
 // rounding, not bit for bit; they ARE bit-identical from run to run and between a single-GPU and
 // an edge-sharded solve (same kernel, same inputs, fixed chunk order).
